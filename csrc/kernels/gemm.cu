@@ -1,0 +1,265 @@
+// gemm.cu — host side of the tcgen05 GEMM engine: tensor-map construction,
+// tile-shape heuristic, launch. C entry points: tdist_gemm (plain GEMM, also the
+// swap-AB skinny path) and tdist_gemm_fused (AG+GEMM / GEMM+RS / GEMM+AR).
+#include <mutex>
+#include <unordered_map>
+
+#include "../runtime/driver.h"
+#include "gemm_sm100.cuh"
+
+namespace tdist {
+
+// ---- tensor-map cache ---------------------------------------------------------
+struct TmapKey {
+  const void* ptr;
+  uint64_t rows, cols, ld;
+  uint32_t box_rows;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+  }
+};
+struct TmapHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    h = h * 1000003u ^ k.rows;
+    h = h * 1000003u ^ k.cols;
+    h = h * 1000003u ^ k.ld;
+    h = h * 1000003u ^ k.box_rows;
+    return h;
+  }
+};
+
+// 2-D K-major 16-bit tensor [rows, cols] with row stride ld (elements); box = [box_rows, 64], 128B swizzle
+static int make_tmap(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapHash> cache;
+  const TmapKey key{ptr, rows, cols, ld, box_rows};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  const DriverApi& d = driver();
+  if (!d.ok) {
+    set_error("CUDA driver not available: " + d.err);
+    return -1;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = d.cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides,
+                                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed: " + cu_err(r));
+    return -1;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, *out);
+  return 0;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int BN, int ST>
+static int launch_inst(const GemmParams& p, int grid, cudaStream_t s, bool cooperative) {
+  using L = GemmSmem<BN, ST>;
+  static bool attr_set = false;
+  auto kern = gemm_sm100_kernel<BN, ST>;
+  if (!attr_set) {
+    TDIST_RT_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = cooperative ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TDIST_RT_TRY(cudaLaunchKernelEx(&cfg, kern, p));
+  return 0;
+}
+
+static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
+  static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64, 32};
+  if (forced > 0) {
+    for (int c : cands)
+      if (c == forced) return c;
+  }
+  long best_cost = -1;
+  int best = 128;
+  for (int bn : cands) {
+    const long tiles = long(M_tiles) * ((N + bn - 1) / bn);
+    const long waves = (tiles + ctas - 1) / ctas;
+    const long cost = waves * (bn + 24);  // +24: fixed per-tile cost (epilogue hand-off, pipeline refill)
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
+}
+
+static int dispatch(const GemmParams& p, int bn, int grid, cudaStream_t s, bool coop) {
+  switch (bn) {
+    case 256: return launch_inst<256, 4>(p, grid, s, coop);
+    case 224: return launch_inst<224, 4>(p, grid, s, coop);
+    case 192: return launch_inst<192, 5>(p, grid, s, coop);
+    case 160: return launch_inst<160, 5>(p, grid, s, coop);
+    case 128: return launch_inst<128, 6>(p, grid, s, coop);
+    case 112: return launch_inst<112, 6>(p, grid, s, coop);
+    case 96: return launch_inst<96, 7>(p, grid, s, coop);
+    case 64: return launch_inst<64, 8>(p, grid, s, coop);
+    case 32: return launch_inst<32, 8>(p, grid, s, coop);
+  }
+  set_error("gemm: unsupported BLOCK_N");
+  return -1;
+}
+
+static int check_common(const tdist_gemm_args* a) {
+  if (a->dtype != TDIST_BF16 && a->dtype != TDIST_F16) {
+    set_error("gemm: dtype must be bf16 or fp16");
+    return -1;
+  }
+  if (a->K % 8 != 0 || a->N % 8 != 0 || a->lda % 8 != 0 || a->ldb % 8 != 0 || a->ldc % 8 != 0) {
+    set_error("gemm: K, N and leading dimensions must be multiples of 8 (16-byte rows)");
+    return -1;
+  }
+  if (a->M <= 0 || a->N <= 0 || a->K <= 0) {
+    set_error("gemm: empty problem");
+    return -1;
+  }
+  return 0;
+}
+
+}  // namespace tdist
+
+using namespace tdist;
+
+extern "C" {
+
+int tdist_gemm(const tdist_gemm_args* a, void* stream) {
+  if (check_common(a) != 0) return -1;
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = GEMM_PLAIN;
+  p.M = a->M;
+  p.N = a->N;
+  p.K = a->K;
+  p.c = a->c;
+  p.ldc = a->ldc;
+  p.is_bf16 = a->dtype == TDIST_BF16;
+  p.rows_per_rank = a->M;
+  p.transpose_out = a->transpose_out;
+  p.ctx.world = 1;
+  const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
+  const int tiles_m = (a->M + kBlockM - 1) / kBlockM;
+  const int bn = pick_block_n(tiles_m, a->N, sms, a->block_n);
+  const int tiles = tiles_m * ((a->N + bn - 1) / bn);
+  p.group_m = a->group_m > 0 ? a->group_m : 8;
+  p.num_comm_ctas = 0;
+  if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
+  if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn) != 0) return -1;
+  const int grid = tiles < sms ? tiles : sms;
+  return dispatch(p, bn, grid, static_cast<cudaStream_t>(stream), false);
+}
+
+int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream) {
+  if (check_common(a) != 0) return -1;
+  const SymmCtx c = to_ctx(&f->ctx);
+  const int W = c.world;
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = f->mode;
+  p.ctx = c;
+  p.M = a->M;
+  p.N = a->N;
+  p.K = a->K;
+  p.is_bf16 = a->dtype == TDIST_BF16;
+  p.flags = f->flags;
+  p.flags2 = f->flags2;
+  p.counters = f->counters;
+  p.ps = PhaseState{f->phase, f->done};
+  p.group_m = a->group_m > 0 ? a->group_m : 8;
+  const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
+  int comm = f->num_comm_ctas;
+  int tiles_m;
+  if (f->mode == TDIST_GEMM_AG) {
+    // a->a = own shard [M/W, K]; f->ws = symmetric workspace [2][M][K]; a->M = full M
+    if (a->M % W != 0) {
+      set_error("ag_gemm: M must be divisible by world size");
+      return -1;
+    }
+    p.rows_per_rank = a->M / W;
+    p.a_local = a->a;
+    p.a_ws = f->ws;
+    p.c = a->c;
+    p.ldc = a->ldc;
+    if (W == 1) comm = 0;
+    if (comm < 0) comm = W > 1 ? 16 : 0;
+    const size_t par = size_t(a->M) * a->K * 2;
+    if (make_tmap(&p.tma_a_local, a->a, p.rows_per_rank, a->K, a->lda, kBlockM) != 0) return -1;
+    if (make_tmap(&p.tma_a[0], f->ws, a->M, a->K, a->K, kBlockM) != 0) return -1;
+    if (make_tmap(&p.tma_a[1], static_cast<char*>(f->ws) + par, a->M, a->K, a->K, kBlockM) != 0) return -1;
+    tiles_m = ((p.rows_per_rank + kBlockM - 1) / kBlockM) * W;
+  } else if (f->mode == TDIST_GEMM_RS) {
+    // a->a = [M, K/W] local; f->ws = symmetric scatter buffer [2][W][M/W][N]; f->out = [M/W, N]
+    if (a->M % W != 0) {
+      set_error("gemm_rs: M must be divisible by world size");
+      return -1;
+    }
+    p.rows_per_rank = a->M / W;
+    p.c = f->ws;
+    p.out = f->out;
+    p.ldc = a->N;
+    comm = 0;
+    if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
+    tiles_m = ((p.rows_per_rank + kBlockM - 1) / kBlockM) * W;
+  } else if (f->mode == TDIST_GEMM_AR) {
+    // a->a = [M, K/W]; f->ws = symmetric tile buffer [2][M][ldc]; f->out = [M, ldc]
+    p.rows_per_rank = a->M;
+    p.c = f->ws;
+    p.out = f->out;
+    p.ldc = a->ldc;
+    p.ar_one_shot = f->ar_one_shot;
+    p.use_mc = c.mc_base != nullptr && f->use_mc;
+    if (comm < 0) comm = 8;
+    if (comm < 1) comm = 1;
+    if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
+    tiles_m = (a->M + kBlockM - 1) / kBlockM;
+  } else {
+    set_error("gemm_fused: unknown mode");
+    return -1;
+  }
+  p.num_comm_ctas = comm;
+  const int gemm_ctas_max = sms - comm;
+  if (gemm_ctas_max < 1) {
+    set_error("gemm_fused: no SMs left for the GEMM");
+    return -1;
+  }
+  const int bn = pick_block_n(tiles_m, a->N, gemm_ctas_max, a->block_n);
+  if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn) != 0) return -1;
+  const int tiles = tiles_m * ((a->N + bn - 1) / bn);
+  // RS: the whole grid takes part in the reduction tail, so always launch every SM
+  const int gemm_ctas = (f->mode == TDIST_GEMM_RS) ? gemm_ctas_max : (tiles < gemm_ctas_max ? tiles : gemm_ctas_max);
+  return dispatch(p, bn, comm + gemm_ctas, static_cast<cudaStream_t>(stream), true);
+}
+
+}  // extern "C"

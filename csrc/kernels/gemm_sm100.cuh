@@ -1,0 +1,538 @@
+// gemm_sm100.cuh — the shared tcgen05/TMEM/TMA GEMM engine.
+//
+// One persistent, warp-specialised kernel computes C[M,N] = A[M,K] * B[N,K]^T
+// (both operands K-major, bf16/fp16 in, fp32 accumulate in TMEM) and is
+// specialised at run time into the fused compute+communication ops:
+//
+//   PLAIN  plain GEMM (gemm_persistent)
+//   AG     AllGather+GEMM: extra "comm" CTAs push this rank's A shard to every
+//          peer with bulk async copies over NVLink while the GEMM CTAs consume
+//          shards in arrival order, gated per 128-row block by flags
+//          (reference op: kernels/nvidia/allgather_gemm.py:158-264, 534-653 —
+//          there the gather runs on the copy engine of a second stream).
+//   RS     GEMM+ReduceScatter: the epilogue stores each partial tile straight
+//          into the owner rank's scatter slot over NVLink, a per-block counter
+//          publishes completion, and the same kernel finishes with the
+//          flag-gated fp32 reduction of the W slots
+//          (reference: gemm_reduce_scatter.py:121-250 FUSE_SCATTER + K15).
+//   AR     GEMM+AllReduce: tiles go to a symmetric buffer with a per-tile flag;
+//          comm CTAs reduce finished tiles across ranks with NVLS
+//          multimem.ld_reduce (or P2P loads) while later tiles are computed
+//          (reference: gemm_allreduce.py:123-315).
+//
+// Warp roles per GEMM CTA (256 threads): warp 0 = TMA producer, warp 1 = MMA
+// issuer (single elected thread, tcgen05.mma cta_group::1, M=128), warp 2 =
+// TMEM allocator, warps 4-7 = epilogue (tcgen05.ld -> bf16 -> smem transpose
+// -> coalesced 128-byte row stores, local or peer). Accumulators are double
+// buffered in TMEM so the epilogue of tile i overlaps the mainloop of tile i+1.
+// Comm CTAs take the LOWEST block indices so they are always scheduled.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace tdist {
+
+enum GemmMode : int { GEMM_PLAIN = 0, GEMM_AG = 1, GEMM_RS = 2, GEMM_AR = 3 };
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // 64 x 16-bit = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kGemmThreads = 256;
+
+struct GemmParams {
+  CUtensorMap tma_a[2];     // AG: gathered workspace for parity 0/1; otherwise [0] only
+  CUtensorMap tma_a_local;  // AG: this rank's own shard [M/W, K]
+  CUtensorMap tma_b;
+  SymmCtx ctx;
+  void* c;        // PLAIN/AG: output [M, N]; RS: scatter buffer (symm, [2][W][M/W][N]); AR: symm tile buffer [2][M][ldc]
+  void* out;      // RS: final output [M/W, N]; AR: final output [M, ldc] (symmetric when two-shot)
+  long long ldc;  // row stride of c in elements
+  int M, N, K;
+  int mode;
+  int is_bf16;
+  int num_comm_ctas;  // CTAs [0, num_comm_ctas) are comm CTAs, the rest run the GEMM roles
+  int group_m;        // L2 swizzle: m-blocks per group (PLAIN/AR)
+  // distributed state
+  const void* a_local;  // AG: own shard (rows_per_rank x K), plain device pointer
+  void* a_ws;           // AG: symmetric gather workspace [2][M][K]
+  uint32_t* flags;      // symmetric flag area (layout depends on mode)
+  uint32_t* flags2;     // AR two-shot: "reduced tile landed" flags [tiles]
+  uint32_t* counters;   // local tile counters (RS: per m-block)
+  PhaseState ps;
+  int rows_per_rank;  // M / W for AG/RS, M otherwise
+  int ar_one_shot;    // AR: every rank reduces every tile (small outputs)
+  int use_mc;         // AR: NVLS available
+  int transpose_out;  // PLAIN: C is written transposed (swap-AB skinny GEMMs)
+};
+
+template <int BLOCK_N, int STAGES>
+struct GemmSmem {
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kEpiBytes = 4 * 32 * 128;  // 4 warps x 32 rows x 128 B
+  static constexpr int kBarOffset = STAGES * kStageBytes + kEpiBytes;
+  static constexpr int kGemmTotal = kBarOffset + (2 * STAGES + 4) * 8 + 16;
+  static constexpr int kPushTotal = 6 * 32 * 1024 + 64;  // AG comm CTA ring
+  static constexpr int kTotal = kGemmTotal > kPushTotal ? kGemmTotal : kPushTotal;
+};
+
+template <int BLOCK_N>
+__host__ __device__ constexpr int tmem_cols() {
+  return 2 * BLOCK_N <= 32 ? 32 : 2 * BLOCK_N <= 64 ? 64 : 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
+}
+
+// ---- tile order -------------------------------------------------------------
+struct TileCoord {
+  int shard;    // AG: source rank of the A rows; RS: owner rank of the C rows; else 0
+  int blk;      // 128-row block inside the shard
+  int row0;     // first global row of the tile
+  int row_end;  // exclusive global row limit for stores (end of shard / matrix)
+  int n_blk;
+};
+__device__ __forceinline__ int blocks_per_shard(const GemmParams& p) { return (p.rows_per_rank + kBlockM - 1) / kBlockM; }
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int t, int tiles_m, int tiles_n) {
+  TileCoord tc;
+  if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
+    // shard-major: AG consumes own shard first then rank+1, ...; RS produces the
+    // segment of rank+1 first and its own last (same rotation as the reference,
+    // allgather_gemm.py:224-229 / gemm_reduce_scatter.py:188,198).
+    const int W = p.ctx.world;
+    const int bps = blocks_per_shard(p);
+    const int per_shard = bps * tiles_n;
+    const int step = t / per_shard;
+    const int r = t - step * per_shard;
+    tc.shard = (p.ctx.rank + step + (p.mode == GEMM_RS ? 1 : 0)) % W;
+    tc.blk = r / tiles_n;
+    tc.n_blk = r % tiles_n;
+    tc.row0 = tc.shard * p.rows_per_rank + tc.blk * kBlockM;
+    tc.row_end = (tc.shard + 1) * p.rows_per_rank;
+  } else {
+    // grouped ordering: walk group_m m-blocks per column sweep for L2 reuse of B
+    const int gm = p.group_m;
+    const int per_group = gm * tiles_n;
+    const int g = t / per_group;
+    const int first_m = g * gm;
+    const int rows = min(gm, tiles_m - first_m);
+    const int r = t - g * per_group;
+    tc.shard = 0;
+    tc.blk = first_m + r % rows;
+    tc.n_blk = r / rows;
+    tc.row0 = tc.blk * kBlockM;
+    tc.row_end = p.M;
+  }
+  return tc;
+}
+
+// ---- comm CTA bodies ----------------------------------------------------------
+// AG producer: push my shard to every peer, 128-row block by block, in the order
+// peers will consume it (peer rank-1 needs it first). One thread drives a ring
+// of bulk copies global -> smem -> peer global; the flag for (src=me, block) is
+// released on the peer after the block's stores have completed.
+__device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem, uint32_t epoch, int comm_idx,
+                                             int num_comm) {
+  constexpr int kChunk = 32 * 1024;
+  constexpr int kSlots = 6;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSlots * kChunk);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kSlots; ++i) ptx::mbar_init(bars + i, 1);
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int W = p.ctx.world, rank = p.ctx.rank;
+  const int bps = blocks_per_shard(p);
+  const size_t row_bytes = size_t(p.K) * 2;
+  const int parity = (epoch >> 1) & 1;
+  const size_t ws_parity_off = size_t(parity) * size_t(p.M) * row_bytes;
+  const char* src_base = static_cast<const char*>(p.a_local);
+  uint32_t bar_phase = 0;  // bit s = parity of slot s
+  // work items: (step t = 1..W-1, block j), flattened, round-robin over comm CTAs
+  const int total = (W - 1) * bps;
+  for (int item = comm_idx; item < total; item += num_comm) {
+    const int t = 1 + item / bps;
+    const int j = item % bps;
+    const int peer = (rank - t + W) % W;
+    const int rows = min(kBlockM, p.rows_per_rank - j * kBlockM);
+    const size_t blk_bytes = size_t(rows) * row_bytes;
+    const char* src = src_base + size_t(j) * kBlockM * row_bytes;
+    char* dst = symm_at(p.ctx, static_cast<char*>(p.a_ws), peer) + ws_parity_off +
+                (size_t(rank) * p.rows_per_rank + size_t(j) * kBlockM) * row_bytes;
+    const int n_chunks = int((blk_bytes + kChunk - 1) / kChunk);
+    int issued = 0;
+    for (; issued < n_chunks && issued < kSlots; ++issued) {
+      const uint32_t bytes = uint32_t(min(size_t(kChunk), blk_bytes - size_t(issued) * kChunk));
+      ptx::mbar_arrive_expect_tx(bars + issued, bytes);
+      ptx::bulk_g2s(smem + issued * kChunk, src + size_t(issued) * kChunk, bytes, bars + issued);
+    }
+    for (int k = 0; k < n_chunks; ++k) {
+      const int slot = k % kSlots;
+      const uint32_t bytes = uint32_t(min(size_t(kChunk), blk_bytes - size_t(k) * kChunk));
+      ptx::mbar_wait(bars + slot, (bar_phase >> slot) & 1);
+      bar_phase ^= 1u << slot;
+      ptx::bulk_s2g(dst + size_t(k) * kChunk, smem + slot * kChunk, bytes);
+      ptx::bulk_commit();
+      // refill the slot used by the previous chunk once its smem has been read
+      if (k >= 1 && issued < n_chunks) {
+        ptx::bulk_wait_read<1>();
+        const int rs = (k - 1) % kSlots;
+        const uint32_t b2 = uint32_t(min(size_t(kChunk), blk_bytes - size_t(issued) * kChunk));
+        ptx::mbar_arrive_expect_tx(bars + rs, b2);
+        ptx::bulk_g2s(smem + rs * kChunk, src + size_t(issued) * kChunk, b2, bars + rs);
+        ++issued;
+      }
+    }
+    ptx::bulk_wait<0>();  // all stores of this block are complete
+    ptx::fence_proxy_async();
+    ptx::fence_acq_rel_sys();
+    // flags layout (AG): [W src][blocks_per_shard]
+    notify(p.ctx, p.flags + rank * bps + j, peer, epoch);
+  }
+}
+
+// RS tail: out[r, :] = sum_src scatter[parity][src][r, :] for my segment,
+// gated per 128-row block by the W arrival flags. Executed by every CTA of the
+// grid after its GEMM work, so the tail runs at full HBM bandwidth.
+template <typename Tag>
+__device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epoch) {
+  const int W = p.ctx.world;
+  const int bps = blocks_per_shard(p);
+  const int parity = (epoch >> 1) & 1;
+  const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
+  const int4* scat = reinterpret_cast<const int4*>(static_cast<const char*>(p.c) + size_t(parity) * W * seg_elems * 2);
+  int4* out = static_cast<int4*>(p.out);
+  const size_t seg_vecs = seg_elems / 8;
+  for (int j = 0; j < bps; ++j) {
+    // flags layout (RS): [W src][bps], written by src when its block j of my segment is complete
+    if (threadIdx.x < W) wait_ge_sys(p.flags + threadIdx.x * bps + j, epoch);
+    __syncthreads();
+    const int rows = min(kBlockM, p.rows_per_rank - j * kBlockM);
+    const size_t blk_vecs = size_t(rows) * p.N / 8;
+    const size_t base = size_t(j) * kBlockM * p.N / 8;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < blk_vecs; i += size_t(gridDim.x) * blockDim.x) {
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+      for (int s = 0; s < W; ++s) Pack<Tag>::add(acc, ptx::ld_v4(scat + size_t(s) * seg_vecs + base + i));
+      out[base + i] = Pack<Tag>::cvt(acc);
+    }
+  }
+}
+
+// AR consumer (comm CTAs): for each tile in production order wait until every
+// rank has published it, then reduce it across ranks into `out`.
+// flags (AR): [tiles] on each rank, value = epoch when the tile is stored.
+template <typename Tag, int BLOCK_N>
+__device__ __forceinline__ void ar_consume_body(const GemmParams& p, uint32_t epoch, int comm_idx, int num_comm,
+                                                int tiles_m, int tiles_n) {
+  const int W = p.ctx.world;
+  const int tiles = tiles_m * tiles_n;
+  constexpr int vec_per_row = BLOCK_N / 8;
+  const int parity = (epoch >> 1) & 1;
+  char* sym_c = static_cast<char*>(p.c) + size_t(parity) * size_t(p.M) * p.ldc * 2;
+  char* out = static_cast<char*>(p.out);
+  for (int t = comm_idx; t < tiles; t += num_comm) {
+    if (!p.ar_one_shot && (t % W) != p.ctx.rank) continue;
+    const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+    if (threadIdx.x < W) wait_ge_sys(symm_at(p.ctx, p.flags + t, threadIdx.x), epoch);
+    __syncthreads();
+    const int rows = min(kBlockM, p.M - tc.row0);
+    const int cols_v = min(vec_per_row, (p.N - tc.n_blk * BLOCK_N) / 8);
+    for (int idx = threadIdx.x; idx < rows * vec_per_row; idx += blockDim.x) {
+      const int r = idx / vec_per_row, cv = idx % vec_per_row;
+      if (cv >= cols_v) continue;
+      const size_t off = (size_t(tc.row0 + r) * p.ldc + size_t(tc.n_blk) * BLOCK_N) * 2 + size_t(cv) * 16;
+      int4 v;
+      if (p.use_mc) {
+        v = Pack<Tag>::mc_ld_reduce(mc_ptr(p.ctx, sym_c) + off);
+      } else {
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+        for (int s = 0; s < W; ++s) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, sym_c, (p.ctx.rank + s) % W) + off));
+        v = Pack<Tag>::cvt(acc);
+      }
+      if (p.ar_one_shot) {
+        *reinterpret_cast<int4*>(out + off) = v;
+      } else if (p.use_mc) {
+        ptx::multimem_st_v4(mc_ptr(p.ctx, out) + off, v);
+      } else {
+#pragma unroll 1
+        for (int s = 0; s < W; ++s) ptx::st_v4(symm_at(p.ctx, out, (p.ctx.rank + s) % W) + off, v);
+      }
+    }
+    __syncthreads();
+    if (!p.ar_one_shot && threadIdx.x < W) {
+      ptx::fence_acq_rel_sys();
+      notify(p.ctx, p.flags2 + t, threadIdx.x, epoch);
+    }
+  }
+  if (!p.ar_one_shot) {
+    // every reduced tile must have landed in my `out` before the kernel may finish
+    for (int t = comm_idx * blockDim.x + threadIdx.x; t < tiles; t += num_comm * blockDim.x) wait_ge_sys(p.flags2 + t, epoch);
+  }
+}
+
+// ---- the kernel ---------------------------------------------------------------
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __grid_constant__ GemmParams p) {
+  using L = GemmSmem<BLOCK_N, STAGES>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int tiles_m = (p.mode == GEMM_AG || p.mode == GEMM_RS) ? blocks_per_shard(p) * p.ctx.world
+                                                               : (p.M + kBlockM - 1) / kBlockM;
+  const int tiles = tiles_m * tiles_n;
+  const int num_k = (p.K + kBlockK - 1) / kBlockK;
+  const int num_gemm = gridDim.x - p.num_comm_ctas;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+
+  uint32_t epoch = 0, phase_base = 0;
+  if (p.mode != GEMM_PLAIN) {
+    phase_base = phase_begin(p.ps);
+    epoch = phase_base + 2;  // flags of this call carry `epoch`; parity = (epoch >> 1) & 1
+  }
+  const int parity = (epoch >> 1) & 1;
+
+  if (gemm_cta < 0) {
+    // ------------------------------------------------------------ comm CTA
+    if (p.mode == GEMM_AG) {
+      ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+    } else if (p.mode == GEMM_AR) {
+      if (p.is_bf16)
+        ar_consume_body<BF16, BLOCK_N>(p, epoch, blockIdx.x, p.num_comm_ctas, tiles_m, tiles_n);
+      else
+        ar_consume_body<F16, BLOCK_N>(p, epoch, blockIdx.x, p.num_comm_ctas, tiles_m, tiles_n);
+    }
+  } else {
+    // ------------------------------------------------------------ GEMM CTA
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * L::kABytes;
+    uint8_t* smem_epi = smem + STAGES * L::kStageBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full = empty_bar + STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    constexpr int kTmemCols = tmem_cols<BLOCK_N>();
+    constexpr int kAccStride = (BLOCK_N + 31) / 32 * 32;
+
+    if (warp == 0 && lane == 0) {
+      ptx::prefetch_tensormap(&p.tma_a[0]);
+      ptx::prefetch_tensormap(&p.tma_b);
+    }
+    if (warp == 1 && lane == 0) {
+      for (int i = 0; i < STAGES; ++i) {
+        ptx::mbar_init(full_bar + i, 1);
+        ptx::mbar_init(empty_bar + i, 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        ptx::mbar_init(tmem_full + i, 1);
+        ptx::mbar_init(tmem_empty + i, 4);  // one arrival per epilogue warp
+      }
+      ptx::fence_barrier_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_ptr_smem);
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+      // ======================================================== TMA producer
+      if (lane == 0) {
+        int stage = 0;
+        uint32_t ph = 0;
+        const int bps = blocks_per_shard(p);
+        for (int t = gemm_cta; t < tiles; t += num_gemm) {
+          const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+          const CUtensorMap* ta = &p.tma_a[0];
+          int a_row = tc.row0;
+          if (p.mode == GEMM_AG) {
+            if (tc.shard == p.ctx.rank) {
+              ta = &p.tma_a_local;
+              a_row = tc.blk * kBlockM;
+            } else {
+              ta = &p.tma_a[parity];
+              // wait until block (src, blk) has landed in my workspace
+              wait_ge_sys(p.flags + tc.shard * bps + tc.blk, epoch);
+              ptx::fence_proxy_async();
+            }
+          }
+          for (int kb = 0; kb < num_k; ++kb) {
+            ptx::mbar_wait(empty_bar + stage, ph ^ 1);
+            ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);
+            ptx::tma_load_2d(smem_a + stage * L::kABytes, ta, full_bar + stage, kb * kBlockK, a_row);
+            ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK,
+                             tc.n_blk * BLOCK_N);
+            if (++stage == STAGES) {
+              stage = 0;
+              ph ^= 1;
+            }
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // ======================================================== MMA issuer
+      if (lane == 0) {
+        const uint32_t idesc = ptx::make_idesc_f16(kBlockM, BLOCK_N, p.is_bf16 != 0);
+        int stage = 0;
+        uint32_t ph = 0;
+        int acc = 0;
+        uint32_t acc_ph = 0;
+        for (int t = gemm_cta; t < tiles; t += num_gemm) {
+          ptx::mbar_wait(tmem_empty + acc, acc_ph ^ 1);
+          ptx::tcgen05_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kAccStride;
+          for (int kb = 0; kb < num_k; ++kb) {
+            ptx::mbar_wait(full_bar + stage, ph);
+            ptx::tcgen05_fence_after();
+            const uint64_t da = ptx::make_smem_desc_sw128(smem_a + stage * L::kABytes);
+            const uint64_t db = ptx::make_smem_desc_sw128(smem_b + stage * L::kBBytes);
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // +32 bytes per K step inside the 128-byte swizzle row (encoded >> 4)
+              ptx::umma_f16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            }
+            ptx::umma_commit(empty_bar + stage);  // frees the smem stage when these MMAs retire
+            if (++stage == STAGES) {
+              stage = 0;
+              ph ^= 1;
+            }
+          }
+          ptx::umma_commit(tmem_full + acc);  // accumulator complete -> epilogue
+          if (++acc == 2) {
+            acc = 0;
+            acc_ph ^= 1;
+          }
+        }
+      }
+    } else if (warp >= 4) {
+      // ======================================================== epilogue
+      const int q = warp - 4;  // TMEM lane quarter this warp may access (warp id % 4)
+      uint8_t* stg = smem_epi + q * (32 * 128);
+      int acc = 0;
+      uint32_t acc_ph = 0;
+      const int W = p.ctx.world;
+      for (int t = gemm_cta; t < tiles; t += num_gemm) {
+        const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+        ptx::mbar_wait(tmem_full + acc, acc_ph);
+        ptx::tcgen05_fence_after();
+        // destination of this tile
+        char* dst_base = static_cast<char*>(p.c);
+        long long ld = p.ldc;
+        int row0 = tc.row0 + q * 32;  // first global row handled by this warp
+        int row_limit = tc.row_end;
+        if (p.mode == GEMM_RS) {
+          const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
+          dst_base = symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) +
+                     (size_t(parity) * W + p.ctx.rank) * seg_elems * 2;
+          row0 -= tc.shard * p.rows_per_rank;
+          row_limit = p.rows_per_rank;
+          ld = p.N;
+        } else if (p.mode == GEMM_AR) {
+          dst_base += size_t(parity) * size_t(p.M) * p.ldc * 2;
+        }
+        const int col0 = tc.n_blk * BLOCK_N;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += 64) {
+          uint32_t v0[32], v1[32];
+          const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + acc * kAccStride + c;
+          ptx::tmem_ld_32x32b_x32(taddr, v0);
+          if (c + 32 < BLOCK_N) ptx::tmem_ld_32x32b_x32(taddr + 32, v1);
+          ptx::tmem_ld_wait();
+          if (c + 64 >= BLOCK_N) {
+            // last TMEM read of this tile: hand the accumulator back to the MMA warp
+            ptx::tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(tmem_empty + acc);
+          }
+          if (!p.transpose_out) {
+            // pack to 16-bit, write my row (128 B) into the staging tile with a 16-byte XOR swizzle
+            uint32_t pk[32];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float a0 = __uint_as_float(v0[2 * i]), a1 = __uint_as_float(v0[2 * i + 1]);
+              const float b0 = __uint_as_float(v1[2 * i]), b1 = __uint_as_float(v1[2 * i + 1]);
+              pk[i] = p.is_bf16 ? ptx::pack_bf16x2(a0, a1) : ptx::pack_f16x2(a0, a1);
+              pk[16 + i] = p.is_bf16 ? ptx::pack_bf16x2(b0, b1) : ptx::pack_f16x2(b0, b1);
+            }
+            __syncwarp();  // previous chunk's readers are done with the staging tile
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              int4 w = make_int4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+              *reinterpret_cast<int4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = w;
+            }
+            __syncwarp();
+            // coalesced stores: 8 lanes cover one 128-byte row, 4 rows per instruction
+            const int cj = lane & 7;
+            const int gcol = col0 + c + cj * 8;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int r = it * 4 + (lane >> 3);
+              const int4 w = *reinterpret_cast<const int4*>(stg + r * 128 + ((cj ^ (r & 7)) << 4));
+              const int grow = row0 + r;
+              if (grow < row_limit && gcol < p.N && c + cj * 8 < BLOCK_N)
+                ptx::st_v4(dst_base + (size_t(grow) * ld + gcol) * 2, w);
+            }
+          } else {
+            // swap-AB skinny GEMM: accumulator row = output column. C[col][row] scalar stores,
+            // a warp writes 32 consecutive output columns of one output row per instruction.
+            const int grow = row0 + lane;
+#pragma unroll
+            for (int i = 0; i < 64; ++i) {
+              const int gc = col0 + c + i;
+              if (c + i < BLOCK_N && gc < p.N && grow < row_limit) {
+                const float f = __uint_as_float(i < 32 ? v0[i & 31] : v1[i & 31]);
+                if (p.is_bf16)
+                  reinterpret_cast<__nv_bfloat16*>(dst_base)[size_t(gc) * ld + grow] = __float2bfloat16(f);
+                else
+                  reinterpret_cast<__half*>(dst_base)[size_t(gc) * ld + grow] = __float2half(f);
+              }
+            }
+          }
+        }
+        if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
+          // publish the tile: all 4 epilogue warps have stored -> one thread signals
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (warp == 4 && lane == 0) {
+            ptx::fence_acq_rel_sys();
+            if (p.mode == GEMM_RS) {
+              const int bps = blocks_per_shard(p);
+              const int cidx = tc.shard * bps + tc.blk;
+              const uint32_t done = ptx::atom_add_acq_rel_gpu(p.counters + cidx, 1) + 1;
+              if (done == static_cast<uint32_t>(tiles_n)) {
+                p.counters[cidx] = 0;
+                ptx::fence_acq_rel_sys();
+                notify(p.ctx, p.flags + p.ctx.rank * bps + tc.blk, tc.shard, epoch);
+              }
+            } else {
+              ptx::st_release_sys(p.flags + t, epoch);
+            }
+          }
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_ph ^= 1;
+        }
+      }
+    }
+    // teardown of the GEMM roles
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+  }
+
+  // ------------------------------------------------------------ fused tails (all CTAs)
+  if (p.mode == GEMM_RS) {
+    __syncthreads();
+    if (p.is_bf16)
+      rs_reduce_body<BF16>(p, epoch);
+    else
+      rs_reduce_body<F16>(p, epoch);
+  }
+  if (p.mode != GEMM_PLAIN) phase_end(p.ps, phase_base, 2);
+}
+
+}  // namespace tdist

@@ -1,0 +1,133 @@
+/* tdist.h — C ABI of libtdist (B200 / sm_100a).
+ *
+ * Every entry point returns 0 on success and -1 on failure; tdist_last_error()
+ * then returns a message for the calling thread. Pointers are raw device
+ * pointers, `stream` is a cudaStream_t. Nothing here synchronises the device
+ * unless stated. Citations name the reference component an entry point stands
+ * in for (paths relative to the reference checkout).
+ */
+#ifndef TDIST_H_
+#define TDIST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TDIST_MAX_RANKS 16
+#define TDIST_MAX_CTAS 160 /* flag rows reserved per collective context */
+
+enum { TDIST_BF16 = 0, TDIST_F16 = 1, TDIST_F32 = 2, TDIST_FP8_E4M3 = 3 };
+
+/* Symmetric-heap view handed BY VALUE to kernels (mirrors tdist::SymmCtx). */
+typedef struct tdist_symm_ctx {
+  char* base[TDIST_MAX_RANKS]; /* base[r]: where rank r's heap is mapped in this process */
+  char* mc_base;               /* NVLS multicast alias of the heap, NULL if unavailable */
+  unsigned long long bytes;    /* bytes per rank */
+  int rank;
+  int world;
+} tdist_symm_ctx;
+
+typedef struct tdist_heap tdist_heap;
+
+const char* tdist_last_error(void);
+
+/* ---- symmetric heap (replaces nvshmem.core.tensor / get_peer_tensor,
+ *      python/triton_dist/utils.py:99-142) ------------------ */
+/* Collective over the ranks of one node. VMM allocation, fd exchange over
+ * abstract UNIX sockets named after job_id, peers mapped at base + p*bytes. */
+int tdist_heap_create(int rank, int world, int device, size_t bytes, const char* job_id, tdist_heap** out);
+/* cudaMalloc + cudaIpc fallback: step 1 returns this rank's 64-byte handle ... */
+int tdist_heap_create_ipc(int rank, int world, int device, size_t bytes, tdist_heap** out, void* handle64);
+/* ... step 2 opens all peers (world*64 bytes, rank order). */
+int tdist_heap_open_ipc(tdist_heap* h, const void* all_handles);
+/* NVLS multicast binding in two collective phases; barrier between them. */
+int tdist_heap_mc_phase_a(tdist_heap* h);
+int tdist_heap_mc_phase_b(tdist_heap* h);
+void* tdist_heap_base(tdist_heap* h, int peer);
+void* tdist_heap_mc_base(tdist_heap* h);
+size_t tdist_heap_bytes(tdist_heap* h);
+int tdist_heap_mode(tdist_heap* h); /* 0 local, 1 VMM, 2 cudaIpc */
+int tdist_heap_fill_ctx(tdist_heap* h, tdist_symm_ctx* out);
+int tdist_heap_destroy(tdist_heap* h);
+
+/* ---- stream memory ops (kernels/nvidia/common_ops.py:347-389) ------------- */
+int tdist_stream_write_value32(void* stream, void* addr, unsigned int value);
+int tdist_stream_wait_value32(void* stream, void* addr, unsigned int value, int cmp_geq);
+int tdist_stream_write_value64(void* stream, void* addr, unsigned long long value);
+int tdist_stream_wait_value64(void* stream, void* addr, unsigned long long value, int cmp_geq);
+
+/* ---- collectives. flags: symmetric uint32[TDIST_MAX_CTAS*TDIST_MAX_RANKS];
+ *      phase/done: device uint32 counters (zero initialised) ---------------- */
+/* stream-ordered barrier across ranks (utils.py:162-164, common_ops.py:141-209) */
+int tdist_barrier_all(const tdist_symm_ctx* ctx, uint32_t* flags, uint32_t* phase, uint32_t* done, void* stream);
+
+enum { TDIST_AR_ONE_SHOT = 1, TDIST_AR_TWO_SHOT = 2, TDIST_AR_ONE_SHOT_MC = 5, TDIST_AR_TWO_SHOT_MC = 6 };
+/* kernels/nvidia/allreduce.py:332-682. ws is symmetric; in_place means `in`
+ * already lives in ws (multimem methods only). nbytes % 16 == 0. */
+int tdist_allreduce(const tdist_symm_ctx* ctx, int method, int dtype, const void* in, void* out, size_t nbytes,
+                    void* ws, size_t ws_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas,
+                    int in_place, void* stream);
+
+enum { TDIST_AG_PULL = 0, TDIST_AG_PUSH = 1, TDIST_AG_PUSH_MC = 2, TDIST_AG_LL = 3, TDIST_AG_LL_MC = 4 };
+/* kernels/nvidia/low_latency_allgather.py:47-777. symm: [W][shard] (LL modes:
+ * [2][W][shard/8] 16-byte packets). out may be NULL (result stays in symm). */
+int tdist_allgather(const tdist_symm_ctx* ctx, int mode, const void* in, void* symm, void* out, size_t shard_bytes,
+                    uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas, void* stream);
+
+/* kernels/nvidia/reduce_scatter.py:285-866. in: [W][seg]; scatter_ws (symm): [2][W][seg]; out: [seg] */
+int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, void* scatter_ws, void* out,
+                         size_t seg_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas,
+                         void* stream);
+/* out = sum of `slots` segments (ring_reduce, reduce_scatter.py:673-810) */
+int tdist_slot_reduce(int dtype, const void* in, void* out, size_t seg_bytes, int slots, int begin, int max_ctas,
+                      void* stream);
+/* kernels/nvidia/p2p.py:30-85 */
+int tdist_p2p_copy(void* dst, const void* src, size_t nbytes, int num_ctas, void* stream);
+/* one-thread signal kernels (graph-capturable twin of the stream mem-ops) */
+int tdist_signal_set(uint32_t* flag, uint32_t value, int add, void* stream);
+int tdist_signal_wait(const uint32_t* flag, uint32_t value, int cmp, void* stream);
+
+/* ---- tcgen05 GEMM engine ------------------------------------ */
+typedef struct tdist_gemm_args {
+  const void* a; /* [M, K] row-major (AG: this rank's shard [M/W, K]) */
+  const void* b; /* [N, K] row-major (nn.Linear weight layout) */
+  void* c;       /* [M, N] row-major, or [N, M] when transpose_out */
+  int M, N, K;
+  long long lda, ldb, ldc; /* in elements */
+  int dtype;               /* TDIST_BF16 / TDIST_F16 */
+  int block_n;             /* 0 = heuristic */
+  int group_m;             /* 0 = default */
+  int num_sms;             /* 0 = all */
+  int transpose_out;       /* store C^T (swap-AB skinny GEMM) */
+} tdist_gemm_args;
+
+/* C = A * B^T (kernels/nvidia/allgather_gemm.py:656-720 gemm_persistent) */
+int tdist_gemm(const tdist_gemm_args* a, void* stream);
+
+enum { TDIST_GEMM_AG = 1, TDIST_GEMM_RS = 2, TDIST_GEMM_AR = 3 };
+typedef struct tdist_fused_args {
+  tdist_symm_ctx ctx;
+  int mode;
+  void* ws;           /* AG: symm gather workspace [2][M][K]; RS: symm scatter [2][W][M/W][N]; AR: symm tiles [2][M][ldc] */
+  void* out;          /* RS: [M/W, N]; AR: [M, ldc] (symmetric when !ar_one_shot) */
+  uint32_t* flags;    /* symmetric, zero initialised, >= W*ceil(M/W/128) (AG/RS) or #tiles (AR) entries */
+  uint32_t* flags2;   /* AR two-shot only: symmetric, #tiles entries */
+  uint32_t* counters; /* RS: local, zero initialised, W*ceil(M/W/128) entries */
+  uint32_t* phase;    /* device counter pair, zero initialised */
+  uint32_t* done;
+  int num_comm_ctas;  /* <0 = default */
+  int ar_one_shot;
+  int use_mc;
+} tdist_fused_args;
+
+/* AG+GEMM (allgather_gemm.py:534-653), GEMM+RS (gemm_reduce_scatter.py:508-583),
+ * GEMM+AR (gemm_allreduce.py:509-575): one launch each. */
+int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDIST_H_ */

@@ -1,0 +1,1 @@
+from .symm import SymmetricHeap, HostHeap, get_heap, init_heap, finalize_heap, heap_initialized, tensor_from_ptr  # noqa: F401

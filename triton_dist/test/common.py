@@ -1,0 +1,65 @@
+"""Shared harness for the script-style tests (run under torchrun, like the
+reference's ``python/triton_dist/test/nvidia/*.py`` under ``scripts/launch.sh``)."""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+from triton_dist.utils import (dist_print, finalize_distributed, initialize_distributed, perf_func_max_over_ranks)
+
+DTYPES = {"bfloat16": torch.bfloat16, "float16": torch.float16, "float32": torch.float32, "bf16": torch.bfloat16,
+          "fp16": torch.float16, "fp32": torch.float32}
+
+# tolerances of the reference's tests (test_gemm_rs.py:108-113, test_allreduce.py:99-103)
+TOL = {torch.bfloat16: dict(atol=6e-2, rtol=6e-2), torch.float16: dict(atol=1e-2, rtol=1e-2),
+       torch.float32: dict(atol=1e-3, rtol=1e-3)}
+
+
+def base_parser(desc: str) -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(description=desc)
+    p.add_argument("--dtype", default="bfloat16", choices=list(DTYPES))
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--iters", type=int, default=20)
+    p.add_argument("--check", action="store_true", help="correctness only")
+    p.add_argument("--verify-iters", type=int, default=4)
+    p.add_argument("--stress", action="store_true", help="random skew between ranks every iteration")
+    p.add_argument("--profile", action="store_true")
+    return p
+
+
+def setup(seed: int = 3407):
+    group = initialize_distributed(seed=None)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(seed + rank)
+    return group, rank, world
+
+
+def device() -> str:
+    return "cuda" if torch.cuda.is_available() else "cpu"
+
+
+def rand(shape, dtype, scale=1.0):
+    return ((torch.rand(shape, dtype=torch.float32, device=device()) * 2 - 1) * scale).to(dtype)
+
+
+def skew(enabled: bool) -> None:
+    """Race/hang provocation: delay this rank by a random amount (reference allgather.py:74-78)."""
+    if enabled and torch.cuda.is_available():
+        torch.cuda._sleep(int(torch.randint(0, 3_000_000, (1,)).item()))
+
+
+def finish(ok: bool = True):
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+    dist.barrier()
+    dist_print("PASS" if ok else "FAIL")
+    finalize_distributed()
+    sys.exit(0 if ok else 1)
+
+
+def bench(fn, args, group=None, flush_l2=True):
+    return perf_func_max_over_ranks(fn, args.iters, args.warmup, group=group, flush_l2=flush_l2)[1]

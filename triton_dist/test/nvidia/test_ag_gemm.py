@@ -1,0 +1,51 @@
+"""AG+GEMM correctness / perf (mirrors reference test/nvidia/test_ag_gemm.py).
+    torchrun --nproc-per-node 8 -m triton_dist.test.nvidia.test_ag_gemm 8192 14336 4096 [--check]
+M is the GLOBAL row count, N the GLOBAL column count (sharded over ranks), K the reduction dim."""
+import torch
+import torch.distributed as dist
+
+from triton_dist.kernels.nvidia.allgather_gemm import ag_gemm, create_ag_gemm_context, torch_ag_gemm
+from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
+from triton_dist.utils import assert_allclose, dist_print, measured_peaks, NVLINK_GBS_MEASURED
+
+if __name__ == "__main__":
+    p = base_parser(__doc__)
+    p.add_argument("M", type=int)
+    p.add_argument("N", type=int)
+    p.add_argument("K", type=int)
+    p.add_argument("--block-n", type=int, default=0)
+    p.add_argument("--comm-sms", type=int, default=-1)
+    args = p.parse_args()
+    group, rank, world = setup()
+    dtype = DTYPES[args.dtype]
+    assert args.M % world == 0 and args.N % world == 0
+    m_loc, n_loc = args.M // world, args.N // world
+    B = rand((n_loc, args.K), dtype, 0.1)
+    A0 = rand((m_loc, args.K), dtype)
+    ctx = create_ag_gemm_context(A0, B, rank, world, max_M=args.M, num_local_ranks=world, BLOCK_N=args.block_n,
+                                 num_comm_sms=args.comm_sms)
+    ok = True
+    for it in range(args.verify_iters):
+        A = rand((m_loc, args.K), dtype)  # fresh inputs every iteration (stale-workspace detection)
+        skew(args.stress)
+        C = ag_gemm(A, B, ctx)
+        ref = torch_ag_gemm(A, B)
+        try:
+            assert_allclose(C.float(), ref.float(), verbose=False, **TOL[dtype])
+        except RuntimeError as e:
+            ok = False
+            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+            break
+    if ok and not args.check:
+        A = rand((m_loc, args.K), dtype)
+        t_fused = bench(lambda: ag_gemm(A, B, ctx), args)
+        t_ref = bench(lambda: torch_ag_gemm(A, B), args)
+        flops = 2.0 * args.M * n_loc * args.K
+        link_bytes = (world - 1) * m_loc * args.K * A.element_size()
+        pk = measured_peaks()
+        roof_ms = max(flops / (pk["bf16_tflops"] * 1e9), link_bytes / (NVLINK_GBS_MEASURED * 1e6))
+        dist_print(f"ag_gemm M={args.M} N={args.N} K={args.K} W={world}: fused {t_fused:.4f} ms "
+                   f"({flops / t_fused / 1e9:.1f} TFLOP/s per GPU), torch(NCCL+cuBLAS) {t_ref:.4f} ms, "
+                   f"speedup {t_ref / t_fused:.2f}x, roofline {roof_ms:.4f} ms -> {roof_ms / t_fused:.2f} of measured")
+    ctx.finalize()
+    finish(ok)

@@ -1,0 +1,48 @@
+"""GEMM+RS correctness / perf (mirrors reference test/nvidia/test_gemm_rs.py).
+    torchrun --nproc-per-node 8 -m triton_dist.test.nvidia.test_gemm_rs 8192 4096 14336 [--check]
+M global rows, N output columns, K GLOBAL reduction dim (sharded over ranks)."""
+import torch
+import torch.distributed as dist
+
+from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs, torch_gemm_rs
+from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
+from triton_dist.utils import assert_allclose, dist_print, measured_peaks, NVLINK_GBS_MEASURED
+
+if __name__ == "__main__":
+    p = base_parser(__doc__)
+    p.add_argument("M", type=int)
+    p.add_argument("N", type=int)
+    p.add_argument("K", type=int)
+    p.add_argument("--block-n", type=int, default=0)
+    args = p.parse_args()
+    group, rank, world = setup()
+    dtype = DTYPES[args.dtype]
+    assert args.M % world == 0 and args.K % world == 0
+    k_loc = args.K // world
+    B = rand((args.N, k_loc), dtype, 0.1)
+    ctx = create_gemm_rs_context(args.M, args.N, rank, world, world, dtype, BLOCK_N=args.block_n)
+    ok = True
+    for it in range(args.verify_iters):
+        A = rand((args.M, k_loc), dtype)
+        skew(args.stress)
+        C = gemm_rs(A, B, ctx)
+        ref = torch_gemm_rs(A, B)
+        try:
+            assert_allclose(C.float(), ref.float(), verbose=False, **TOL[dtype])
+        except RuntimeError as e:
+            ok = False
+            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+            break
+    if ok and not args.check:
+        A = rand((args.M, k_loc), dtype)
+        t_fused = bench(lambda: gemm_rs(A, B, ctx), args)
+        t_ref = bench(lambda: torch_gemm_rs(A, B), args)
+        flops = 2.0 * args.M * args.N * k_loc
+        link_bytes = (world - 1) * (args.M // world) * args.N * A.element_size()
+        pk = measured_peaks()
+        roof_ms = max(flops / (pk["bf16_tflops"] * 1e9), link_bytes / (NVLINK_GBS_MEASURED * 1e6))
+        dist_print(f"gemm_rs M={args.M} N={args.N} K={args.K} W={world}: fused {t_fused:.4f} ms "
+                   f"({flops / t_fused / 1e9:.1f} TFLOP/s per GPU), torch(cuBLAS+NCCL) {t_ref:.4f} ms, "
+                   f"speedup {t_ref / t_fused:.2f}x, roofline {roof_ms:.4f} ms -> {roof_ms / t_fused:.2f} of measured")
+    ctx.finalize()
+    finish(ok)

@@ -1,0 +1,37 @@
+"""Reduce-scatter correctness / perf (mirrors reference test/nvidia/test_reduce_scatter.py)."""
+import torch
+import torch.distributed as dist
+
+from triton_dist.kernels.nvidia.reduce_scatter import create_reduce_scater_2d_ctx, reduce_scatter_2d_op, torch_reduce_scatter
+from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
+from triton_dist.utils import assert_allclose, dist_print
+
+if __name__ == "__main__":
+    p = base_parser(__doc__)
+    p.add_argument("M", type=int)
+    p.add_argument("N", type=int)
+    args = p.parse_args()
+    group, rank, world = setup()
+    dtype = DTYPES[args.dtype]
+    ctx = create_reduce_scater_2d_ctx(args.M, args.N, rank, world, world, dtype)
+    ok = True
+    for it in range(args.verify_iters):
+        x = rand((args.M, args.N), dtype)
+        skew(args.stress)
+        y = reduce_scatter_2d_op(x, ctx)
+        ref = torch_reduce_scatter(x)
+        try:
+            assert_allclose(y.float(), ref.float(), verbose=False, **TOL[dtype])
+        except RuntimeError as e:
+            ok = False
+            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+            break
+    if ok and not args.check:
+        x = rand((args.M, args.N), dtype)
+        t = bench(lambda: reduce_scatter_2d_op(x, ctx), args, flush_l2=False)
+        t_ref = bench(lambda: torch_reduce_scatter(x), args, flush_l2=False)
+        nbytes = x.numel() * x.element_size()
+        dist_print(f"reduce_scatter [{args.M},{args.N}] W={world}: {t * 1e3:.1f} us busbw "
+                   f"{nbytes * (world - 1) / world / t / 1e6:.1f} GB/s, NCCL {t_ref * 1e3:.1f} us")
+    ctx.finalize()
+    finish(ok)

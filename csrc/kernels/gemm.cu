@@ -103,12 +103,16 @@ static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
     for (int c : cands)
       if (c == forced) return c;
   }
-  long best_cost = -1;
+  // relative mainloop efficiency of each tile width, measured on B200 (profiles/gemm_tile_sweep.md): narrow
+  // tiles re-read the 128-row A operand from shared memory more often per FLOP and become smem-bound.
+  static const double eff[] = {1.0, 0.943, 0.826, 0.70, 0.585, 0.52, 0.45, 0.32, 0.17};
+  double best_cost = -1;
   int best = 128;
-  for (int bn : cands) {
+  for (size_t i = 0; i < sizeof(cands) / sizeof(cands[0]); ++i) {
+    const int bn = cands[i];
     const long tiles = long(M_tiles) * ((N + bn - 1) / bn);
     const long waves = (tiles + ctas - 1) / ctas;
-    const long cost = waves * (bn + 24);  // +24: fixed per-tile cost (epilogue hand-off, pipeline refill)
+    const double cost = double(waves) * (bn / eff[i] + 6.0);  // +6: per-tile hand-off
     if (best_cost < 0 || cost < best_cost) {
       best_cost = cost;
       best = bn;

@@ -127,6 +127,38 @@ typedef struct tdist_fused_args {
  * GEMM+AR (gemm_allreduce.py:509-575): one launch each. */
 int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream);
 
+/* ---- decode-path kernels (csrc/kernels/decode.cu) -------------------------
+ * Reference: kernels/nvidia/flash_decode.py:129-532 and the mega_triton_kernel task kernels;
+ * norm / rope / sampling are flashinfer calls in the reference's layers. */
+/* y[M,N] = x[M,K] w[N,K]^T (+bias), 1 <= M <= 16: weight-streaming GEMV */
+int tdist_gemv(int dtype, const void* x, const void* w, const void* bias, void* y, int M, int N, int K, long long ldx,
+               long long ldw, long long ldy, void* stream);
+/* y = rmsnorm(x + residual) * weight; residual (optional, contiguous [rows, hidden]) is updated to x + residual */
+int tdist_rmsnorm(int dtype, const void* x, void* residual, const void* weight, void* y, int rows, int hidden, float eps,
+                  long long ldx, long long ldy, void* stream);
+/* out[t, :] = silu(gate_up[t, :I]) * gate_up[t, I:] */
+int tdist_silu_mul(int dtype, const void* gate_up, void* out, long long tokens, int inter, void* stream);
+int tdist_add(int dtype, const void* a, const void* b, void* out, long long numel, void* stream);
+/* per-head q/k RMSNorm (weights optional) + NeoX RoPE + KV-cache append; qkv [T, (Hq+2Hkv)*128];
+ * cos_sin fp32 [max_pos, 128] (cos | sin); cache dense (block_table NULL: strides batch/seq/head) or paged
+ * (kv_batch_stride = page stride). */
+int tdist_qk_norm_rope_kv(int dtype, const void* qkv, const void* q_norm_w, const void* k_norm_w, const float* cos_sin,
+                          const int* positions, const int* batch_idx, void* q_out, void* k_cache, void* v_cache,
+                          int tokens, int Hq, int Hkv, int head_dim, float eps, long long kv_batch_stride,
+                          long long kv_seq_stride, long long kv_head_stride, const int* block_table, int page_size,
+                          int max_pages, void* stream);
+/* GQA split-KV flash decode: partial [B,Hq,splits,129] fp32 (out|lse), then (if out16 or out_lse given) the
+ * intra-rank combine into out16 [B,Hq,128] and/or out_lse [B,Hq,129]. */
+int tdist_flash_decode(int dtype, const void* q, const void* k_cache, const void* v_cache, const int* kv_lens,
+                       float* partial, void* out16, float* out_lse, int B, int Hq, int Hkv, int head_dim, int splits,
+                       float sm_scale, long long kv_batch_stride, long long kv_seq_stride, long long kv_head_stride,
+                       const int* block_table, int page_size, int max_pages, void* stream);
+/* log-sum-exp merge of `splits` partials with arbitrary strides (floats): inter-rank combine of distributed decode */
+int tdist_flash_decode_combine(int dtype, const float* partial, void* out16, float* out_lse, int B, int H, int splits,
+                               long long stride_b, long long stride_h, long long stride_s, void* stream);
+int tdist_embedding(int dtype, const long long* ids, const void* table, void* out, int tokens, int hidden, void* stream);
+int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vocab, long long ld, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,59 @@
+"""CPU checks of the op layer's torch paths (the oracles used by the GPU tests) and of pure-host logic."""
+import math
+
+import torch
+
+
+def test_rmsnorm_cpu_matches_formula():
+    from triton_dist.kernels.nvidia.elementwise import rmsnorm
+
+    x = torch.randn(4, 64)
+    w = torch.rand(64) + 0.5
+    y = rmsnorm(x, w, 1e-6)
+    ref = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-6) * w
+    torch.testing.assert_close(y, ref)
+
+
+def test_rope_cache_roundtrip_cpu():
+    from triton_dist.kernels.nvidia.elementwise import make_cos_sin_cache, qk_norm_rope_update_kvcache
+
+    T, Hq, Hkv, D = 3, 4, 2, 128
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D)
+    cs = make_cos_sin_cache(D, 16, device="cpu")
+    kc, vc = torch.zeros(1, 16, Hkv, D), torch.zeros(1, 16, Hkv, D)
+    pos = torch.tensor([0, 1, 2], dtype=torch.int32)
+    q = qk_norm_rope_update_kvcache(qkv, None, None, cs, pos, kc, vc, Hq, Hkv, D)
+    # position 0 is the identity rotation
+    torch.testing.assert_close(q[0], qkv[0].view(Hq + 2 * Hkv, D)[:Hq])
+    torch.testing.assert_close(vc[0, 2], qkv[2].view(Hq + 2 * Hkv, D)[Hq + Hkv:])
+    # rotation preserves the norm
+    torch.testing.assert_close(q[2].norm(dim=-1), qkv[2].view(Hq + 2 * Hkv, D)[:Hq].norm(dim=-1))
+
+
+def test_paged_decode_oracle_matches_sdpa():
+    from triton_dist.kernels.nvidia.flash_decode import inter_rank_combine, torch_paged_decode
+
+    B, Hq, Hkv, D, page, n = 2, 4, 2, 128, 4, 10
+    q = torch.randn(B, Hq, D)
+    kc, vc = torch.randn(8, page, Hkv, D), torch.randn(8, page, Hkv, D)
+    bt = torch.tensor([[0, 1, 2, 3], [4, 5, 6, 7]], dtype=torch.int32)
+    lens = torch.tensor([n, n], dtype=torch.int32)
+    out, lse = torch_paged_decode(q, kc, vc, lens, bt, 1 / math.sqrt(D))
+    k = kc.view(2, 16, Hkv, D)[:, :n].repeat_interleave(2, dim=2).transpose(1, 2)
+    v = vc.view(2, 16, Hkv, D)[:, :n].repeat_interleave(2, dim=2).transpose(1, 2)
+    ref = torch.nn.functional.scaled_dot_product_attention(q[:, :, None], k, v)[:, :, 0]
+    torch.testing.assert_close(out, ref, atol=1e-5, rtol=1e-5)
+    # splitting the KV in two and merging by lse is exact
+    o0, l0 = torch_paged_decode(q, kc, vc, torch.tensor([4, 4], dtype=torch.int32), bt, 1 / math.sqrt(D))
+    kc2, vc2 = kc.view(2, 16, Hkv, D)[:, 4:].reshape(-1, page, Hkv, D), vc.view(2, 16, Hkv, D)[:, 4:].reshape(-1, page, Hkv, D)
+    bt2 = torch.tensor([[0, 1, 2], [3, 4, 5]], dtype=torch.int32)
+    o1, l1 = torch_paged_decode(q, kc2, vc2, torch.tensor([6, 6], dtype=torch.int32), bt2, 1 / math.sqrt(D))
+    parts = torch.stack([torch.cat([o0, l0[..., None]], -1), torch.cat([o1, l1[..., None]], -1)])
+    torch.testing.assert_close(inter_rank_combine(parts, dtype=torch.float32), ref, atol=1e-5, rtol=1e-5)
+
+
+def test_allreduce_method_names():
+    from triton_dist.kernels.allreduce import AllReduceMethod, get_allreduce_methods, to_allreduce_method
+
+    assert to_allreduce_method("two_shot_multimem") == AllReduceMethod.TwoShot_Multimem
+    assert "one_shot" in get_allreduce_methods()

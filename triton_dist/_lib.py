@@ -122,6 +122,16 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_p2p_copy", [vp, vp, sz, i32, vp])
     sig("tdist_signal_set", [vp, u32, i32, vp])
     sig("tdist_signal_wait", [vp, u32, i32, vp])
+    f32, ll = ctypes.c_float, ctypes.c_longlong
+    sig("tdist_gemv", [i32, vp, vp, vp, vp, i32, i32, i32, ll, ll, ll, vp])
+    sig("tdist_rmsnorm", [i32, vp, vp, vp, vp, i32, i32, f32, ll, ll, vp])
+    sig("tdist_silu_mul", [i32, vp, vp, ll, i32, vp])
+    sig("tdist_add", [i32, vp, vp, vp, ll, vp])
+    sig("tdist_qk_norm_rope_kv", [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, ll, ll, ll, vp, i32, i32, vp])
+    sig("tdist_flash_decode", [i32, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, ll, ll, ll, vp, i32, i32, vp])
+    sig("tdist_flash_decode_combine", [i32, vp, vp, vp, i32, i32, i32, ll, ll, ll, vp])
+    sig("tdist_embedding", [i32, vp, vp, vp, i32, i32, vp])
+    sig("tdist_argmax", [i32, vp, vp, i32, i32, ll, vp])
     sig("tdist_gemm", [P(GemmArgs), vp])
     sig("tdist_gemm_fused", [P(GemmArgs), P(FusedArgs), vp])
 

@@ -28,6 +28,7 @@ def base_parser(desc: str) -> argparse.ArgumentParser:
     p.add_argument("--verify-iters", type=int, default=4)
     p.add_argument("--stress", action="store_true", help="random skew between ranks every iteration")
     p.add_argument("--profile", action="store_true")
+    p.add_argument("--graph", action="store_true", help="time inside a CUDA graph (no host launch overhead)")
     return p
 
 
@@ -35,6 +36,9 @@ def setup(seed: int = 3407):
     group = initialize_distributed(seed=None)
     rank, world = dist.get_rank(), dist.get_world_size()
     torch.manual_seed(seed + rank)
+    from triton_dist.runtime import get_heap
+    h = get_heap()
+    dist_print(f"[setup] world={world} heap_mode={h.mode} (1=VMM 2=cudaIpc -1=host) multicast={h.multicast}")
     return group, rank, world
 
 
@@ -62,4 +66,6 @@ def finish(ok: bool = True):
 
 
 def bench(fn, args, group=None, flush_l2=True):
-    return perf_func_max_over_ranks(fn, args.iters, args.warmup, group=group, flush_l2=flush_l2)[1]
+    graph = getattr(args, "graph", False)
+    return perf_func_max_over_ranks(fn, args.iters, args.warmup, group=group, flush_l2=flush_l2 and not graph,
+                                    use_graph=graph)[1]

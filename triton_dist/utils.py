@@ -298,21 +298,60 @@ def perf_func(func: Callable, iters: int, warmup_iters: int):
     return out, start.elapsed_time(stop) / max(iters, 1)
 
 
-def perf_func_max_over_ranks(func: Callable, iters: int, warmup_iters: int, group=None, flush_l2: bool = False):
-    """Device-timed ms per call, MAX over ranks (what every multi-GPU number in this repo reports)."""
-    if flush_l2 and torch.cuda.is_available():
-        flush = torch.empty(256 * 2**20, dtype=torch.uint8, device="cuda")
-        inner = func
+def perf_func_max_over_ranks(func: Callable, iters: int, warmup_iters: int, group=None, flush_l2: bool = False,
+                             use_graph: bool = False):
+    """Device-timed ms per call, MAX over ranks (what every multi-GPU number in this repo reports).
 
-        def func():  # noqa: F811
-            flush.zero_()
-            return inner()
-
+    ``flush_l2``: a 256 MiB write evicts L2 before every call; each call is then timed by its own event
+    pair so that the flush is outside the measured span. ``use_graph``: capture ``iters`` calls in one CUDA
+    graph (removes host launch overhead; for latency-bound ops)."""
     if dist.is_initialized():
         dist.barrier(group=group)
-    if torch.cuda.is_available():
+    out = None
+    if not torch.cuda.is_available():
+        out, ms = perf_func(func, iters, warmup_iters)
+    elif use_graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup_iters, 3)):
+                out = func()
+        torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
-    out, ms = perf_func(func, iters, warmup_iters)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(iters):
+                out = func()
+        g.replay()
+        torch.cuda.synchronize()
+        if dist.is_initialized():
+            dist.barrier(group=group)
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record()
+        g.replay()
+        stop.record()
+        torch.cuda.synchronize()
+        ms = start.elapsed_time(stop) / iters
+    elif flush_l2:
+        flush = torch.empty(256 * 2**20, dtype=torch.uint8, device="cuda")
+        for _ in range(warmup_iters):
+            out = func()
+        torch.cuda.synchronize()
+        if dist.is_initialized():
+            dist.barrier(group=group)
+        evs = []
+        for _ in range(iters):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            out = func()
+            e.record()
+            evs.append((s, e))
+        torch.cuda.synchronize()
+        ms = sum(s.elapsed_time(e) for s, e in evs) / max(iters, 1)
+    else:
+        torch.cuda.synchronize()
+        out, ms = perf_func(func, iters, warmup_iters)
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=default_device())
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)

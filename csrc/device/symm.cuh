@@ -39,7 +39,8 @@ __device__ __forceinline__ int num_ranks(const SymmCtx& c) { return c.world; }
 // Translate a pointer into my heap to the same object on `peer`.
 template <typename T>
 __device__ __forceinline__ T* symm_at(const SymmCtx& c, T* local, int peer) {
-  return reinterpret_cast<T*>(c.base[peer] + (reinterpret_cast<char*>(local) - c.base[c.rank]));
+  return reinterpret_cast<T*>(reinterpret_cast<uintptr_t>(c.base[peer]) +
+                              (reinterpret_cast<uintptr_t>(local) - reinterpret_cast<uintptr_t>(c.base[c.rank])));
 }
 template <typename T>
 __device__ __forceinline__ T* remote_ptr(const SymmCtx& c, T* local, int peer) {
@@ -48,7 +49,8 @@ __device__ __forceinline__ T* remote_ptr(const SymmCtx& c, T* local, int peer) {
 // Multicast alias of a heap pointer (stores reach every rank, ld_reduce sums over ranks).
 template <typename T>
 __device__ __forceinline__ T* mc_ptr(const SymmCtx& c, T* local) {
-  return reinterpret_cast<T*>(c.mc_base + (reinterpret_cast<char*>(local) - c.base[c.rank]));
+  return reinterpret_cast<T*>(reinterpret_cast<uintptr_t>(c.mc_base) +
+                              (reinterpret_cast<uintptr_t>(local) - reinterpret_cast<uintptr_t>(c.base[c.rank])));
 }
 
 // ---------------------------------------------------------------- notify / wait (32-bit flags)

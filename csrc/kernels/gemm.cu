@@ -97,6 +97,7 @@ static int launch_inst(const GemmParams& p, int grid, cudaStream_t s, bool coope
   return 0;
 }
 
+static double g_last_cost = 0;
 static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
   static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64, 32};
   if (forced > 0) {
@@ -118,6 +119,7 @@ static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
       best = bn;
     }
   }
+  g_last_cost = best_cost;
   return best;
 }
 
@@ -172,6 +174,7 @@ int tdist_gemm(const tdist_gemm_args* a, void* stream) {
   p.is_bf16 = a->dtype == TDIST_BF16;
   p.rows_per_rank = a->M;
   p.transpose_out = a->transpose_out;
+  p.block_expert = a->block_expert;
   p.ctx.world = 1;
   const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
   const int tiles_m = (a->M + kBlockM - 1) / kBlockM;
@@ -180,7 +183,8 @@ int tdist_gemm(const tdist_gemm_args* a, void* stream) {
   p.group_m = a->group_m > 0 ? a->group_m : 8;
   p.num_comm_ctas = 0;
   if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
-  if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn) != 0) return -1;
+  const int b_rows = a->block_expert != nullptr ? a->N * (a->num_experts > 0 ? a->num_experts : 1) : a->N;
+  if (make_tmap(&p.tma_b, a->b, b_rows, a->K, a->ldb, bn) != 0) return -1;
   const int grid = tiles < sms ? tiles : sms;
   return dispatch(p, bn, grid, static_cast<cudaStream_t>(stream), false);
 }
@@ -217,7 +221,19 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.c = a->c;
     p.ldc = a->ldc;
     if (W == 1) comm = 0;
-    if (comm < 0) comm = W > 1 ? 16 : 0;
+    if (comm < 0) {
+      // as many push CTAs as the wave count of the GEMM part tolerates (they are free until they add a wave)
+      const int tm = ((a->M / W + kBlockM - 1) / kBlockM) * W;
+      double best = -1;
+      comm = 12;
+      for (int c2 = 12; c2 <= 32; c2 += 4) {
+        pick_block_n(tm, a->N, sms - c2, a->block_n);
+        if (best < 0 || g_last_cost <= best * 1.001) {
+          best = best < 0 ? g_last_cost : (g_last_cost < best ? g_last_cost : best);
+          comm = c2;
+        }
+      }
+    }
     const size_t par = size_t(a->M) * a->K * 2;
     if (make_tmap(&p.tma_a_local, a->a, p.rows_per_rank, a->K, a->lda, kBlockM) != 0) return -1;
     if (make_tmap(&p.tma_a[0], f->ws, a->M, a->K, a->K, kBlockM) != 0) return -1;

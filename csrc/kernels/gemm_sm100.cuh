@@ -39,6 +39,7 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 x 16-bit = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 256;
+constexpr int kAgParts = 4;  // AG: each 128-row block is pushed as 4 independently flagged 32-row parts
 
 struct GemmParams {
   CUtensorMap tma_a[2];     // AG: gathered workspace for parity 0/1; otherwise [0] only
@@ -64,6 +65,9 @@ struct GemmParams {
   int ar_one_shot;    // AR: every rank reduces every tile (small outputs)
   int use_mc;         // AR: NVLS available
   int transpose_out;  // PLAIN: C is written transposed (swap-AB skinny GEMMs)
+  // grouped (MoE) GEMM: block_expert[m_blk] selects the expert whose [N, K] weight slab (rows
+  // expert*N .. of B) multiplies the 128-row block; negative = padding block, skipped by all roles
+  const int* block_expert;
 };
 
 template <int BLOCK_N, int STAGES>
@@ -149,46 +153,52 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
   const size_t ws_parity_off = size_t(parity) * size_t(p.M) * row_bytes;
   const char* src_base = static_cast<const char*>(p.a_local);
   uint32_t bar_phase = 0;  // bit s = parity of slot s
-  // work items: (step t = 1..W-1, block j), flattened, round-robin over comm CTAs
-  const int total = (W - 1) * bps;
+  // work items: (step t = 1..W-1, block j, part q), flattened in consumption order and dealt round-robin to
+  // the comm CTAs, so that at any time all of them work on the blocks the peers need next
+  const int total = (W - 1) * bps * kAgParts;
   for (int item = comm_idx; item < total; item += num_comm) {
-    const int t = 1 + item / bps;
-    const int j = item % bps;
+    const int t = 1 + item / (bps * kAgParts);
+    const int j = (item / kAgParts) % bps;
+    const int q = item % kAgParts;
     const int peer = (rank - t + W) % W;
-    const int rows = min(kBlockM, p.rows_per_rank - j * kBlockM);
-    const size_t blk_bytes = size_t(rows) * row_bytes;
-    const char* src = src_base + size_t(j) * kBlockM * row_bytes;
-    char* dst = symm_at(p.ctx, static_cast<char*>(p.a_ws), peer) + ws_parity_off +
-                (size_t(rank) * p.rows_per_rank + size_t(j) * kBlockM) * row_bytes;
-    const int n_chunks = int((blk_bytes + kChunk - 1) / kChunk);
-    int issued = 0;
-    for (; issued < n_chunks && issued < kSlots; ++issued) {
-      const uint32_t bytes = uint32_t(min(size_t(kChunk), blk_bytes - size_t(issued) * kChunk));
-      ptx::mbar_arrive_expect_tx(bars + issued, bytes);
-      ptx::bulk_g2s(smem + issued * kChunk, src + size_t(issued) * kChunk, bytes, bars + issued);
-    }
-    for (int k = 0; k < n_chunks; ++k) {
-      const int slot = k % kSlots;
-      const uint32_t bytes = uint32_t(min(size_t(kChunk), blk_bytes - size_t(k) * kChunk));
-      ptx::mbar_wait(bars + slot, (bar_phase >> slot) & 1);
-      bar_phase ^= 1u << slot;
-      ptx::bulk_s2g(dst + size_t(k) * kChunk, smem + slot * kChunk, bytes);
-      ptx::bulk_commit();
-      // refill the slot used by the previous chunk once its smem has been read
-      if (k >= 1 && issued < n_chunks) {
-        ptx::bulk_wait_read<1>();
-        const int rs = (k - 1) % kSlots;
-        const uint32_t b2 = uint32_t(min(size_t(kChunk), blk_bytes - size_t(issued) * kChunk));
-        ptx::mbar_arrive_expect_tx(bars + rs, b2);
-        ptx::bulk_g2s(smem + rs * kChunk, src + size_t(issued) * kChunk, b2, bars + rs);
-        ++issued;
+    const int blk_rows = min(kBlockM, p.rows_per_rank - j * kBlockM);
+    const int r0 = q * (kBlockM / kAgParts);
+    const int rows = min(kBlockM / kAgParts, blk_rows - r0);
+    if (rows > 0) {
+      const size_t part_bytes = size_t(rows) * row_bytes;
+      const char* src = src_base + (size_t(j) * kBlockM + r0) * row_bytes;
+      char* dst = symm_at(p.ctx, static_cast<char*>(p.a_ws), peer) + ws_parity_off +
+                  (size_t(rank) * p.rows_per_rank + size_t(j) * kBlockM + r0) * row_bytes;
+      const int n_chunks = int((part_bytes + kChunk - 1) / kChunk);
+      int issued = 0;
+      for (; issued < n_chunks && issued < kSlots; ++issued) {
+        const uint32_t bytes = uint32_t(min(size_t(kChunk), part_bytes - size_t(issued) * kChunk));
+        ptx::mbar_arrive_expect_tx(bars + issued, bytes);
+        ptx::bulk_g2s(smem + issued * kChunk, src + size_t(issued) * kChunk, bytes, bars + issued);
       }
+      for (int k = 0; k < n_chunks; ++k) {
+        const int slot = k % kSlots;
+        const uint32_t bytes = uint32_t(min(size_t(kChunk), part_bytes - size_t(k) * kChunk));
+        ptx::mbar_wait(bars + slot, (bar_phase >> slot) & 1);
+        bar_phase ^= 1u << slot;
+        ptx::bulk_s2g(dst + size_t(k) * kChunk, smem + slot * kChunk, bytes);
+        ptx::bulk_commit();
+        // refill the slot used by the previous chunk once its smem has been read
+        if (k >= 1 && issued < n_chunks) {
+          ptx::bulk_wait_read<1>();
+          const int rs = (k - 1) % kSlots;
+          const uint32_t b2 = uint32_t(min(size_t(kChunk), part_bytes - size_t(issued) * kChunk));
+          ptx::mbar_arrive_expect_tx(bars + rs, b2);
+          ptx::bulk_g2s(smem + rs * kChunk, src + size_t(issued) * kChunk, b2, bars + rs);
+          ++issued;
+        }
+      }
+      ptx::bulk_wait<0>();  // all stores of this part are complete
+      ptx::fence_proxy_async();
+      ptx::fence_acq_rel_sys();
     }
-    ptx::bulk_wait<0>();  // all stores of this block are complete
-    ptx::fence_proxy_async();
-    ptx::fence_acq_rel_sys();
-    // flags layout (AG): [W src][blocks_per_shard]
-    notify(p.ctx, p.flags + rank * bps + j, peer, epoch);
+    // flags layout (AG): [W src][blocks_per_shard][kAgParts]; empty parts are flagged too
+    notify(p.ctx, p.flags + (rank * bps + j) * kAgParts + q, peer, epoch);
   }
 }
 
@@ -347,6 +357,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
         const int bps = blocks_per_shard(p);
         for (int t = gemm_cta; t < tiles; t += num_gemm) {
           const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+          int b_row = tc.n_blk * BLOCK_N;
+          if (p.block_expert != nullptr) {
+            const int e = p.block_expert[tc.blk];
+            if (e < 0) continue;
+            b_row += e * p.N;
+          }
           const CUtensorMap* ta = &p.tma_a[0];
           int a_row = tc.row0;
           if (p.mode == GEMM_AG) {
@@ -355,8 +371,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               a_row = tc.blk * kBlockM;
             } else {
               ta = &p.tma_a[parity];
-              // wait until block (src, blk) has landed in my workspace
-              wait_ge_sys(p.flags + tc.shard * bps + tc.blk, epoch);
+              // wait until all parts of block (src, blk) have landed in my workspace
+#pragma unroll
+              for (int q = 0; q < kAgParts; ++q) wait_ge_sys(p.flags + (tc.shard * bps + tc.blk) * kAgParts + q, epoch);
               ptx::fence_proxy_async();
             }
           }
@@ -364,8 +381,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             ptx::mbar_wait(empty_bar + stage, ph ^ 1);
             ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);
             ptx::tma_load_2d(smem_a + stage * L::kABytes, ta, full_bar + stage, kb * kBlockK, a_row);
-            ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK,
-                             tc.n_blk * BLOCK_N);
+            ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK, b_row);
             if (++stage == STAGES) {
               stage = 0;
               ph ^= 1;
@@ -382,6 +398,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
         int acc = 0;
         uint32_t acc_ph = 0;
         for (int t = gemm_cta; t < tiles; t += num_gemm) {
+          if (p.block_expert != nullptr && p.block_expert[tile_coord(p, t, tiles_m, tiles_n).blk] < 0) continue;
           ptx::mbar_wait(tmem_empty + acc, acc_ph ^ 1);
           ptx::tcgen05_fence_after();
           const uint32_t d_tmem = tmem_base + acc * kAccStride;
@@ -415,10 +432,32 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       int acc = 0;
       uint32_t acc_ph = 0;
       const int W = p.ctx.world;
+      // RS/AR: a finished tile is published (system fence + counter/flag) one tile LATER, right before the next
+      // tile's stores are issued: by then its NVLink stores have drained, so the fence costs nothing instead of
+      // stalling the epilogue for a link round trip per tile.
+      int pend_t = -1, pend_shard = 0, pend_blk = 0;
+      auto publish = [&](int t_done, int shard, int blk) {
+        ptx::fence_acq_rel_sys();
+        if (p.mode == GEMM_RS) {
+          const int bps = blocks_per_shard(p);
+          const int cidx = shard * bps + blk;
+          const uint32_t done = ptx::atom_add_acq_rel_gpu(p.counters + cidx, 1) + 1;
+          if (done == static_cast<uint32_t>(tiles_n)) {
+            p.counters[cidx] = 0;
+            ptx::fence_acq_rel_sys();
+            notify(p.ctx, p.flags + p.ctx.rank * bps + blk, shard, epoch);
+          }
+        } else {
+          ptx::st_release_sys(p.flags + t_done, epoch);
+        }
+      };
       for (int t = gemm_cta; t < tiles; t += num_gemm) {
         const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+        if (p.block_expert != nullptr && p.block_expert[tc.blk] < 0) continue;
         ptx::mbar_wait(tmem_full + acc, acc_ph);
         ptx::tcgen05_fence_after();
+        if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk);
+        pend_t = -1;
         // destination of this tile
         char* dst_base = static_cast<char*>(p.c);
         long long ld = p.ldc;
@@ -494,29 +533,18 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           }
         }
         if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
-          // publish the tile: all 4 epilogue warps have stored -> one thread signals
+          // all 4 epilogue warps have issued their stores; remember the tile, publish it one tile later
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (warp == 4 && lane == 0) {
-            ptx::fence_acq_rel_sys();
-            if (p.mode == GEMM_RS) {
-              const int bps = blocks_per_shard(p);
-              const int cidx = tc.shard * bps + tc.blk;
-              const uint32_t done = ptx::atom_add_acq_rel_gpu(p.counters + cidx, 1) + 1;
-              if (done == static_cast<uint32_t>(tiles_n)) {
-                p.counters[cidx] = 0;
-                ptx::fence_acq_rel_sys();
-                notify(p.ctx, p.flags + p.ctx.rank * bps + tc.blk, tc.shard, epoch);
-              }
-            } else {
-              ptx::st_release_sys(p.flags + t, epoch);
-            }
-          }
+          pend_t = t;
+          pend_shard = tc.shard;
+          pend_blk = tc.blk;
         }
         if (++acc == 2) {
           acc = 0;
           acc_ph ^= 1;
         }
       }
+      if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk);
     }
     // teardown of the GEMM roles
     ptx::tcgen05_fence_before();

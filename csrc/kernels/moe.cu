@@ -1,0 +1,233 @@
+// moe.cu — MoE index preparation, row gather, top-k weighted reduce and the fused
+// top-k-reduce + reduce-scatter.
+//
+// Reference counterparts: csrc/lib/moe_utils.cu:60-312 (dead CUDA prototype of the align/sort),
+// kernels/nvidia/allgather_group_gemm.py:84-165 (calc_sorted_gather_index_kernel),
+// kernels/nvidia/moe_utils.py:50-405 (index + reduce_topk kernels),
+// kernels/nvidia/moe_reduce_rs.py:292-376 (reduce_topk_reduce_scatter_a2a_intra_node_kernel).
+//
+// Layout convention: "pairs" are flattened (token, k) indices p = token * topk + k. After align/sort,
+// row i of the expert-sorted (block-padded) matrix holds pair sorted_pair_ids[i] (or `num_pairs` for a
+// padding row) and pair p sits at row pair_to_row[p].
+#include "common.cuh"
+
+namespace tdist {
+
+// ------------------------------------------------------------------ align + sort (single CTA)
+// counts -> per-expert padded offsets -> scatter. Order inside an expert is arbitrary (atomic cursor);
+// every row is computed independently downstream, so results do not depend on it.
+__global__ void __launch_bounds__(1024) moe_align_sort_kernel(const int* __restrict__ topk_ids, int num_pairs,
+                                                              int num_experts, int block_m, int* sorted_pair_ids,
+                                                              int* pair_to_row, int* block_expert, int* meta,
+                                                              int max_rows) {
+  extern __shared__ int sh[];  // counts[E] | offsets[E + 1] | cursor[E]
+  int* counts = sh;
+  int* offsets = sh + num_experts;
+  int* cursor = offsets + num_experts + 1;
+  for (int e = threadIdx.x; e < num_experts; e += blockDim.x) counts[e] = 0;
+  __syncthreads();
+  for (int p = threadIdx.x; p < num_pairs; p += blockDim.x) {
+    const int e = topk_ids[p];
+    if (e >= 0 && e < num_experts) atomicAdd(&counts[e], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int e = 0; e < num_experts; ++e) {
+      offsets[e] = acc;
+      acc += (counts[e] + block_m - 1) / block_m * block_m;
+    }
+    offsets[num_experts] = acc;
+    meta[0] = acc;            // rows after padding
+    meta[1] = acc / block_m;  // blocks
+  }
+  __syncthreads();
+  const int total = offsets[num_experts];
+  for (int e = threadIdx.x; e < num_experts; e += blockDim.x) {
+    cursor[e] = offsets[e];
+    for (int b = offsets[e] / block_m; b < offsets[e + 1] / block_m; ++b) block_expert[b] = e;
+  }
+  for (int b = total / block_m + threadIdx.x; b < max_rows / block_m; b += blockDim.x) block_expert[b] = -1;
+  for (int i = threadIdx.x; i < max_rows; i += blockDim.x) sorted_pair_ids[i] = num_pairs;
+  __syncthreads();
+  for (int p = threadIdx.x; p < num_pairs; p += blockDim.x) {
+    const int e = topk_ids[p];
+    if (e >= 0 && e < num_experts) {
+      const int row = atomicAdd(&cursor[e], 1);
+      sorted_pair_ids[row] = p;
+      pair_to_row[p] = row;
+    } else {
+      pair_to_row[p] = -1;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ gather rows into expert-sorted order
+// dst[i, :] = src[sorted_pair_ids[i] / topk, :] (zeros for padding rows). One warp per row.
+__global__ void __launch_bounds__(256) moe_gather_rows_kernel(const int4* __restrict__ src, int4* __restrict__ dst,
+                                                              const int* __restrict__ sorted_pair_ids,
+                                                              const int* __restrict__ meta, int num_pairs, int topk,
+                                                              int row_vecs) {
+  const int rows = meta[0];
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int i = warp; i < rows; i += nwarps) {
+    const int p = sorted_pair_ids[i];
+    int4* d = dst + size_t(i) * row_vecs;
+    if (p >= num_pairs) {
+      for (int v = lane; v < row_vecs; v += 32) d[v] = make_int4(0, 0, 0, 0);
+    } else {
+      const int4* s = src + size_t(p / topk) * row_vecs;
+      for (int v = lane; v < row_vecs; v += 32) d[v] = ptx::ld_nc_v4(s + v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ top-k weighted reduce
+// out[t, :] = sum_k w[t, k] * y[pair_to_row[t * topk + k], :]. One warp per token.
+template <typename Tag>
+__device__ __forceinline__ void topk_reduce_row(const int4* __restrict__ y, const int* __restrict__ pair_to_row,
+                                                const float* __restrict__ weights, int t, int topk, int row_vecs,
+                                                int v, float (&acc)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int k = 0; k < topk; ++k) {
+    const int row = pair_to_row[t * topk + k];
+    if (row < 0) continue;
+    float part[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    Pack<Tag>::add(part, ptx::ld_nc_v4(y + size_t(row) * row_vecs + v));
+    const float w = weights ? weights[t * topk + k] : 1.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = fmaf(w, part[i], acc[i]);
+  }
+}
+
+template <typename Tag>
+__global__ void __launch_bounds__(256) moe_topk_reduce_kernel(const int4* __restrict__ y, int4* __restrict__ out,
+                                                              const int* __restrict__ pair_to_row,
+                                                              const float* __restrict__ weights, int tokens, int topk,
+                                                              int row_vecs) {
+  const size_t total = size_t(tokens) * row_vecs;
+  for (size_t idx = blockIdx.x * size_t(blockDim.x) + threadIdx.x; idx < total; idx += size_t(gridDim.x) * blockDim.x) {
+    const int t = int(idx / row_vecs), v = int(idx % row_vecs);
+    float acc[8];
+    topk_reduce_row<Tag>(y, pair_to_row, weights, t, topk, row_vecs, v, acc);
+    out[idx] = Pack<Tag>::cvt(acc);
+  }
+}
+
+// ------------------------------------------------------------------ fused top-k reduce + reduce-scatter
+// Every rank holds y (expert-sorted partial outputs of ALL tokens, FFN dim sharded). Token segment s
+// (tokens [s*T/W, (s+1)*T/W)) belongs to rank s. Each CTA reduces its slice of segment s over top-k and
+// stores it into slot `rank` of rank s's scatter buffer; after the per-CTA flag exchange the owner sums
+// the W slots. scat (symm): [2 parity][W][seg_tokens * row_vecs].
+template <typename Tag>
+__global__ void __launch_bounds__(512) moe_reduce_rs_kernel(SymmCtx c, const int4* __restrict__ y, int4* scat,
+                                                            int4* __restrict__ out, const int* __restrict__ pair_to_row,
+                                                            const float* __restrict__ weights, int tokens, int topk,
+                                                            int row_vecs, uint32_t* flags, PhaseState ps) {
+  const uint32_t base = phase_begin(ps);
+  const int W = c.world;
+  const int seg_tokens = tokens / W;
+  const size_t seg_vecs = size_t(seg_tokens) * row_vecs;
+  int4* buf = scat + ((base >> 1) & 1) * W * seg_vecs;
+  const size_t per_cta = (seg_vecs + gridDim.x - 1) / gridDim.x;
+  const size_t beg = blockIdx.x * per_cta;
+  const size_t end = min(beg + per_cta, seg_vecs);
+#pragma unroll 1
+  for (int p = 1; p <= W; ++p) {
+    const int o = (c.rank + p) % W;  // own segment last
+    int4* dst = symm_at(c, buf, o) + c.rank * seg_vecs;
+    for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
+      const int t = o * seg_tokens + int(i / row_vecs), v = int(i % row_vecs);
+      float acc[8];
+      topk_reduce_row<Tag>(y, pair_to_row, weights, t, topk, row_vecs, v, acc);
+      ptx::st_v4(dst + i, Pack<Tag>::cvt(acc));
+    }
+  }
+  barrier_all_block(c, flags + blockIdx.x * TDIST_MAX_RANKS, base + 1);
+  for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int s = 0; s < W; ++s) Pack<Tag>::add(acc, ptx::ld_v4(buf + s * seg_vecs + i));
+    out[i] = Pack<Tag>::cvt(acc);
+  }
+  phase_end(ps, base, 2);
+}
+
+}  // namespace tdist
+
+using namespace tdist;
+
+extern "C" {
+
+int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,
+                         int* pair_to_row, int* block_expert, int* meta, int max_rows, void* stream) {
+  if (max_rows % block_m != 0) {
+    set_error("moe_align_sort: max_rows must be a multiple of block_m");
+    return -1;
+  }
+  const size_t smem = (size_t(num_experts) * 3 + 1) * sizeof(int);
+  if (smem > 48 * 1024) {
+    set_error("moe_align_sort: too many experts");
+    return -1;
+  }
+  moe_align_sort_kernel<<<1, 1024, smem, static_cast<cudaStream_t>(stream)>>>(
+      topk_ids, num_pairs, num_experts, block_m, sorted_pair_ids, pair_to_row, block_expert, meta, max_rows);
+  return check_launch("moe_align_sort");
+}
+
+int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, int num_pairs,
+                          int topk, int row_bytes, int max_rows, void* stream) {
+  if (row_bytes % 16 != 0) {
+    set_error("moe_gather_rows: row bytes must be a multiple of 16");
+    return -1;
+  }
+  int grid = (max_rows + 7) / 8;
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  moe_gather_rows_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const int4*>(src), static_cast<int4*>(dst), sorted_pair_ids, meta, num_pairs, topk, row_bytes / 16);
+  return check_launch("moe_gather_rows");
+}
+
+int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,
+                          int topk, int row_bytes, void* stream) {
+  if (row_bytes % 16 != 0) {
+    set_error("moe_topk_reduce: row bytes must be a multiple of 16");
+    return -1;
+  }
+  const int row_vecs = row_bytes / 16;
+  size_t total = size_t(tokens) * row_vecs;
+  int grid = int((total + 255) / 256);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  TDIST_DISPATCH_DTYPE(dtype, {
+    moe_topk_reduce_kernel<Tag><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const int4*>(y), static_cast<int4*>(out), pair_to_row, weights, tokens, topk, row_vecs);
+  });
+  return check_launch("moe_topk_reduce");
+}
+
+int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, void* out,
+                        const int* pair_to_row, const float* weights, int tokens, int topk, int row_bytes, uint32_t* flags,
+                        uint32_t* phase, uint32_t* done, int max_ctas, void* stream) {
+  const SymmCtx c = to_ctx(ctx);
+  if (row_bytes % 16 != 0 || tokens % c.world != 0) {
+    set_error("moe_reduce_rs: row bytes must be a multiple of 16 and tokens divisible by world size");
+    return -1;
+  }
+  const int row_vecs = row_bytes / 16;
+  const size_t seg_vecs = size_t(tokens / c.world) * row_vecs;
+  if (max_ctas > TDIST_MAX_CTAS) max_ctas = TDIST_MAX_CTAS;
+  int grid = int((seg_vecs + 511) / 512);
+  if (grid > max_ctas) grid = max_ctas;
+  if (grid < 1) grid = 1;
+  TDIST_DISPATCH_DTYPE(dtype, {
+    moe_reduce_rs_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+        c, static_cast<const int4*>(y), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), pair_to_row, weights,
+        tokens, topk, row_vecs, flags, PhaseState{phase, done});
+  });
+  return check_launch("moe_reduce_rs");
+}
+
+}  // extern "C"

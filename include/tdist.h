@@ -102,6 +102,10 @@ typedef struct tdist_gemm_args {
   int group_m;             /* 0 = default */
   int num_sms;             /* 0 = all */
   int transpose_out;       /* store C^T (swap-AB skinny GEMM) */
+  /* grouped (MoE) GEMM: b is [num_experts * N, K]; block_expert[i] (device) = expert of 128-row block i of A,
+   * negative = padding block (skipped). NULL = ordinary GEMM. (allgather_group_gemm.py:534-608, moe_reduce_rs.py:166-244) */
+  const int* block_expert;
+  int num_experts;
 } tdist_gemm_args;
 
 /* C = A * B^T (kernels/nvidia/allgather_gemm.py:656-720 gemm_persistent) */
@@ -126,6 +130,37 @@ typedef struct tdist_fused_args {
 /* AG+GEMM (allgather_gemm.py:534-653), GEMM+RS (gemm_reduce_scatter.py:508-583),
  * GEMM+AR (gemm_allreduce.py:509-575): one launch each. */
 int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream);
+
+/* ---- MoE helpers (csrc/kernels/moe.cu; reference csrc/lib/moe_utils.cu, kernels/nvidia/moe_utils.py) ---- */
+/* sort (token,k) pairs by expert, pad every expert to block_m rows. meta[0] = padded rows, meta[1] = blocks. */
+int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,
+                         int* pair_to_row, int* block_expert, int* meta, int max_rows, void* stream);
+int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, int num_pairs,
+                          int topk, int row_bytes, int max_rows, void* stream);
+int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,
+                          int topk, int row_bytes, void* stream);
+/* fused top-k reduce + reduce-scatter over token segments (moe_reduce_rs.py:292-376) */
+int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, void* out,
+                        const int* pair_to_row, const float* weights, int tokens, int topk, int row_bytes, uint32_t* flags,
+                        uint32_t* phase, uint32_t* done, int max_ctas, void* stream);
+
+/* ---- expert-parallel all-to-all (csrc/kernels/ep_a2a.cu) ------------------ */
+/* fixed-slot low-latency all-to-all (kernels/nvidia/low_latency_all_to_all.py:35-257). send rows are sorted by
+ * expert, splits_cumsum has num_experts+1 entries; recv_data (symm) [2][W][max_m][row_bytes], recv_splits (symm)
+ * [2][W*epr], recv_scale (symm, optional) [2][W][max_m]; flags (symm) uint32[2*W] zero initialised. */
+int tdist_a2a(const tdist_symm_ctx* ctx, const void* send, const int* splits_cumsum, const float* send_scale, void* recv_data,
+              int* recv_splits, float* recv_scale, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_m, int row_bytes,
+              int experts_per_rank, int ctas_per_peer, void* stream);
+/* token-level dispatch / combine (kernels/nvidia/ep_a2a.py:36-334, layers/nvidia/ep_a2a_layer.py:118-248) */
+int tdist_ep_counts(const tdist_symm_ctx* ctx, const int* topk_ids, int num_pairs, int num_experts, int* full_counts,
+                    uint32_t* flags, uint32_t* phase, uint32_t* done, void* stream);
+int tdist_ep_dispatch(const tdist_symm_ctx* ctx, int dtype, const void* x, const int* topk_ids, const int* full_counts,
+                      void* recv_buf, float* recv_scale, int* recv_src_pair, int* scatter_idx, int* cursors,
+                      int* recv_expert_counts, int* num_recv, int tokens, int topk, int hidden, int num_experts, int fp8,
+                      uint32_t* flags, uint32_t* grid_counter, uint32_t* phase, uint32_t* done, int num_ctas, void* stream);
+int tdist_ep_combine(const tdist_symm_ctx* ctx, int dtype, const void* expert_out, const int* topk_ids, const int* scatter_idx,
+                     const float* weights, void* out, int tokens, int topk, int hidden, int num_experts, uint32_t* flags,
+                     uint32_t* grid_counter, uint32_t* phase, uint32_t* done, int num_ctas, void* stream);
 
 /* ---- decode-path kernels (csrc/kernels/decode.cu) -------------------------
  * Reference: kernels/nvidia/flash_decode.py:129-532 and the mega_triton_kernel task kernels;

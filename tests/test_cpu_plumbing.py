@@ -33,3 +33,25 @@ def test_fast_allgather_cpu():
 
 def test_reduce_scatter_cpu():
     run_dist(N + "test_reduce_scatter", [256, 128, "--check", "--verify-iters", 1], 2)
+
+
+@pytest.mark.parametrize("model", ["qwen3", "llama", "qwen3_moe"])
+def test_tp_e2e_vs_hf_cpu(model):
+    """DenseLLM / Qwen3MoE sharded over 2 ranks reproduce the HF model's logits in every backend mode."""
+    run_dist(N + "test_tp_e2e", ["--model", model, "--check"], 2, timeout=900)
+
+
+def test_ep_dispatch_combine_cpu():
+    run_dist(N + "test_ep_a2a", ["--check", "--verify-iters", 2], 2)
+
+
+def test_low_latency_all_to_all_cpu():
+    run_dist(N + "test_all_to_all", ["--check", "--verify-iters", 2, "--with-scale"], 2)
+
+
+def test_tp_moe_cpu():
+    run_dist(N + "test_tp_moe", ["--check", "--verify-iters", 1, "-M", 64, "--hidden", 64, "--inter", 32, "-E", 4, "--topk", 2], 2)
+
+
+def test_sp_flash_decode_cpu():
+    run_dist(N + "test_sp_decode_attn", ["--check", "--verify-iters", 1, "--kv-len", 256, "--q-heads", 4, "--kv-heads", 2], 2)

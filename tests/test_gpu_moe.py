@@ -1,0 +1,81 @@
+"""GPU tests of the MoE / EP kernels and of the TP models (native kernels vs torch oracles / HF)."""
+import pytest
+import torch
+
+from conftest import gpu_count, run_dist
+
+pytestmark = pytest.mark.gpu
+N = "triton_dist.test.nvidia."
+
+
+def _worlds():
+    n = gpu_count()
+    return sorted({1, min(n, 2), n} - {0}) if n else [1]
+
+
+@pytest.mark.parametrize("T,E,topk", [(37, 8, 2), (1024, 128, 8), (4096, 256, 8), (5, 64, 4)])
+def test_moe_align_sort_matches_oracle(T, E, topk):
+    from triton_dist.kernels.nvidia.moe_utils import moe_align_sort, torch_align_sort
+
+    torch.manual_seed(0)
+    ids = torch.rand(T, E, device="cuda").topk(topk, dim=-1).indices.int()
+    got, ref = moe_align_sort(ids, E), torch_align_sort(ids, E)
+    assert torch.equal(got.meta, ref.meta)
+    assert torch.equal(got.block_expert, ref.block_expert)
+    # same multiset of pairs inside every expert's row range (order inside an expert is free)
+    flat = ids.reshape(-1)
+    rows = got.pair_to_row.long()
+    assert torch.equal(got.sorted_pair_ids[rows].long(), torch.arange(T * topk, device="cuda"))
+    assert torch.equal(got.block_expert[rows // 128].long(), flat.long())
+    assert int((got.sorted_pair_ids < T * topk).sum()) == T * topk
+
+
+@pytest.mark.parametrize("T,H,I,E,topk", [(256, 1024, 512, 16, 4), (77, 512, 256, 8, 2)])
+def test_grouped_gemm_pipeline(T, H, I, E, topk):
+    from triton_dist.kernels.nvidia.elementwise import silu_mul
+    from triton_dist.kernels.nvidia.moe_utils import grouped_gemm, moe_align_sort, moe_gather_rows, reduce_topk
+
+    torch.manual_seed(1)
+    x = torch.randn(T, H, device="cuda").bfloat16()
+    w1 = (0.05 * torch.randn(E, 2 * I, H, device="cuda")).bfloat16()
+    w2 = (0.05 * torch.randn(E, H, I, device="cuda")).bfloat16()
+    probs = torch.softmax(torch.randn(T, E, device="cuda"), -1)
+    wt, ids = probs.topk(topk, dim=-1)
+    sort = moe_align_sort(ids, E)
+    h = silu_mul(grouped_gemm(moe_gather_rows(x, sort), w1, sort))
+    out = reduce_topk(grouped_gemm(h, w2, sort), sort, wt)
+    ref = torch.zeros(T, H, device="cuda")
+    for e in range(E):
+        tok, k = (ids == e).nonzero(as_tuple=True)
+        if tok.numel():
+            g, u = (x[tok].float() @ w1[e].float().t()).bfloat16().float().chunk(2, -1)
+            hh = (torch.nn.functional.silu(g) * u).bfloat16().float()
+            ref.index_add_(0, tok, (hh @ w2[e].float().t()).bfloat16().float() * wt[tok, k, None])
+    torch.testing.assert_close(out.float(), ref, atol=3e-2 * float(ref.abs().max()), rtol=3e-2)
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_ep_dispatch_combine(world):
+    run_dist(N + "test_ep_a2a", ["--check", "--verify-iters", 3, "--stress"], world)
+    run_dist(N + "test_ep_a2a", ["--check", "--verify-iters", 2, "--fp8"], world)
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_low_latency_all_to_all(world):
+    run_dist(N + "test_all_to_all", ["--check", "--verify-iters", 3, "--with-scale", "--stress"], world)
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_tp_moe(world):
+    run_dist(N + "test_tp_moe", ["--check", "--verify-iters", 2, "--stress"], world)
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_sp_flash_decode(world):
+    run_dist(N + "test_sp_decode_attn", ["--check", "--verify-iters", 2, "--stress"], world)
+
+
+@pytest.mark.parametrize("world", _worlds())
+@pytest.mark.parametrize("model", ["qwen3", "llama", "qwen3_moe"])
+def test_tp_e2e_vs_hf(world, model):
+    run_dist(N + "test_tp_e2e", ["--model", model, "--check"], world, timeout=600)

@@ -55,6 +55,8 @@ class GemmArgs(ctypes.Structure):
         ("group_m", ctypes.c_int),
         ("num_sms", ctypes.c_int),
         ("transpose_out", ctypes.c_int),
+        ("block_expert", ctypes.c_void_p),
+        ("num_experts", ctypes.c_int),
     ]
 
 
@@ -132,6 +134,15 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_flash_decode_combine", [i32, vp, vp, vp, i32, i32, i32, ll, ll, ll, vp])
     sig("tdist_embedding", [i32, vp, vp, vp, i32, i32, vp])
     sig("tdist_argmax", [i32, vp, vp, i32, i32, ll, vp])
+    sig("tdist_moe_align_sort", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp])
+    sig("tdist_moe_gather_rows", [vp, vp, vp, vp, i32, i32, i32, i32, vp])
+    sig("tdist_moe_topk_reduce", [i32, vp, vp, vp, vp, i32, i32, i32, vp])
+    sig("tdist_moe_reduce_rs", [P(SymmCtx), i32, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, i32, vp])
+    sig("tdist_a2a", [P(SymmCtx), vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp])
+    sig("tdist_ep_counts", [P(SymmCtx), vp, i32, i32, vp, vp, vp, vp, vp])
+    sig("tdist_ep_dispatch", [P(SymmCtx), i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp,
+                              i32, vp])
+    sig("tdist_ep_combine", [P(SymmCtx), i32, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
     sig("tdist_gemm", [P(GemmArgs), vp])
     sig("tdist_gemm_fused", [P(GemmArgs), P(FusedArgs), vp])
 

@@ -101,7 +101,7 @@ class AllGatherGEMMTensorParallelContext:
             # [2 parity][max_M][K] gather workspace + per-(src, 128-row block) arrival flags
             self.symm_workspace = heap.alloc((2, self.max_M, self.K), self.tensor_dtype, zero=False)
             self.symm_workspaces = heap.peer_views(self.symm_workspace)
-            self.state = CollectiveState(self.num_ranks * ((self.max_M + 127) // 128) + 64)
+            self.state = CollectiveState(4 * (self.num_ranks * ((self.max_M // self.num_ranks + 127) // 128) + 16))
             self.max_gemm_sm = torch.cuda.get_device_properties("cuda").multi_processor_count
             heap.barrier_all()
             torch.cuda.synchronize()

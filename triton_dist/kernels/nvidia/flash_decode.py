@@ -90,6 +90,28 @@ def gqa_fwd_batch_decode_intra_rank(q, k_cache, v_cache, workspace, q_lens, kv_l
     return output_combine
 
 
+def dense_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, kv_lens: torch.Tensor, scale: float,
+                 kv_split: int = -1, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Decode attention over a DENSE cache [B, S, Hkv, D] (the layout of models.KV_Cache): q [B, Hq, D] -> [B, Hq, D]."""
+    B, Hq, D = q.shape
+    S, Hkv = k_cache.shape[1], k_cache.shape[2]
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    if not (q.is_cuda and q.dtype in (torch.bfloat16, torch.float16) and D == 128):
+        bt = torch.arange(B, dtype=torch.int32, device=q.device)[:, None]
+        o, _ = torch_paged_decode(q, k_cache[:B], v_cache[:B], kv_lens, bt, scale)
+        out.copy_(o.to(q.dtype))
+        return out
+    if kv_split in (-1, None):  # enough CTAs to fill the GPU, at least ~256 positions per split
+        kv_split = max(1, min(64, S // 256, max(1, 296 // max(B * Hkv, 1))))
+    partial = torch.empty((B, Hq, kv_split, D + 1), dtype=torch.float32, device=q.device)
+    _lib.check(_lib.lib().tdist_flash_decode(
+        _lib.dtype_code(q.dtype), q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), kv_lens.data_ptr(), partial.data_ptr(),
+        out.data_ptr(), None, B, Hq, Hkv, D, kv_split, float(scale), k_cache.stride(0), k_cache.stride(1), k_cache.stride(2),
+        None, 0, 0, _lib.stream_ptr()), "flash_decode(dense)")
+    return out
+
+
 def inter_rank_combine(all_ranks_partial: torch.Tensor, out: Optional[torch.Tensor] = None, dtype=torch.bfloat16) -> torch.Tensor:
     """all_ranks_partial: fp32 [W, B, Hq, D+1] (out | lse per rank) -> [B, Hq, D]."""
     W, B, Hq, D1 = all_ranks_partial.shape

@@ -50,6 +50,31 @@ def rand(shape, dtype, scale=1.0):
     return ((torch.rand(shape, dtype=torch.float32, device=device()) * 2 - 1) * scale).to(dtype)
 
 
+def all_ok(ok: bool) -> bool:
+    """Cross-rank AND of a pass/fail flag, so that every rank leaves a verify loop together (a rank that
+    stopped calling a fused op would otherwise hang its peers inside the kernel)."""
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device())
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        ok = bool(t.item())
+    return ok
+
+
+def check_close(x: torch.Tensor, ref_fp32: torch.Tensor, dtype, what: str = "") -> bool:
+    """Compare against an fp32 ground truth with a tolerance scaled to the output magnitude: a few units of
+    the output dtype's epsilon times max|ref| (partial sums are rounded to 16 bit before the cross-rank reduction,
+    exactly as in the reference's symmetric-buffer design). Prints and returns False on mismatch."""
+    eps = {torch.bfloat16: 2.0 ** -8, torch.float16: 2.0 ** -11, torch.float32: 2.0 ** -20}[dtype]
+    scale = float(ref_fp32.abs().max().clamp_min(1e-6))
+    err = (x.float() - ref_fp32).abs()
+    tol = 6 * eps * scale
+    bad = int((err > tol).sum())
+    if bad:
+        dist_print(f"{what}: {bad}/{x.numel()} elements off by more than {tol:.4g} (max err {float(err.max()):.4g}, "
+                   f"max|ref| {scale:.4g})", allowed_ranks="all", prefix=True)
+    return bad == 0
+
+
 def skew(enabled: bool) -> None:
     """Race/hang provocation: delay this rank by a random amount (reference allgather.py:74-78)."""
     if enabled and torch.cuda.is_available():

@@ -5,8 +5,8 @@ import torch
 import torch.distributed as dist
 
 from triton_dist.kernels.nvidia.allgather_gemm import ag_gemm, create_ag_gemm_context, torch_ag_gemm
-from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
-from triton_dist.utils import assert_allclose, dist_print, measured_peaks, NVLINK_GBS_MEASURED
+from triton_dist.test.common import DTYPES, all_ok, base_parser, bench, check_close, finish, rand, setup, skew
+from triton_dist.utils import dist_print, measured_peaks, NVLINK_GBS_MEASURED
 
 if __name__ == "__main__":
     p = base_parser(__doc__)
@@ -29,12 +29,9 @@ if __name__ == "__main__":
         A = rand((m_loc, args.K), dtype)  # fresh inputs every iteration (stale-workspace detection)
         skew(args.stress)
         C = ag_gemm(A, B, ctx)
-        ref = torch_ag_gemm(A, B)
-        try:
-            assert_allclose(C.float(), ref.float(), verbose=False, **TOL[dtype])
-        except RuntimeError as e:
-            ok = False
-            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+        ref = torch_ag_gemm(A.float(), B.float())
+        ok = all_ok(check_close(C, ref, dtype, f"ag_gemm iter {it}"))
+        if not ok:
             break
     if ok and not args.check:
         A = rand((m_loc, args.K), dtype)

@@ -5,8 +5,8 @@ import torch.distributed as dist
 
 from triton_dist.kernels.allreduce import AllReduceMethod, get_allreduce_methods, to_allreduce_method
 from triton_dist.kernels.nvidia.allreduce import all_reduce, create_allreduce_ctx
-from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
-from triton_dist.utils import assert_allclose, dist_print
+from triton_dist.test.common import DTYPES, all_ok, base_parser, bench, check_close, finish, rand, setup, skew
+from triton_dist.utils import dist_print
 
 if __name__ == "__main__":
     p = base_parser(__doc__)
@@ -16,7 +16,7 @@ if __name__ == "__main__":
     args = p.parse_args()
     group, rank, world = setup()
     dtype = DTYPES[args.dtype]
-    ctx = create_allreduce_ctx(max(args.max_bytes, 2**20) * 2 * world + 2**20, rank, world, world)
+    ctx = create_allreduce_ctx(min(max(args.max_bytes, 2**20) * 2 * world + 2**20, 1 << 30), rank, world, world)
     methods = get_allreduce_methods() if args.method == "all" else [args.method]
     ok = True
     sizes = []
@@ -32,15 +32,14 @@ if __name__ == "__main__":
                 x = rand((numel,), dtype)
                 skew(args.stress)
                 y = all_reduce(x, method=method, ctx=ctx)
-                ref = x.clone()
+                ref = x.float()
                 if world > 1:
                     dist.all_reduce(ref)
-                try:
-                    assert_allclose(y.float(), ref.float(), verbose=False, **TOL[dtype])
-                except RuntimeError as e:
-                    ok = False
-                    dist_print(f"{name} {nbytes}B iter {it}: {e}", allowed_ranks="all", prefix=True)
+                ok = all_ok(check_close(y, ref, dtype, f"{name} {nbytes}B iter {it}"))
+                if not ok:
                     break
+            if not ok:
+                break
             if ok and not args.check:
                 x = rand((numel,), dtype)
                 out = torch.empty_like(x)
@@ -50,5 +49,7 @@ if __name__ == "__main__":
                 algo = nbytes / t / 1e6
                 dist_print(f"allreduce {name:22s} {nbytes:>10d} B: {t * 1e3:8.1f} us  algbw {algo:7.1f} GB/s  "
                            f"busbw {algo * 2 * (world - 1) / world:7.1f} GB/s   NCCL {t_nccl * 1e3:8.1f} us")
+        if not ok:
+            break
     ctx.finalize()
     finish(ok)

@@ -4,7 +4,7 @@ import torch.distributed as dist
 
 from triton_dist.kernels.nvidia.low_latency_allgather import (FAST_ALLGATHER_FUNC_DISPATCH, create_fast_allgather_context,
                                                               fast_allgather)
-from triton_dist.test.common import base_parser, bench, finish, setup, skew
+from triton_dist.test.common import all_ok, base_parser, bench, finish, setup, skew
 from triton_dist.utils import bitwise_equal, dist_print, symm_tensor
 
 if __name__ == "__main__":
@@ -36,10 +36,14 @@ if __name__ == "__main__":
                 dist.barrier()
                 skew(args.stress)
                 fast_allgather(buf, ctx, mode=mode)
-                if not bitwise_equal(buf, torch.stack(ref)):
-                    ok = False
+                good = bitwise_equal(buf, torch.stack(ref))
+                if not good:
                     dist_print(f"mode {mode} {nbytes} B iter {it}: mismatch", allowed_ranks="all", prefix=True)
+                ok = all_ok(good)
+                if not ok:
                     break
+            if not ok:
+                break
             if ok and not args.check:
                 t = bench(lambda: fast_allgather(buf, ctx, mode=mode), args, flush_l2=False)
                 dist_print(f"fast_allgather {mode:26s} {nbytes:>9d} B: {t * 1e3:8.1f} us  {nbytes / t / 1e6:7.1f} GB/s")

@@ -5,8 +5,8 @@ import torch.distributed as dist
 
 from triton_dist.kernels.nvidia.gemm_allreduce import (create_gemm_ar_context, gemm_allreduce_op,
                                                        low_latency_gemm_allreduce_op, torch_gemm_ar)
-from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
-from triton_dist.utils import assert_allclose, dist_print
+from triton_dist.test.common import DTYPES, all_ok, base_parser, bench, check_close, finish, rand, setup, skew
+from triton_dist.utils import dist_print
 
 if __name__ == "__main__":
     p = base_parser(__doc__)
@@ -26,12 +26,9 @@ if __name__ == "__main__":
         A = rand((args.M, k_loc), dtype)
         skew(args.stress)
         C = op(ctx, A, B)
-        ref = torch_gemm_ar(A, B)
-        try:
-            assert_allclose(C.float(), ref.float(), verbose=False, **TOL[dtype])
-        except RuntimeError as e:
-            ok = False
-            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+        ref = torch_gemm_ar(A.float(), B.float())
+        ok = all_ok(check_close(C, ref, dtype, f"gemm_ar iter {it}"))
+        if not ok:
             break
     if ok and not args.check:
         A = rand((args.M, k_loc), dtype)

@@ -5,8 +5,8 @@ import torch
 import torch.distributed as dist
 
 from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs, torch_gemm_rs
-from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
-from triton_dist.utils import assert_allclose, dist_print, measured_peaks, NVLINK_GBS_MEASURED
+from triton_dist.test.common import DTYPES, all_ok, base_parser, bench, check_close, finish, rand, setup, skew
+from triton_dist.utils import dist_print, measured_peaks, NVLINK_GBS_MEASURED
 
 if __name__ == "__main__":
     p = base_parser(__doc__)
@@ -26,12 +26,9 @@ if __name__ == "__main__":
         A = rand((args.M, k_loc), dtype)
         skew(args.stress)
         C = gemm_rs(A, B, ctx)
-        ref = torch_gemm_rs(A, B)
-        try:
-            assert_allclose(C.float(), ref.float(), verbose=False, **TOL[dtype])
-        except RuntimeError as e:
-            ok = False
-            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+        ref = torch_gemm_rs(A.float(), B.float())  # fp32 ground truth
+        ok = all_ok(check_close(C, ref, dtype, f"gemm_rs iter {it}"))
+        if not ok:
             break
     if ok and not args.check:
         A = rand((args.M, k_loc), dtype)

@@ -3,8 +3,8 @@ import torch
 import torch.distributed as dist
 
 from triton_dist.kernels.nvidia.reduce_scatter import create_reduce_scater_2d_ctx, reduce_scatter_2d_op, torch_reduce_scatter
-from triton_dist.test.common import DTYPES, TOL, base_parser, bench, finish, rand, setup, skew
-from triton_dist.utils import assert_allclose, dist_print
+from triton_dist.test.common import DTYPES, all_ok, base_parser, bench, check_close, finish, rand, setup, skew
+from triton_dist.utils import dist_print
 
 if __name__ == "__main__":
     p = base_parser(__doc__)
@@ -19,12 +19,9 @@ if __name__ == "__main__":
         x = rand((args.M, args.N), dtype)
         skew(args.stress)
         y = reduce_scatter_2d_op(x, ctx)
-        ref = torch_reduce_scatter(x)
-        try:
-            assert_allclose(y.float(), ref.float(), verbose=False, **TOL[dtype])
-        except RuntimeError as e:
-            ok = False
-            dist_print(f"iter {it}: {e}", allowed_ranks="all", prefix=True)
+        ref = torch_reduce_scatter(x.float())
+        ok = all_ok(check_close(y, ref, dtype, f"reduce_scatter iter {it}"))
+        if not ok:
             break
     if ok and not args.check:
         x = rand((args.M, args.N), dtype)

@@ -535,3 +535,17 @@ def measured_peaks() -> dict:
 
 
 NVLINK_GBS_MEASURED = 770.0  # per direction per GPU, B200_PROFILING.md
+
+
+def all_to_all_compat(outs: List[torch.Tensor], ins: List[torch.Tensor], group=None) -> None:
+    """dist.all_to_all that also works on gloo (CPU plumbing tests): variable-size exchange through
+    all_gather_object when the backend has no alltoall."""
+    if ins[0].is_cuda:
+        dist.all_to_all(outs, ins, group=group)
+        return
+    rank = dist.get_rank(group)
+    world = dist.get_world_size(group)
+    gathered: List[Optional[list]] = [None] * world
+    dist.all_gather_object(gathered, [t.clone() for t in ins], group=group)
+    for s in range(world):
+        outs[s].copy_(gathered[s][rank].reshape(outs[s].shape))

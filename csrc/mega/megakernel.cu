@@ -1,0 +1,648 @@
+// megakernel.cu — the persistent decode megakernel: one launch executes a whole decode step.
+//
+// Every CTA (one per SM) walks its static work queue; a task spins on the scoreboard slots of the ops it
+// depends on, runs its body, and bumps its own op's slot. Scoreboard values are monotone (slot value after step
+// s == s * tiles(op)), so nothing is reset between steps and the launch is CUDA-graph capturable.
+// Reference dispatcher: mega_triton_kernel/core/code_generator.py:31-89; task bodies:
+// mega_triton_kernel/kernels/{linear,mlp_fc1,norm,activation,elementwise,flash_attn,allreduce,barrier,prefetch}.py.
+//
+// B200 specifics: all decode linears are weight-streaming GEMVs on CUDA cores (M = batch <= 8 rows; the tensor
+// core would idle at this arithmetic intensity) with 16-byte loads, 8 in flight per lane, and the FIRST batch of
+// weight loads is issued BEFORE the dependency wait — weights do not depend on activations, so the HBM latency of
+// every task start hides behind the scoreboard wait. RMSNorm is folded into the consumer linear's prologue, SiLU*up
+// into fc1's epilogue and the residual add into the all-reduce, which removes three scoreboard hops per layer.
+// The all-reduce is NVLS multimem.ld_reduce with a per-tile cross-rank flag exchange.
+#include <cuda_bf16.h>
+#include <math_constants.h>
+
+#include "../kernels/common.cuh"
+#include "mega.h"
+
+namespace tdist {
+namespace mega {
+
+using bf16 = __nv_bfloat16;
+
+__device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = ptx::unpack_bf16x2(u[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ int4 pack8(const float (&f)[8]) {
+  int4 r;
+  r.x = ptx::pack_bf16x2(f[0], f[1]);
+  r.y = ptx::pack_bf16x2(f[2], f[3]);
+  r.z = ptx::pack_bf16x2(f[4], f[5]);
+  r.w = ptx::pack_bf16x2(f[6], f[7]);
+  return r;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  v = ptx::warp_reduce_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) scratch[w] = v;
+  __syncthreads();
+  float r = l < (kThreads >> 5) ? scratch[l] : 0.f;
+  r = ptx::warp_reduce_sum(r);
+  return r;
+}
+
+__device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t target) {
+  if (slot < 0) return;
+  while (static_cast<int32_t>(ptx::ld_acquire_gpu(sb + slot) - target) < 0) {
+  }
+}
+
+// ------------------------------------------------------------------ LINEAR (GEMV, M <= 8)
+// i0 bit0: silu pairing (W = [2I, K], out = silu(gate) * up, N = I); i1: ldy; i2: out parity stride (bytes, 0 = none)
+template <int MAXM>
+__device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* smem, uint32_t step, const uint32_t* sb,
+                                            const Task& t, uint32_t dep_target0, uint32_t dep_target1) {
+  constexpr int UN = 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = kThreads >> 5;
+  const int K = a.K, kv = K >> 3;
+  const bool pair = (a.i0 & 1) != 0;
+  const bf16* W = static_cast<const bf16*>(a.in1);
+  const int c_beg = tile * a.cols_per_tile, c_end = min(c_beg + a.cols_per_tile, a.N);
+  bf16* xs = reinterpret_cast<bf16*>(smem);            // [M][K] normalised activations
+  float* scratch = reinterpret_cast<float*>(smem + size_t(a.M) * K * 2);
+
+  // (1) first batch of weight loads for this warp's first column: issued before the dependency wait
+  int4 wpre[UN];
+  const int c_first = c_beg + warp;
+  if (c_first < c_end) {
+    const bf16* wr = W + size_t(c_first) * K;
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+      const int kk = lane + u * 32;
+      wpre[u] = kk < kv ? ptx::ld_nc_v4(wr + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
+    }
+  }
+  // (2) dependencies
+  if (threadIdx.x == 0) {
+    wait_slot(sb, t.dep0, dep_target0);
+    wait_slot(sb, t.dep1, dep_target1);
+  }
+  __syncthreads();
+  // (3) stage x (optionally RMS-normalised) in shared memory
+  const bf16* x = static_cast<const bf16*>(a.in0);
+  const bf16* nw = static_cast<const bf16*>(a.in2);
+  for (int m = 0; m < a.M; ++m) {
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < kv; i += kThreads) {
+      const int4 raw = ptx::ld_v4(x + size_t(m) * K + size_t(i) * 8);
+      *reinterpret_cast<int4*>(xs + size_t(m) * K + size_t(i) * 8) = raw;
+      if (nw != nullptr) {
+        float f[8];
+        unpack8(raw, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss = fmaf(f[j], f[j], ss);
+      }
+    }
+    if (nw != nullptr) {
+      const float tot = block_sum(ss, scratch);
+      const float inv = rsqrtf(tot / K + a.f0);
+      for (int i = threadIdx.x; i < kv; i += kThreads) {
+        float f[8], w[8];
+        unpack8(*reinterpret_cast<const int4*>(xs + size_t(m) * K + size_t(i) * 8), f);
+        unpack8(ptx::ld_nc_v4(nw + size_t(i) * 8), w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = __bfloat162float(__float2bfloat16(f[j] * inv)) * w[j];  // round like the unfused norm
+        *reinterpret_cast<int4*>(xs + size_t(m) * K + size_t(i) * 8) = pack8(f);
+      }
+    }
+  }
+  __syncthreads();
+  // (4) stream the weights
+  char* out_base = static_cast<char*>(a.out0) + (a.i2 ? size_t(step & 1) * a.i2 : 0);
+  bf16* y = reinterpret_cast<bf16*>(out_base);
+  const bf16* bias = static_cast<const bf16*>(a.in3);
+  for (int c = c_first; c < c_end; c += nwarps) {
+    float acc[MAXM], acc2[MAXM];
+#pragma unroll
+    for (int m = 0; m < MAXM; ++m) acc[m] = acc2[m] = 0.f;
+    const int passes = pair ? 2 : 1;
+    for (int ps = 0; ps < passes; ++ps) {
+      const bf16* wr = W + size_t(ps == 0 ? c : c + a.N) * K;
+      for (int k0 = lane; k0 < kv; k0 += 32 * UN) {
+        int4 wv[UN];
+        if (c == c_first && ps == 0 && k0 == lane) {
+#pragma unroll
+          for (int u = 0; u < UN; ++u) wv[u] = wpre[u];
+        } else {
+#pragma unroll
+          for (int u = 0; u < UN; ++u) {
+            const int kk = k0 + u * 32;
+            wv[u] = kk < kv ? ptx::ld_nc_v4(wr + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < UN; ++u) {
+          const int kk = k0 + u * 32;
+          if (kk >= kv) break;
+          float wf[8];
+          unpack8(wv[u], wf);
+#pragma unroll
+          for (int m = 0; m < MAXM; ++m) {
+            if (m < a.M) {
+              float xf[8];
+              unpack8(*reinterpret_cast<const int4*>(xs + size_t(m) * K + size_t(kk) * 8), xf);
+              float s = 0.f;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) s = fmaf(wf[i], xf[i], s);
+              if (ps == 0)
+                acc[m] += s;
+              else
+                acc2[m] += s;
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < MAXM; ++m) {
+      if (m < a.M) {
+        float g = ptx::warp_reduce_sum(acc[m]);
+        if (pair) {
+          const float u = ptx::warp_reduce_sum(acc2[m]);
+          // round gate/up to bf16 first: matches the unfused fc1 -> silu_mul sequence bit for bit in the common case
+          g = __bfloat162float(__float2bfloat16(g));
+          const float uu = __bfloat162float(__float2bfloat16(u));
+          g = g / (1.f + __expf(-g)) * uu;
+        }
+        if (bias != nullptr) g += __bfloat162float(bias[c]);
+        if (lane == 0) y[size_t(m) * a.i1 + c] = __float2bfloat16(g);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ RMS_NORM (tile = row), optional residual add
+__device__ __forceinline__ void rmsnorm_body(const OpArgs& a, int tile, uint8_t* smem) {
+  const int K = a.K, kv = K >> 3;
+  float* row = reinterpret_cast<float*>(smem);
+  float* scratch = row + K;
+  const bf16* x = static_cast<const bf16*>(a.in0) + size_t(tile) * K;
+  bf16* res = a.in3 ? static_cast<bf16*>(const_cast<void*>(a.in3)) + size_t(tile) * K : nullptr;
+  float ss = 0.f;
+  for (int i = threadIdx.x; i < kv; i += kThreads) {
+    float f[8];
+    unpack8(ptx::ld_v4(x + size_t(i) * 8), f);
+    if (res) {
+      float r[8];
+      unpack8(ptx::ld_v4(res + size_t(i) * 8), r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+      const int4 p = pack8(f);
+      *reinterpret_cast<int4*>(res + size_t(i) * 8) = p;
+      unpack8(p, f);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      row[i * 8 + j] = f[j];
+      ss = fmaf(f[j], f[j], ss);
+    }
+  }
+  const float inv = rsqrtf(block_sum(ss, scratch) / K + a.f0);
+  const bf16* w = static_cast<const bf16*>(a.in2);
+  bf16* y = static_cast<bf16*>(a.out0) + size_t(tile) * K;
+  for (int i = threadIdx.x; i < kv; i += kThreads) {
+    float wv[8], o[8];
+    unpack8(ptx::ld_nc_v4(w + size_t(i) * 8), wv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = __bfloat162float(__float2bfloat16(row[i * 8 + j] * inv)) * wv[j];
+    *reinterpret_cast<int4*>(y + size_t(i) * 8) = pack8(o);
+  }
+}
+
+// ------------------------------------------------------------------ elementwise
+__device__ __forceinline__ void silu_mul_body(const OpArgs& a, int tile) {
+  const int inter = a.N, iv = inter >> 3;
+  const long long total = (long long)a.M * iv;
+  const bf16* gu = static_cast<const bf16*>(a.in0);
+  bf16* out = static_cast<bf16*>(a.out0);
+  for (long long idx = (long long)tile * kThreads + threadIdx.x; idx < total; idx += (long long)a.tiles * kThreads) {
+    const long long r = idx / iv;
+    const int c = int(idx % iv);
+    float g[8], u[8], o[8];
+    unpack8(ptx::ld_v4(gu + r * 2 * inter + size_t(c) * 8), g);
+    unpack8(ptx::ld_v4(gu + r * 2 * inter + inter + size_t(c) * 8), u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = g[j] / (1.f + __expf(-g[j])) * u[j];
+    *reinterpret_cast<int4*>(out + r * inter + size_t(c) * 8) = pack8(o);
+  }
+}
+__device__ __forceinline__ void add_body(const OpArgs& a, int tile) {
+  const long long nv = (long long)a.N >> 3;
+  const int4* x = static_cast<const int4*>(a.in0);
+  const int4* y = static_cast<const int4*>(a.in1);
+  int4* o = static_cast<int4*>(a.out0);
+  for (long long i = (long long)tile * kThreads + threadIdx.x; i < nv; i += (long long)a.tiles * kThreads) {
+    float p[8], q[8];
+    unpack8(ptx::ld_v4(x + i), p);
+    unpack8(ptx::ld_v4(y + i), q);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] += q[j];
+    o[i] = pack8(p);
+  }
+}
+
+// ------------------------------------------------------------------ q/k norm + RoPE + KV append (head_dim 128)
+// in0 qkv [B, (Hq+2Hkv)*128]; in1/in2 k/v cache; in3/in4 q/k norm weights; in5 cos_sin fp32 [max_pos,128];
+// out0 q_out [B,Hq,128]; out1 positions (int32 [B]); out2 block_table (int32 [B,max_pages]) or null.
+// i0 Hq, i1 Hkv, i2 page_size, i3 max_pages; l0/l1/l2 batch(page)/seq/head strides of the cache.
+__device__ __forceinline__ void qk_rope_body(const OpArgs& a, int tile) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Hq = a.i0, Hkv = a.i1, heads = Hq + 2 * Hkv;
+  const int total = a.M * heads;
+  const int* positions = static_cast<const int*>(a.out1);
+  const int* block_table = static_cast<const int*>(a.out2);
+  for (int item = tile * (kThreads >> 5) + warp; item < total; item += a.tiles * (kThreads >> 5)) {
+    const int b = item / heads, h = item % heads;
+    const bf16* src = static_cast<const bf16*>(a.in0) + (size_t(b) * heads + h) * 128 + lane * 4;
+    const uint2 raw = *reinterpret_cast<const uint2*>(src);
+    float f[4];
+    {
+      const float2 p = ptx::unpack_bf16x2(raw.x), q = ptx::unpack_bf16x2(raw.y);
+      f[0] = p.x, f[1] = p.y, f[2] = q.x, f[3] = q.y;
+    }
+    const bool is_q = h < Hq, is_k = !is_q && h < Hq + Hkv;
+    const int pos = positions[b];
+    if (is_q || is_k) {
+      const bf16* nw = static_cast<const bf16*>(is_q ? a.in3 : a.in4);
+      if (nw != nullptr) {
+        float ss = f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];
+        ss = ptx::warp_reduce_sum(ss);
+        const float inv = rsqrtf(ss / 128.f + a.f0);
+        const uint2 wr = *reinterpret_cast<const uint2*>(nw + lane * 4);
+        const float2 wa = ptx::unpack_bf16x2(wr.x), wb = ptx::unpack_bf16x2(wr.y);
+        f[0] = __bfloat162float(__float2bfloat16(f[0] * inv)) * wa.x;
+        f[1] = __bfloat162float(__float2bfloat16(f[1] * inv)) * wa.y;
+        f[2] = __bfloat162float(__float2bfloat16(f[2] * inv)) * wb.x;
+        f[3] = __bfloat162float(__float2bfloat16(f[3] * inv)) * wb.y;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f[i] = __bfloat162float(__float2bfloat16(f[i]));
+      }
+      const float* cs = static_cast<const float*>(a.in5) + size_t(pos) * 128 + (lane & 15) * 4;
+      const float4 c = *reinterpret_cast<const float4*>(cs), s = *reinterpret_cast<const float4*>(cs + 64);
+      const float cc[4] = {c.x, c.y, c.z, c.w}, sn[4] = {s.x, s.y, s.z, s.w};
+      float o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float other = __shfl_xor_sync(0xffffffffu, f[i], 16);
+        o[i] = lane < 16 ? f[i] * cc[i] - other * sn[i] : f[i] * cc[i] + other * sn[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) f[i] = o[i];
+    }
+    uint2 packed;
+    packed.x = ptx::pack_bf16x2(f[0], f[1]);
+    packed.y = ptx::pack_bf16x2(f[2], f[3]);
+    if (is_q) {
+      *reinterpret_cast<uint2*>(static_cast<bf16*>(a.out0) + (size_t(b) * Hq + h) * 128 + lane * 4) = packed;
+    } else {
+      const int kvh = is_k ? h - Hq : h - Hq - Hkv;
+      size_t off;
+      if (block_table != nullptr) {
+        const int page = block_table[size_t(b) * a.i3 + pos / a.i2];
+        off = size_t(page) * a.l0 + size_t(pos % a.i2) * a.l1 + size_t(kvh) * a.l2;
+      } else {
+        off = size_t(b) * a.l0 + size_t(pos) * a.l1 + size_t(kvh) * a.l2;
+      }
+      bf16* dst = static_cast<bf16*>(const_cast<void*>(is_k ? a.in1 : a.in2)) + off + lane * 4;
+      *reinterpret_cast<uint2*>(dst) = packed;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ attention: split-KV decode (head_dim 128)
+// in0 q [B,Hq,128]; in1/in2 caches; in3 block_table; in4 positions (kv_len = pos + 1); out0 partial [B,Hq,S,129].
+// i0 Hq, i1 Hkv, i2 page_size, i3 max_pages, i4 splits; f0 scale. tile = (b * Hkv + kvh) * S + split.
+template <int G>
+__device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int g_total, int g_off) {
+  constexpr int D = 128, NG = kThreads / 16;  // 32 position groups
+  const int S = a.i4, Hq = a.i0, Hkv = a.i1;
+  const int split = tile % S, kvh = (tile / S) % Hkv, b = tile / (S * Hkv);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane & 15, grp = warp * 2 + (lane >> 4);
+  const int kv_len = static_cast<const int*>(a.in4)[b] + 1;
+  const int per_split = (kv_len + S - 1) / S;
+  const int s_beg = split * per_split, s_end = min(s_beg + per_split, kv_len);
+  const int h0 = kvh * g_total + g_off;
+  const bf16* q = static_cast<const bf16*>(a.in0);
+  const bf16* kc = static_cast<const bf16*>(a.in1);
+  const bf16* vc = static_cast<const bf16*>(a.in2);
+  const int* block_table = static_cast<const int*>(a.in3);
+  float qf[G][8], m[G], l[G], o[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    unpack8(ptx::ld_v4(q + (size_t(b) * Hq + h0 + g) * D + sub * 8), qf[g]);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      qf[g][i] *= a.f0 * 1.4426950408889634f;
+      o[g][i] = 0.f;
+    }
+    m[g] = -CUDART_INF_F;
+    l[g] = 0.f;
+  }
+  auto kv_off = [&](int pos) -> size_t {
+    if (block_table != nullptr) {
+      const int page = block_table[size_t(b) * a.i3 + pos / a.i2];
+      return size_t(page) * a.l0 + size_t(pos % a.i2) * a.l1 + size_t(kvh) * a.l2;
+    }
+    return size_t(b) * a.l0 + size_t(pos) * a.l1 + size_t(kvh) * a.l2;
+  };
+  constexpr int UN = 2;
+  for (int p0 = s_beg + grp * UN; p0 < s_end; p0 += NG * UN) {
+    int4 kr[UN], vr[UN];
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+      if (p0 + u < s_end) {
+        const size_t off = kv_off(p0 + u) + sub * 8;
+        kr[u] = ptx::ld_v4(kc + off);
+        vr[u] = ptx::ld_v4(vc + off);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+      if (p0 + u >= s_end) break;
+      float kf[8], vf[8];
+      unpack8(kr[u], kf);
+      unpack8(vr[u], vf);
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s = fmaf(qf[g][i], kf[i], s);
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        const float mn = fmaxf(m[g], s);
+        const float corr = exp2f(m[g] - mn), pe = exp2f(s - mn);
+        l[g] = l[g] * corr + pe;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[g][i] = fmaf(pe, vf[i], o[g][i] * corr);
+        m[g] = mn;
+      }
+    }
+  }
+  float* sh_m = reinterpret_cast<float*>(smem);  // [NG][G]
+  float* sh_l = sh_m + NG * G;
+  float* sh_o = sh_l + NG * G;                   // [NG][G][D]
+  __syncthreads();
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    if (sub == 0) {
+      sh_m[grp * G + g] = m[g];
+      sh_l[grp * G + g] = l[g];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sh_o[(grp * G + g) * D + sub * 8 + i] = o[g][i];
+  }
+  __syncthreads();
+  float* partial = static_cast<float*>(a.out0);
+  for (int idx = threadIdx.x; idx < G * D; idx += kThreads) {
+    const int g = idx / D, d = idx % D;
+    float mm = -CUDART_INF_F;
+    for (int r = 0; r < NG; ++r) mm = fmaxf(mm, sh_m[r * G + g]);
+    float ll = 0.f, acc = 0.f;
+    for (int r = 0; r < NG; ++r) {
+      const float mr = sh_m[r * G + g];
+      const float w = mr == -CUDART_INF_F ? 0.f : exp2f(mr - mm);
+      ll += sh_l[r * G + g] * w;
+      acc += sh_o[(r * G + g) * D + d] * w;
+    }
+    float* dst = partial + ((size_t(b) * Hq + h0 + g) * S + split) * (D + 1);
+    dst[d] = ll > 0.f ? acc / ll : 0.f;
+    if (d == 0) dst[D] = ll > 0.f ? (mm + log2f(ll)) * 0.6931471805599453f : -CUDART_INF_F;
+  }
+  __syncthreads();
+}
+
+// combine: in0 partial [B,Hq,S,129] -> out0 [B,Hq,128] bf16. tile = 4 (b,h) pairs.
+__device__ __forceinline__ void attn_combine_body(const OpArgs& a, int tile) {
+  constexpr int D = 128;
+  const int S = a.i4, Hq = a.i0;
+  const int bh = tile * (kThreads / D) + threadIdx.x / D, d = threadIdx.x % D;
+  if (bh >= a.M * Hq) return;
+  const float* base = static_cast<const float*>(a.in0) + size_t(bh) * S * (D + 1);
+  float mx = -CUDART_INF_F;
+  for (int s = 0; s < S; ++s) mx = fmaxf(mx, base[size_t(s) * (D + 1) + D]);
+  float den = 0.f, acc = 0.f;
+  for (int s = 0; s < S; ++s) {
+    const float lse = base[size_t(s) * (D + 1) + D];
+    const float w = lse == -CUDART_INF_F ? 0.f : __expf(lse - mx);
+    den += w;
+    acc += w * base[size_t(s) * (D + 1) + d];
+  }
+  static_cast<bf16*>(a.out0)[size_t(bh) * D + d] = __float2bfloat16(den > 0.f ? acc / den : 0.f);
+}
+
+// ------------------------------------------------------------------ all-reduce (+ residual add)
+// in0: symmetric partial buffer (bf16, N elements per parity, i2 = parity stride bytes); in3: residual (updated in
+// place: residual += sum) or null; out0: reduced output (bf16) or null when only the residual is wanted.
+// i0 = AR op ordinal (flag row block). Per-tile cross-rank flag exchange, then NVLS ld_reduce (P2P sum without NVLS).
+__device__ __forceinline__ void allreduce_body(const KernelParams& p, const OpArgs& a, int tile, uint32_t step) {
+  const SymmCtx& c = p.ctx;
+  const int W = c.world;
+  uint32_t* flags = p.ar_flags + (size_t(a.i0) * kMaxArTiles + tile) * TDIST_MAX_RANKS;
+  if (W > 1) barrier_all_block(c, flags, step);
+  char* buf = static_cast<char*>(const_cast<void*>(a.in0)) + (a.i2 ? size_t(step & 1) * a.i2 : 0);
+  const long long nv = (long long)a.N >> 3;
+  const long long per = (nv + a.tiles - 1) / a.tiles;
+  const long long beg = (long long)tile * per, end = min(beg + per, nv);
+  bf16* res = static_cast<bf16*>(const_cast<void*>(a.in3));
+  bf16* out = static_cast<bf16*>(a.out0);
+  for (long long i = beg + threadIdx.x; i < end; i += kThreads) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (W > 1 && c.mc_base != nullptr) {
+      unpack8(ptx::multimem_ld_reduce_bf16x8(mc_ptr(c, buf) + i * 16), acc);
+    } else {
+      for (int s = 0; s < W; ++s) {
+        float part[8];
+        unpack8(ptx::ld_v4(symm_at(c, buf, (c.rank + s) % W) + i * 16), part);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += part[j];
+      }
+    }
+    if (res != nullptr) {
+      // the summed projection is rounded to bf16 first, exactly like an unfused all-reduce followed by an add
+      float r[8];
+      unpack8(ptx::ld_v4(res + i * 8), r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = __bfloat162float(__float2bfloat16(acc[j])) + r[j];
+      *reinterpret_cast<int4*>(res + i * 8) = pack8(acc);
+    }
+    if (out != nullptr) *reinterpret_cast<int4*>(out + i * 8) = pack8(acc);
+  }
+}
+
+__device__ __forceinline__ void prefetch_body(const OpArgs& a, int tile) {
+  const size_t bytes = size_t(a.N) * a.K * 2;
+  const size_t piece = 4096;
+  const size_t pieces = (bytes + piece - 1) / piece;
+  const char* base = static_cast<const char*>(a.in1);
+  for (size_t i = size_t(tile) * kThreads + threadIdx.x; i < pieces; i += size_t(a.tiles) * kThreads) {
+    const size_t off = i * piece;
+    ptx::prefetch_l2_bulk(base + off, uint32_t(min(piece, bytes - off)));
+  }
+}
+
+__device__ __forceinline__ void embedding_body(const OpArgs& a, int tile) {
+  const long long id = static_cast<const long long*>(a.in0)[tile];
+  const int4* src = reinterpret_cast<const int4*>(static_cast<const bf16*>(a.in1) + size_t(id) * a.K);
+  int4* dst = reinterpret_cast<int4*>(static_cast<bf16*>(a.out0) + size_t(tile) * a.K);
+  for (int i = threadIdx.x; i < a.K / 8; i += kThreads) dst[i] = src[i];
+}
+
+__device__ __forceinline__ void argmax_body(const OpArgs& a, int tile, uint8_t* smem) {
+  float* sv = reinterpret_cast<float*>(smem);
+  int* si = reinterpret_cast<int*>(smem + 64 * sizeof(float));
+  const bf16* row = static_cast<const bf16*>(a.in0) + size_t(tile) * a.i1;
+  float best = -CUDART_INF_F;
+  int bi = 0;
+  for (int i = threadIdx.x; i < a.N; i += kThreads) {
+    const float v = __bfloat162float(row[i]);
+    if (v > best) {
+      best = v;
+      bi = i;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) {
+      best = ov;
+      bi = oi;
+    }
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) {
+    sv[threadIdx.x >> 5] = best;
+    si[threadIdx.x >> 5] = bi;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (kThreads >> 5); ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) {
+        best = sv[w];
+        bi = si[w];
+      }
+    static_cast<long long*>(a.out0)[tile] = bi;
+  }
+}
+
+// ------------------------------------------------------------------ the interpreter
+__global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant__ KernelParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const PhaseState ps{p.step_state, p.step_state + 1};
+  const uint32_t base = phase_begin(ps);
+  const uint32_t step = base + 1;
+  const int n = p.queue_len[blockIdx.x];
+  const Task* q = p.queues + size_t(blockIdx.x) * p.max_tasks;
+  for (int i = 0; i < n; ++i) {
+    const Task t = q[i];
+    const OpArgs& a = p.ops[t.op];
+    const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1 = step * uint32_t(t.dep1_cnt);
+    if (t.type == OP_LINEAR) {
+      // waits for its dependencies inside (after issuing the first weight loads)
+      if (a.M <= 1)
+        linear_body<1>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
+      else if (a.M <= 2)
+        linear_body<2>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
+      else if (a.M <= 4)
+        linear_body<4>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
+      else
+        linear_body<8>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
+    } else {
+      if (threadIdx.x == 0) {
+        wait_slot(p.scoreboard, t.dep0, tgt0);
+        wait_slot(p.scoreboard, t.dep1, tgt1);
+      }
+      __syncthreads();
+      switch (t.type) {
+        case OP_RMS_NORM: rmsnorm_body(a, t.tile, smem); break;
+        case OP_SILU_MUL: silu_mul_body(a, t.tile); break;
+        case OP_ADD: add_body(a, t.tile); break;
+        case OP_QK_NORM_ROPE_KV: qk_rope_body(a, t.tile); break;
+        case OP_ATTN_SPLIT: {
+          const int g = a.i0 / a.i1;
+          int done = 0;
+          while (done < g) {
+            const int rem = g - done;
+            if (rem >= 8) {
+              attn_split_body<8>(a, t.tile, smem, g, done);
+              done += 8;
+            } else if (rem >= 4) {
+              attn_split_body<4>(a, t.tile, smem, g, done);
+              done += 4;
+            } else if (rem >= 2) {
+              attn_split_body<2>(a, t.tile, smem, g, done);
+              done += 2;
+            } else {
+              attn_split_body<1>(a, t.tile, smem, g, done);
+              done += 1;
+            }
+          }
+          break;
+        }
+        case OP_ATTN_COMBINE: attn_combine_body(a, t.tile); break;
+        case OP_ALLREDUCE: allreduce_body(p, a, t.tile, step); break;
+        case OP_BARRIER:
+          if (p.ctx.world > 1) barrier_all_block(p.ctx, p.ar_flags + (size_t(a.i0) * kMaxArTiles) * TDIST_MAX_RANKS, step);
+          break;
+        case OP_PREFETCH: prefetch_body(a, t.tile); break;
+        case OP_EMBEDDING: embedding_body(a, t.tile); break;
+        case OP_ARGMAX: argmax_body(a, t.tile, smem); break;
+        default: break;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && t.out_slot >= 0) {
+      __threadfence();
+      atomicAdd(p.scoreboard + t.out_slot, 1u);
+    }
+  }
+  phase_end(ps, base, 1);
+}
+
+}  // namespace mega
+}  // namespace tdist
+
+extern "C" int tdist_mega_launch(const void* params, int num_ctas, int smem_bytes, void* stream) {
+  using namespace tdist::mega;
+  static int attr_set = 0;
+  if (attr_set < smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(megakernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) {
+      tdist::set_error(std::string("megakernel smem attribute: ") + cudaGetErrorString(e));
+      return -1;
+    }
+    attr_set = smem_bytes;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_ctas);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const KernelParams* kp = static_cast<const KernelParams*>(params);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, megakernel, *kp);
+  if (e != cudaSuccess) {
+    tdist::set_error(std::string("megakernel launch: ") + cudaGetErrorString(e));
+    return -1;
+  }
+  return 0;
+}

@@ -194,6 +194,32 @@ int tdist_flash_decode_combine(int dtype, const float* partial, void* out16, flo
 int tdist_embedding(int dtype, const long long* ids, const void* table, void* out, int tokens, int hidden, void* stream);
 int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vocab, long long ld, void* stream);
 
+/* ---- persistent decode megakernel (csrc/mega; reference python/triton_dist/mega_triton_kernel) ---- */
+enum {
+  TDIST_MEGA_LINEAR = 0, TDIST_MEGA_RMS_NORM = 1, TDIST_MEGA_SILU_MUL = 2, TDIST_MEGA_ADD = 3, TDIST_MEGA_QK_NORM_ROPE_KV = 4,
+  TDIST_MEGA_ATTN_SPLIT = 5, TDIST_MEGA_ATTN_COMBINE = 6, TDIST_MEGA_ALLREDUCE = 7, TDIST_MEGA_BARRIER = 8,
+  TDIST_MEGA_PREFETCH = 9, TDIST_MEGA_EMBEDDING = 10, TDIST_MEGA_ARGMAX = 11
+};
+/* Generic op record; the meaning of every slot per op type is documented in csrc/mega/megakernel.cu. */
+typedef struct tdist_mega_op {
+  const void* in[6];
+  void* out[3];
+  int M, N, K;
+  int i[6];
+  long long l[3];
+  float f[2];
+} tdist_mega_op;
+int tdist_mega_create(int rank, int world, int num_ctas, void** out);
+/* returns the op index (>= 0) or -1. dep0: -2 previous op, -1 none, >= 0 explicit; dep1: -1 none or explicit. */
+int tdist_mega_add_op(void* builder, int type, const tdist_mega_op* desc, int dep0, int dep1, int chain);
+/* ar_flags: symmetric uint32[(#allreduce + #barrier ops) * 32 * TDIST_MAX_RANKS], zero initialised (NULL if world == 1) */
+int tdist_mega_compile(void* builder, const tdist_symm_ctx* ctx, uint32_t* ar_flags);
+int tdist_mega_run(void* builder, void* stream);
+int tdist_mega_info(void* builder, int* out6); /* ops, tasks, max queue length, smem bytes, CTAs, #cross-rank ops */
+int tdist_mega_op_tiles(void* builder, int op_index);
+int tdist_mega_get_queue(void* builder, int cta, int* out_8ints_per_task, int cap);
+int tdist_mega_destroy(void* builder);
+
 #ifdef __cplusplus
 }
 #endif

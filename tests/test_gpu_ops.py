@@ -1,7 +1,7 @@
 """GPU tests: numerics of every native kernel against a plain PyTorch fp32 reference.
 
-Single-process tests call the C ABI through the Python wrappers; distributed ops run the
-script-style tests under torchrun at world sizes 1 and min(#GPUs, 8)."""
+Single-process tests call the C ABI through the Python wrappers; distributed ops run as suites of the script-style
+tests (one torchrun launch per suite and world size: 1 GPU and all GPUs of the box)."""
 import pytest
 import torch
 
@@ -9,12 +9,10 @@ from conftest import gpu_count, run_dist
 
 pytestmark = pytest.mark.gpu
 
-N = "triton_dist.test.nvidia."
-
 
 def _worlds():
     n = gpu_count()
-    return sorted({1, min(n, 2), n} - {0}) if n else [1]
+    return sorted({1, n} - {0}) if n else [1]
 
 
 def test_native_library_is_loaded():
@@ -61,36 +59,6 @@ def test_gemm_skinny_swap_ab(M):
 
 
 @pytest.mark.parametrize("world", _worlds())
-def test_ag_gemm(world):
-    run_dist(N + "test_ag_gemm", [2048 * world, 512 * world, 1024, "--check", "--stress"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_ag_gemm_ragged(world):
-    run_dist(N + "test_ag_gemm", [200 * world, 136 * world, 520, "--check"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_gemm_rs(world):
-    run_dist(N + "test_gemm_rs", [2048 * world, 1024, 512 * world, "--check", "--stress"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_gemm_ar(world):
-    run_dist(N + "test_gemm_ar", [64, 1024, 512 * world, "--check", "--low-latency", "--stress"], world)
-    run_dist(N + "test_gemm_ar", [2048, 1024, 256 * world, "--check"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_allreduce(world):
-    run_dist(N + "test_allreduce", ["--check", "--max-bytes", 4 * 2**20, "--verify-iters", 2, "--stress"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_fast_allgather(world):
-    run_dist(N + "test_fast_allgather", ["--check", "--max-bytes", 2**20, "--verify-iters", 2, "--stress"], world)
-
-
-@pytest.mark.parametrize("world", _worlds())
-def test_reduce_scatter(world):
-    run_dist(N + "test_reduce_scatter", [1024 * world, 1024, "--check", "--stress"], world)
+def test_distributed_core_suite(world):
+    """AG+GEMM, GEMM+RS, GEMM+AR, AllReduce (all methods), fast AllGather (all modes), ReduceScatter."""
+    run_dist("triton_dist.test.nvidia.run_suite", ["--suite", "core"], world, timeout=900)

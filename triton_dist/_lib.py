@@ -77,6 +77,19 @@ class FusedArgs(ctypes.Structure):
     ]
 
 
+class MegaOp(ctypes.Structure):
+    _fields_ = [
+        ("inp", ctypes.c_void_p * 6),
+        ("out", ctypes.c_void_p * 3),
+        ("M", ctypes.c_int),
+        ("N", ctypes.c_int),
+        ("K", ctypes.c_int),
+        ("i", ctypes.c_int * 6),
+        ("l", ctypes.c_longlong * 3),
+        ("f", ctypes.c_float * 2),
+    ]
+
+
 _LIB: Optional[ctypes.CDLL] = None
 _LIB_ERR: Optional[str] = None
 
@@ -143,6 +156,14 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_ep_dispatch", [P(SymmCtx), i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp,
                               i32, vp])
     sig("tdist_ep_combine", [P(SymmCtx), i32, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
+    sig("tdist_mega_create", [i32, i32, i32, P(vp)])
+    sig("tdist_mega_add_op", [vp, i32, P(MegaOp), i32, i32, i32])
+    sig("tdist_mega_compile", [vp, P(SymmCtx), vp])
+    sig("tdist_mega_run", [vp, vp])
+    sig("tdist_mega_info", [vp, P(i32 * 6)])
+    sig("tdist_mega_op_tiles", [vp, i32])
+    sig("tdist_mega_get_queue", [vp, i32, vp, i32])
+    sig("tdist_mega_destroy", [vp])
     sig("tdist_gemm", [P(GemmArgs), vp])
     sig("tdist_gemm_fused", [P(GemmArgs), P(FusedArgs), vp])
 

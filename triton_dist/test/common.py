@@ -32,8 +32,15 @@ def base_parser(desc: str) -> argparse.ArgumentParser:
     return p
 
 
+_SUITE = {"active": False, "group": None, "results": []}
+
+
 def setup(seed: int = 3407):
-    group = initialize_distributed(seed=None)
+    if _SUITE["active"] and _SUITE["group"] is not None:  # suite mode: one process group / heap for many cases
+        group = _SUITE["group"]
+    else:
+        group = initialize_distributed(seed=None)
+        _SUITE["group"] = group
     rank, world = dist.get_rank(), dist.get_world_size()
     torch.manual_seed(seed + rank)
     from triton_dist.runtime import get_heap
@@ -85,9 +92,45 @@ def finish(ok: bool = True):
     if torch.cuda.is_available():
         torch.cuda.synchronize()
     dist.barrier()
+    if _SUITE["active"]:
+        _SUITE["results"].append(bool(ok))
+        raise SystemExit(0 if ok else 1)
     dist_print("PASS" if ok else "FAIL")
     finalize_distributed()
     sys.exit(0 if ok else 1)
+
+
+def run_suite(cases) -> bool:
+    """Run several script-style tests in ONE process group (saves the ~20 s start-up per torchrun launch).
+    ``cases``: list of (module, [argv...])."""
+    import runpy
+    import traceback
+
+    _SUITE["active"] = True
+    all_good = True
+    for mod, argv in cases:
+        sys.argv = [mod] + [str(a) for a in argv]
+        good = False
+        try:
+            runpy.run_module(mod, run_name="__main__")
+        except SystemExit as e:
+            good = (e.code in (0, None))
+        except Exception:
+            traceback.print_exc()
+            good = False
+        good = all_ok(good) if dist.is_initialized() else good
+        dist_print(f"[suite] {mod.split('.')[-1]} {' '.join(str(a) for a in argv)}: {'ok' if good else 'FAILED'}")
+        all_good = all_good and good
+        if not good:
+            break  # peers may be out of step after a failure: stop here
+    _SUITE["active"] = False
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+    if dist.is_initialized():
+        dist.barrier()
+    dist_print("PASS" if all_good else "FAIL")
+    finalize_distributed()
+    return all_good
 
 
 def bench(fn, args, group=None, flush_l2=True):

@@ -1,0 +1,47 @@
+"""Run a named group of distributed checks in one torchrun launch.
+    torchrun --nproc-per-node N -m triton_dist.test.nvidia.run_suite --suite core|moe|models|all"""
+import argparse
+import os
+import sys
+
+from triton_dist.test.common import run_suite
+
+T = "triton_dist.test.nvidia."
+M = "triton_dist.mega_triton_kernel.test.models."
+
+
+def cases(suite: str, world: int):
+    core = [
+        (T + "test_ag_gemm", [2048 * world, 512 * world, 1024, "--check", "--stress"]),
+        (T + "test_ag_gemm", [200 * world, 136 * world, 520, "--check", "--verify-iters", 2]),
+        (T + "test_gemm_rs", [2048 * world, 1024, 512 * world, "--check", "--stress"]),
+        (T + "test_gemm_ar", [64, 1024, 512 * world, "--check", "--low-latency", "--stress"]),
+        (T + "test_gemm_ar", [2048, 1024, 256 * world, "--check", "--verify-iters", 2]),
+        (T + "test_allreduce", ["--check", "--max-bytes", 4 * 2**20, "--verify-iters", 2, "--stress"]),
+        (T + "test_fast_allgather", ["--check", "--max-bytes", 2**20, "--verify-iters", 2, "--stress"]),
+        (T + "test_reduce_scatter", [1024 * world, 1024, "--check", "--stress"]),
+    ]
+    moe = [
+        (T + "test_ep_a2a", ["--check", "--verify-iters", 3, "--stress"]),
+        (T + "test_ep_a2a", ["--check", "--verify-iters", 2, "--fp8"]),
+        (T + "test_all_to_all", ["--check", "--verify-iters", 3, "--with-scale", "--stress"]),
+        (T + "test_tp_moe", ["--check", "--verify-iters", 2, "--stress"]),
+        (T + "test_sp_decode_attn", ["--check", "--verify-iters", 2, "--stress"]),
+    ]
+    models = [
+        (T + "test_tp_e2e", ["--model", "qwen3", "--check"]),
+        (T + "test_tp_e2e", ["--model", "llama", "--check"]),
+        (T + "test_tp_e2e", ["--model", "qwen3_moe", "--check"]),
+        (M + "test_qwen3", []),
+        (M + "test_qwen3", ["--unfused"]),
+    ]
+    return {"core": core, "moe": moe, "models": models, "all": core + moe + models}[suite]
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--suite", default="all", choices=["core", "moe", "models", "all"])
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    ok = run_suite(cases(args.suite, world))
+    sys.exit(0 if ok else 1)

@@ -78,7 +78,7 @@ def build(verbose: bool = False, clean: bool = False) -> Path:
     cmd = [ninja or sys.executable, "-f", str(ninja_file)] if ninja else [sys.executable, "-m", "ninja", "-f", str(ninja_file)]
     if verbose:
         cmd.append("-v")
-    subprocess.run(cmd, check=True, cwd=str(ROOT))
+    subprocess.run(cmd, check=True, cwd=str(BUILD_DIR))  # .ninja_log / .ninja_deps stay inside build/
     return LIB
 
 

@@ -198,3 +198,33 @@ __device__ __forceinline__ void grid_barrier(uint32_t* counter) {
 }
 
 }  // namespace tdist
+
+// ---------------------------------------------------------------- small device utilities
+namespace tdist {
+// Binary search helpers (reference common_ops.py:256-344 bisect_left / bisect_right): first index in the sorted
+// array a[0..n) whose element is >= v (left) or > v (right).
+template <typename T>
+__device__ __forceinline__ int bisect_left(const T* a, int n, T v) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (a[mid] < v)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+template <typename T>
+__device__ __forceinline__ int bisect_right(const T* a, int n, T v) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (a[mid] <= v)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  return lo;
+}
+}  // namespace tdist

@@ -266,6 +266,7 @@ __global__ void __launch_bounds__(128) flash_decode_split_kernel(
   constexpr int D = 128;
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t half_mask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
   const int sub = lane & 15;         // which 8-dim slice
   const int grp = warp * 2 + (lane >> 4);  // position group 0..7
   const int kv_len = kv_lens[b];
@@ -320,10 +321,12 @@ __global__ void __launch_bounds__(128) flash_decode_split_kernel(
 #pragma unroll
         for (int i = 0; i < 8; ++i) s = fmaf(qf[g][i], kf[i], s);
         // reduce over the 16 lanes of this half-warp
-        s += __shfl_xor_sync(0xffffffffu, s, 8);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        // the two half-warps walk different key positions and may leave the loop at different times:
+        // shuffle only inside this half-warp
+        s += __shfl_xor_sync(half_mask, s, 8);
+        s += __shfl_xor_sync(half_mask, s, 4);
+        s += __shfl_xor_sync(half_mask, s, 2);
+        s += __shfl_xor_sync(half_mask, s, 1);
         const float mn = fmaxf(m[g], s);
         const float corr = exp2f(m[g] - mn);
         const float pexp = exp2f(s - mn);

@@ -331,6 +331,7 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
   const int split = tile % S, kvh = (tile / S) % Hkv, b = tile / (S * Hkv);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int sub = lane & 15, grp = warp * 2 + (lane >> 4);
+  const uint32_t half_mask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
   const int kv_len = static_cast<const int*>(a.in4)[b] + 1;
   const int per_split = (kv_len + S - 1) / S;
   const int s_beg = split * per_split, s_end = min(s_beg + per_split, kv_len);
@@ -380,10 +381,12 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
         float s = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) s = fmaf(qf[g][i], kf[i], s);
-        s += __shfl_xor_sync(0xffffffffu, s, 8);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        // the two half-warps walk different key positions and may leave the loop at different times:
+        // shuffle only inside this half-warp
+        s += __shfl_xor_sync(half_mask, s, 8);
+        s += __shfl_xor_sync(half_mask, s, 4);
+        s += __shfl_xor_sync(half_mask, s, 2);
+        s += __shfl_xor_sync(half_mask, s, 1);
         const float mn = fmaxf(m[g], s);
         const float corr = exp2f(m[g] - mn), pe = exp2f(s - mn);
         l[g] = l[g] * corr + pe;

@@ -194,6 +194,17 @@ int tdist_flash_decode_combine(int dtype, const float* partial, void* out16, flo
 int tdist_embedding(int dtype, const long long* ids, const void* table, void* out, int tokens, int hidden, void* stream);
 int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vocab, long long ld, void* stream);
 
+/* ---- sequence-parallel prefill attention (csrc/kernels/sp_attn.cu; reference
+ *      kernels/nvidia/sp_ag_attention_intra_node.py:186-425) ------------------------------------------------ */
+/* varlen causal GQA flash-attention of this rank's query shard over the all-gathered K/V (global token order).
+ * q/out [total_q_local, Hq, 128]; k/v gathered [total_k_global, Hkv, 128]; cu_q local / cu_k global offsets [B+1]. */
+int tdist_sp_attn_fwd(const void* q, const void* k_gathered, const void* v_gathered, void* out, const int* cu_q, const int* cu_k,
+                      int B, int max_q_local, int Hq, int Hkv, int head_dim, int rank, int world, int causal, int zigzag,
+                      float sm_scale, void* stream);
+/* scatter this rank's K (or V) shard rows into global order in a gathered buffer (local or peer-mapped) */
+int tdist_sp_kv_scatter(const void* src, void* dst, const int* cu_k_global, int B, int max_local_rows, int row_bytes, int rank,
+                        int world, int zigzag, void* stream);
+
 /* ---- persistent decode megakernel (csrc/mega; reference python/triton_dist/mega_triton_kernel) ---- */
 enum {
   TDIST_MEGA_LINEAR = 0, TDIST_MEGA_RMS_NORM = 1, TDIST_MEGA_SILU_MUL = 2, TDIST_MEGA_ADD = 3, TDIST_MEGA_QK_NORM_ROPE_KV = 4,

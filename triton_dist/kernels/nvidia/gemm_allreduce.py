@@ -54,6 +54,7 @@ class GemmARContext:
             self.state = CollectiveState(n_tiles + 64)
             self.flags2 = heap.alloc((n_tiles + 64,), torch.int32)
             self.use_mc = bool(heap.multicast)
+            self.gemv_state = CollectiveState(16 * _lib.MAX_RANKS)  # decode path: GEMV + in-place NVLS all-reduce
 
     def get_gemm_out_buf(self, input, weight):
         M, N = input.shape[0], weight.shape[0]
@@ -67,6 +68,7 @@ class GemmARContext:
             heap.free(self.symm_ar_out_buf)
             heap.free(self.flags2)
             self.state.free()
+            self.gemv_state.free()
             self.symm_gemm_out_buf = None
 
 
@@ -121,6 +123,19 @@ def _launch(ctx: GemmARContext, a: torch.Tensor, b: torch.Tensor, one_shot: bool
     if not ctx.native:
         return torch_gemm_ar(a, b)
     heap = _symm.get_heap()
+    if M <= 16 and one_shot and ctx.use_mc and K % 8 == 0:
+        # decode: the tensor core would idle at <= 16 rows. Weight-streaming GEMV straight into the symmetric buffer,
+        # then the NVLS one-shot all-reduce in place (multimem.ld_reduce; no staging copy).
+        from .elementwise import gemv
+
+        sym = ctx.symm_gemm_out_buf.view(-1)[:M * N].view(M, N)
+        gemv(a, b, out=sym)
+        out = torch.empty((M, N), dtype=a.dtype, device=a.device)
+        st = ctx.gemv_state
+        _lib.check(_lib.lib().tdist_allreduce(ctypes.byref(heap.ctx), 5, _lib.dtype_code(a.dtype), sym.data_ptr(), out.data_ptr(),
+                                              M * N * a.element_size(), sym.data_ptr(), M * N * a.element_size(), st.flags_ptr,
+                                              st.phase_ptr, st.done_ptr, 8, 1, _lib.stream_ptr()), "gemv_allreduce")
+        return out
     if one_shot:
         out = torch.empty((M, N), dtype=a.dtype, device=a.device)
     else:

@@ -670,3 +670,81 @@ int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vo
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ flash decode without any allocation
+//
+// tdist_flash_decode() needs a caller-provided fp32 scratch buffer for the per-split partial results. Some callers
+// cannot provide one: code running inside a CUDA-graph capture or inside a serving loop that has handed all device
+// memory to its own pool, plugins that are loaded into a process whose allocator they must not touch, and C callers
+// that have no allocator wired up at all. For them the scratch below lives inside the library image: the driver
+// reserves it once per GPU when the module is loaded and keeps it until the process exits, so this entry point never
+// calls cudaMalloc / cudaFree (nor any torch or library routine that could).
+//
+// Capacity: kNoAllocMaxRows partial rows of 129 floats (one row per batch x query head x kv split), i.e. ~2.0 MiB per
+// GPU. Larger problems are rejected with an error; use tdist_flash_decode() with your own buffer for those.
+//
+// Two things to know when calling it:
+//  * The first call on each GPU looks up where that GPU's copy of the scratch lives (cudaGetSymbolAddress, with the
+//    calling thread's current device). That lookup is a host-side query which may load the module, so make the first
+//    call on a device ordinary (eager) work; later calls on that device only launch kernels.
+//  * There is ONE scratch per GPU, shared by every call and left holding the previous call's partials. Calls issued to
+//    the same stream are ordered and safe. Two calls that can run at the same time on one GPU (different streams,
+//    different host threads) would overwrite each other's partials: serialise them or use tdist_flash_decode().
+namespace tdist {
+constexpr int kNoAllocMaxRows = 4096;
+static __device__ __align__(256) float g_flash_decode_scratch[kNoAllocMaxRows * 129];
+
+// In host code `g_flash_decode_scratch` is only a handle for the symbol, not an address the GPU can use: the device
+// address has to be looked up per device (every GPU that loads the library has its own copy of the array).
+constexpr int kMaxDevices = 64;
+static float* g_scratch_dev_ptr[kMaxDevices] = {nullptr};
+
+static int no_alloc_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error(std::string("flash_decode_noalloc: cannot identify the current device: ") + cudaGetErrorString(e));
+    return -1;
+  }
+  if (g_scratch_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_flash_decode_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error(std::string("flash_decode_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+      return -1;
+    }
+    g_scratch_dev_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_scratch_dev_ptr[dev];
+  return 0;
+}
+}  // namespace tdist
+
+extern "C" int tdist_flash_decode_noalloc(int dtype, const void* q, const void* k_cache, const void* v_cache,
+                                          const int* kv_lens, void* out16, int B, int Hq, int Hkv, int head_dim, int splits,
+                                          float sm_scale, long long kv_batch_stride, long long kv_seq_stride,
+                                          long long kv_head_stride, const int* block_table, int page_size, int max_pages,
+                                          void* stream) {
+  if (head_dim != 128 || Hkv <= 0 || Hq % Hkv != 0) {
+    set_error("flash_decode_noalloc: head_dim must be 128 and Hq a multiple of Hkv");
+    return -1;
+  }
+  if (B <= 0 || splits <= 0 || out16 == nullptr) {
+    set_error("flash_decode_noalloc: B and splits must be positive and out16 must be given");
+    return -1;
+  }
+  const long long rows = (long long)B * Hq * splits;
+  if (rows > kNoAllocMaxRows) {
+    set_error("flash_decode_noalloc: B * Hq * splits = " + std::to_string(rows) + " exceeds the built-in scratch of " +
+              std::to_string(kNoAllocMaxRows) + " rows; use tdist_flash_decode() with a caller-provided buffer");
+    return -1;
+  }
+  float* scratch = nullptr;
+  if (no_alloc_scratch(&scratch) != 0) return -1;
+  // Nothing has to be cleared: the split kernel writes every (batch, head, split) row it is launched for, including
+  // the "empty split" marker, and the combine kernel reads exactly those rows.
+  FlashDecodeArgs a{q, k_cache, v_cache, kv_lens, scratch, out16, nullptr, B, Hq, Hkv, splits, sm_scale,
+                    kv_batch_stride, kv_seq_stride, kv_head_stride, block_table, page_size, max_pages};
+  DISPATCH_16(dtype, { launch_flash_decode<T>(a, static_cast<cudaStream_t>(stream)); });
+  return check_launch("flash_decode_noalloc");
+}

@@ -191,6 +191,20 @@ int tdist_flash_decode(int dtype, const void* q, const void* k_cache, const void
 /* log-sum-exp merge of `splits` partials with arbitrary strides (floats): inter-rank combine of distributed decode */
 int tdist_flash_decode_combine(int dtype, const float* partial, void* out16, float* out_lse, int B, int H, int splits,
                                long long stride_b, long long stride_h, long long stride_s, void* stream);
+/* Decode attention for callers that may not allocate device memory (no counterpart in the reference: it was added
+ * for this library's own users). Same computation as tdist_flash_decode(), but the split-KV scratch is a fixed array
+ * inside the library (about 2 MiB per GPU, reserved by the driver when the library is loaded and held until the process
+ * exits), so the call performs no cudaMalloc/cudaFree and pulls in no allocating library. Meant for code that runs
+ * where allocation is forbidden or unavailable: inside a serving loop whose pool owns all device memory, in a plugin
+ * that must not use its host's allocator, or from C with no allocator wired up.
+ * Limit: B * Hq * splits <= 4096 partial rows, otherwise -1 with a message (use tdist_flash_decode with your own buffer).
+ * The first call on each GPU also resolves that GPU's copy of the scratch (cudaGetSymbolAddress on the current device):
+ * make that first call outside any stream capture. All calls on a GPU share the one scratch, which still holds the
+ * previous call's partials; calls ordered on one stream are safe, calls that may overlap on the GPU race. */
+int tdist_flash_decode_noalloc(int dtype, const void* q, const void* k_cache, const void* v_cache, const int* kv_lens,
+                               void* out16, int B, int Hq, int Hkv, int head_dim, int splits, float sm_scale,
+                               long long kv_batch_stride, long long kv_seq_stride, long long kv_head_stride,
+                               const int* block_table, int page_size, int max_pages, void* stream);
 int tdist_embedding(int dtype, const long long* ids, const void* table, void* out, int tokens, int hidden, void* stream);
 int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vocab, long long ld, void* stream);
 

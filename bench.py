@@ -1,13 +1,14 @@
 #!/usr/bin/env python
 """Headline benchmark (driver contract, see README/DESIGN).
 
-Metric: aggregate TFLOP/s of one tensor-parallel MLP projection pair on the
-Llama-3-8B shape named in BASELINE.json config 2 —
+Metric: aggregate TFLOP/s of one tensor-parallel MLP projection pair on the Llama-3-8B shape named in BASELINE.json
+config 2 —
   step = AG+GEMM  (M=8192, K=4096,  N=14336 sharded over ranks)
        + GEMM+RS  (M=8192, K=14336 sharded over ranks, N=4096)
-run at TP = number of GPUs, bf16, synthetic inputs, random weights. Total work is
-fixed as GPUs are added (strong scaling). Device-timed with CUDA events around
-every step, L2 flushed between steps, max over ranks.
+run at TP = number of GPUs, bf16, synthetic inputs, random weights. Total work is fixed as GPUs are added (strong
+scaling). Device-timed with CUDA events around every step, L2 flushed between steps, max over ranks.
+The JSON line also carries the second half of the BASELINE.json metric, Qwen3-32B decode ms/token at TP=N (bs=1,
+ctx=512, random-init weights, one megakernel launch per token), under "decode".
 
     python bench.py --gpus 1 --steps 20 --warmup 5
     python -m torch.distributed.run --nproc-per-node 8 ... bench.py --gpus 8 --steps 20 --warmup 5
@@ -19,8 +20,8 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
+import threading
 import time
 from pathlib import Path
 
@@ -32,8 +33,8 @@ METRIC = "ag_gemm+gemm_rs aggregate TFLOP/s (Llama-3-8B MLP shape, TP=N)"
 
 
 def reference_arm(args) -> None:
-    """The reference needs its Triton fork (LLVM + NVIDIA toolchain downloads) and nvshmem4py; the offline
-    install fails (DESIGN.md 'Reference arm'), so there is nothing to run."""
+    """The reference needs its Triton fork (LLVM + NVIDIA toolchain downloads) and nvshmem4py; the offline install
+    fails, so there is nothing to run."""
     ref = ROOT / "baseline" / "_ref"
     why = "reference not installable offline: python/setup.py downloads LLVM/toolchain (URLError), nvshmem4py absent"
     if ref.exists() and any(ref.iterdir()):
@@ -43,45 +44,91 @@ def reference_arm(args) -> None:
 
 
 class ClockSampler:
-    def __init__(self, enabled: bool):
-        self.proc = None
-        self.path = Path(os.environ.get("TMPDIR", "/tmp")) / f"tdist_clocks_{os.getpid()}.csv"
-        if enabled:
-            try:
-                q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-                     "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-                     "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-                self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
-                                             stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
-            except Exception:
-                self.proc = None
+    """NVML poller (SM clock + throttle reasons of the GPUs in use) running in a thread while the timed region executes;
+    a 5 ms period gives samples even for regions of a few tens of milliseconds."""
 
-    def stop(self, n_gpus: int) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        self.proc.terminate()
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, n_gpus: int, enabled: bool):
+        self.samples, self.max_clock, self.reasons = [], None, set()
+        self._stop = threading.Event()
+        self._thread = None
+        self.nv = None
+        if not enabled:
+            return
         try:
-            self.proc.wait(timeout=5)
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handles = [pynvml.nvmlDeviceGetHandleByIndex(i) for i in range(n_gpus)]
+            self.max_clock = max(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM) for h in self.handles)
         except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        try:
-            for ln in self.path.read_text().splitlines():
-                f = [x.strip() for x in ln.split(",")]
-                if len(f) < 9 or not f[0].isdigit() or int(f[0]) >= n_gpus:
-                    continue
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-                for name, v in zip(names, f[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            self.path.unlink(missing_ok=True)
-        except Exception:
-            pass
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                for h in self.handles:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    for bit, name in self.REASONS.items():
+                        if mask & bit:
+                            self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def start(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self) -> dict:
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_clock, "reasons": ["unsampled"], "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_clock, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def decode_section(rank: int, world: int, steps: int):
+    """Qwen3-32B decode latency at TP=world: bs=1, ctx=512, megakernel (one launch per token)."""
+    import torch
+    import torch.distributed as dist
+
+    from triton_dist.mega_triton_kernel import ModelBuilder, Qwen3Model
+    from triton_dist.models import DenseLLM, ModelConfig
+    from triton_dist.utils import measured_peaks, perf_func_max_over_ranks
+
+    cfg = ModelConfig(model_name="Qwen/Qwen3-32B", max_length=1024, dtype=torch.bfloat16, rank=rank, world_size=world)
+    dense = DenseLLM(cfg, None)
+    builder = ModelBuilder(rank, world, world)
+    mega = Qwen3Model(1, cfg, builder, dense=dense)
+    mega.set_kv_len(512, fill_random=True)
+    ids = torch.full((1,), 1225, dtype=torch.long, device="cuda")
+
+    def step():
+        mega.kv_cache.set_position(512)
+        return mega.mega_forwrad(ids)
+
+    _, ms = perf_func_max_over_ranks(step, steps, 3)
+    wbytes = dense.lm_head.numel() * 2 + sum(w.numel() * 2 for l in dense.layers for w in (l.attn.wqkv, l.attn.wo, l.mlp.gate_up_proj, l.mlp.down_proj))
+    pk = measured_peaks()
+    floor = wbytes / (pk["hbm_gbs"] * 1e6)
+    info = builder.info()
+    out = {"model": "Qwen3-32B (random init)", "tp": world, "bsz": 1, "ctx": 512, "ms_per_token": round(ms, 4),
+           "weight_bytes_per_token_per_rank": wbytes, "hbm_floor_ms_of_" + pk["source"]: round(floor, 4),
+           "fraction_of_hbm_floor": round(floor / ms, 3), "launches_per_token": 1, "graph": info,
+           "reference_published_ms_8xH800": 7.41 if world == 8 else None}
+    mega.finalize()
+    del dense
+    torch.cuda.empty_cache()
+    return out
 
 
 def main() -> None:
@@ -90,6 +137,7 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="tdist", choices=["tdist", "torch", "reference"])
+    ap.add_argument("--no-decode", action="store_true", help="skip the Qwen3-32B decode section")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
@@ -105,7 +153,7 @@ def main() -> None:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29555")
     from triton_dist.kernels.nvidia.allgather_gemm import ag_gemm, create_ag_gemm_context, torch_ag_gemm
-    from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs, torch_gemm_rs
+    from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs, gemm_rs_op, torch_gemm_rs
     from triton_dist.utils import NVLINK_GBS_MEASURED, finalize_distributed, initialize_distributed, measured_peaks
 
     initialize_distributed(seed=1234)
@@ -129,7 +177,6 @@ def main() -> None:
     if args.impl == "tdist":
         def step(x):
             ag_gemm(x, w_up, ag_ctx, out=h)
-            from triton_dist.kernels.nvidia.gemm_reduce_scatter import gemm_rs_op
             return gemm_rs_op(h, w_down, rs_ctx, output=y)
         launches_per_step = 2
     else:
@@ -137,42 +184,66 @@ def main() -> None:
             return torch_gemm_rs(torch_ag_gemm(x, w_up), w_down)
         launches_per_step = 0
 
-    def timed(n_steps: int, e2e: bool):
+    def timed_device(n_steps: int) -> float:
         """Sum of per-step device times (ms); L2 flushed before every step, outside the timed span."""
         evs = []
         for _ in range(n_steps):
             flush.zero_()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
-            if e2e:
-                xin = x_host.to(dev, non_blocking=True)  # H2D of this step's input from pinned memory
-                out = step(xin)
-                res_host.copy_(out[0, :8].float(), non_blocking=True)  # D2H read of the step's result
-            else:
-                out = step(x_dev)
+            step(x_dev)
             e.record()
             evs.append((s, e))
         torch.cuda.synchronize()
         return sum(s.elapsed_time(e) for s, e in evs)
 
-    def run(n_steps: int, e2e: bool) -> float:
+    # end-to-end: every step copies its input from pinned host memory and reads a result back. The copies run on a
+    # copy stream into two alternating device buffers so that the H2D of step i+1 overlaps the compute of step i
+    # (what a serving loop does); the timed span covers all copies, all compute and all read-backs of the K steps.
+    copy_stream = torch.cuda.Stream()
+    x_bufs = [torch.empty_like(x_dev), torch.empty_like(x_dev)]
+
+    def timed_e2e(n_steps: int) -> float:
+        cur = torch.cuda.current_stream()
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        copy_stream.wait_stream(cur)
+        start.record(cur)
+        copy_stream.wait_event(start)
+        for i in range(n_steps):
+            b = i & 1
+            with torch.cuda.stream(copy_stream):
+                if i >= 2:
+                    copy_stream.wait_event(consumed[b])  # buffer b is free once step i-2 has read it
+                x_bufs[b].copy_(x_host, non_blocking=True)  # H2D of this step's input
+                ready[b].record(copy_stream)
+            cur.wait_event(ready[b])
+            out = step(x_bufs[b])
+            consumed[b].record(cur)
+            res_host.copy_(out[0, :8].float(), non_blocking=True)  # D2H read of the step's result
+        stop.record(cur)
+        torch.cuda.synchronize()
+        return start.elapsed_time(stop)
+
+    def run(fn, n_steps: int) -> float:
         dist.barrier()
         torch.cuda.synchronize()
-        ms = timed(n_steps, e2e)
+        ms = fn(n_steps)
         torch.cuda.synchronize()
         dist.barrier()
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    run(args.warmup, False)
-    sampler = ClockSampler(rank == 0)
-    total_ms = run(args.steps, False)
-    clocks = sampler.stop(world)
-    run(max(args.warmup // 2, 2), True)
-    e2e_ms = run(args.steps, True)
+    sampler = ClockSampler(world, rank == 0)
+    run(timed_device, args.warmup)
+    sampler.start()
+    total_ms = run(timed_device, args.steps)
+    clocks = sampler.stop()
+    run(timed_e2e, max(args.warmup // 2, 3))
+    e2e_ms = run(timed_e2e, args.steps)
 
-    # per-op breakdown (same timing rules), untimed w.r.t. the headline
     def op_ms(fn):
         for _ in range(3):
             fn()
@@ -214,7 +285,8 @@ def main() -> None:
                    "timing": "CUDA events per step, max over ranks"},
         "clocks": clocks,
         "e2e": {"value": round(flops_step / (e2e_ms / args.steps * 1e-3) / 1e12, 2), "unit": "TFLOP/s",
-                "ms_per_step": round(e2e_ms / args.steps, 5), "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 32},
+                "ms_per_step": round(e2e_ms / args.steps, 5), "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 32,
+                "note": "H2D of step i+1 overlaps compute of step i (copy stream, two device buffers)"},
         "gpu_launches": launches_per_step * args.steps,
         "breakdown": {
             "ag_gemm_ms": round(ag_ms, 5), "ag_gemm_tflops_per_gpu": round(per_gpu_flops / ag_ms / 1e9, 1),
@@ -226,10 +298,15 @@ def main() -> None:
             "speedup_vs_torch_nccl_cublas": None if base_ms is None else round(base_ms / ms_per_step, 3),
         },
     }
-    if rank == 0:
-        print(json.dumps(out))
     ag_ctx.finalize()
     rs_ctx.finalize()
+    if args.impl == "tdist" and not args.no_decode and os.environ.get("TDIST_BENCH_DECODE", "1") != "0":
+        try:
+            out["decode"] = decode_section(rank, world, max(args.steps, 10))
+        except Exception as e:  # the headline number must survive a failure of the secondary section
+            out["decode"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    if rank == 0:
+        print(json.dumps(out))
     finalize_distributed()
 
 

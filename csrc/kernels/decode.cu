@@ -63,41 +63,51 @@ __device__ __forceinline__ float block_reduce_sum(float v, float* sh) {
 }
 
 // ------------------------------------------------------------------ GEMV / skinny linear (M <= 16)
-// y[m, n] = sum_k x[m, k] * w[n, k] (+ bias[n]). One warp per output column n,
-// lanes stream the weight row with 16-byte loads (4 in flight), x is re-read
-// through L1/L2 (it is tiny and hot). fp32 accumulate.
+// y[m, n] = sum_k x[m, k] * w[n, k] (+ bias[n]). Each warp owns TWO output columns at a time and keeps 2 x 4
+// sixteen-byte weight loads per lane in flight (4 KB per warp): with 8 warps per CTA and several CTAs per SM that is
+// enough outstanding bytes to cover HBM latency (the one-column version reached 43% of peak, see profiles/).
+// x is re-read through L1/L2 (it is tiny and hot). fp32 accumulate.
 template <typename T, int MAXM>
 __global__ void __launch_bounds__(256) gemv_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                    const T* __restrict__ bias, T* __restrict__ y, int M, int N, int K,
                                                    long long ldx, long long ldw, long long ldy) {
+  constexpr int UN = 4;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warps_per_cta = blockDim.x >> 5;
-  for (int n = blockIdx.x * warps_per_cta + warp; n < N; n += gridDim.x * warps_per_cta) {
-    float acc[MAXM];
+  const int kv = K >> 3;  // 16-byte vectors per row
+  for (int n0 = (blockIdx.x * warps_per_cta + warp) * 2; n0 < N; n0 += gridDim.x * warps_per_cta * 2) {
+    const bool two = n0 + 1 < N;
+    float acc0[MAXM], acc1[MAXM];
 #pragma unroll
-    for (int m = 0; m < MAXM; ++m) acc[m] = 0.f;
-    const T* wr = w + size_t(n) * ldw;
-    const int kv = K >> 3;  // 16-byte vectors per row
-    for (int k0 = lane; k0 < kv; k0 += 32 * 4) {
-      int4 wv[4];
+    for (int m = 0; m < MAXM; ++m) acc0[m] = acc1[m] = 0.f;
+    const T* w0 = w + size_t(n0) * ldw;
+    const T* w1 = w + size_t(two ? n0 + 1 : n0) * ldw;
+    for (int k0 = lane; k0 < kv; k0 += 32 * UN) {
+      int4 a[UN], b[UN];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < UN; ++u) {
         const int kk = k0 + u * 32;
-        wv[u] = kk < kv ? ptx::ld_nc_v4(wr + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
+        const bool ok = kk < kv;
+        a[u] = ok ? ptx::ld_nc_v4(w0 + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
+        b[u] = ok ? ptx::ld_nc_v4(w1 + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < UN; ++u) {
         const int kk = k0 + u * 32;
         if (kk >= kv) break;
-        float wf[8];
-        unpack8<T>(wv[u], wf);
+        float af[8], bf[8];
+        unpack8<T>(a[u], af);
+        unpack8<T>(b[u], bf);
 #pragma unroll
         for (int m = 0; m < MAXM; ++m) {
           if (m < M) {
             float xf[8];
             unpack8<T>(*reinterpret_cast<const int4*>(x + size_t(m) * ldx + size_t(kk) * 8), xf);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) acc[m] = fmaf(wf[i], xf[i], acc[m]);
+            for (int i = 0; i < 8; ++i) {
+              acc0[m] = fmaf(af[i], xf[i], acc0[m]);
+              acc1[m] = fmaf(bf[i], xf[i], acc1[m]);
+            }
           }
         }
       }
@@ -105,8 +115,12 @@ __global__ void __launch_bounds__(256) gemv_kernel(const T* __restrict__ x, cons
 #pragma unroll
     for (int m = 0; m < MAXM; ++m) {
       if (m < M) {
-        const float s = ptx::warp_reduce_sum(acc[m]);
-        if (lane == 0) y[size_t(m) * ldy + n] = Cvt<T>::one(s + (bias ? Cvt<T>::f(bias[n]) : 0.f));
+        const float s0 = ptx::warp_reduce_sum(acc0[m]);
+        const float s1 = ptx::warp_reduce_sum(acc1[m]);
+        if (lane == 0) {
+          y[size_t(m) * ldy + n0] = Cvt<T>::one(s0 + (bias ? Cvt<T>::f(bias[n0]) : 0.f));
+          if (two) y[size_t(m) * ldy + n0 + 1] = Cvt<T>::one(s1 + (bias ? Cvt<T>::f(bias[n0 + 1]) : 0.f));
+        }
       }
     }
   }
@@ -527,7 +541,7 @@ int tdist_gemv(int dtype, const void* x, const void* w, const void* bias, void* 
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int warps = 8;
-  int grid = (N + warps - 1) / warps;
+  int grid = (N + 2 * warps - 1) / (2 * warps);
   if (grid > 148 * 8) grid = 148 * 8;
   DISPATCH_16(dtype, {
     const T* xp = static_cast<const T*>(x);

@@ -5,7 +5,7 @@
 #include <unordered_map>
 
 #include "../runtime/driver.h"
-#include "gemm_sm100.cuh"
+#include "gemm_sm100_2cta.cuh"
 
 namespace tdist {
 
@@ -97,6 +97,83 @@ static int launch_inst(const GemmParams& p, int grid, cudaStream_t s, bool coope
   return 0;
 }
 
+template <int BN, int ST>
+static int launch_inst2(const GemmParams& p, int grid, cudaStream_t s) {
+  using L = GemmSmem2<BN, ST>;
+  static bool attr_set = false;
+  auto kern = gemm_sm100_2cta_kernel<BN, ST>;
+  if (!attr_set) {
+    TDIST_RT_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = L::kTotal;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TDIST_RT_TRY(cudaLaunchKernelEx(&cfg, kern, p));
+  return 0;
+}
+
+// CTA-pair kernel: tile widths and stage counts (per-CTA stage = 16 KB of A + BLOCK_N * 64 B of B)
+static int dispatch2(const GemmParams& p, int bn, int grid, cudaStream_t s) {
+  switch (bn) {
+    case 256: return launch_inst2<256, 6>(p, grid, s);
+    case 224: return launch_inst2<224, 6>(p, grid, s);
+    case 192: return launch_inst2<192, 7>(p, grid, s);
+    case 160: return launch_inst2<160, 7>(p, grid, s);
+    case 128: return launch_inst2<128, 8>(p, grid, s);
+    case 112: return launch_inst2<112, 8>(p, grid, s);
+    case 96: return launch_inst2<96, 8>(p, grid, s);
+    case 64: return launch_inst2<64, 8>(p, grid, s);
+  }
+  set_error("gemm (cta pair): unsupported BLOCK_N");
+  return -1;
+}
+
+// tile-width choice for the CTA-pair kernel: 256-row tiles on `pairs` CTA pairs. Narrow tiles stay efficient here
+// because each CTA only stages half of B (see gemm_sm100_2cta.cuh), so the model is dominated by wave quantisation.
+static int pick_block_n2(int ptiles_m, int N, int pairs, int forced) {
+  static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64};
+  static const double eff[] = {1.0, 0.99, 0.97, 0.95, 0.92, 0.88, 0.84, 0.70};
+  if (forced > 0)
+    for (int c : cands)
+      if (c == forced) return c;
+  double best_cost = -1;
+  int best = 256;
+  for (size_t i = 0; i < sizeof(cands) / sizeof(cands[0]); ++i) {
+    const int bn = cands[i];
+    const long tiles = long(ptiles_m) * ((N + bn - 1) / bn);
+    const long waves = (tiles + pairs - 1) / pairs;
+    const double cost = double(waves) * (bn / eff[i] + 6.0);
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
+}
+
+static int want_cta_pair(const tdist_gemm_args* a) {
+  if (a->cta_group == 1) return 0;
+  if (a->cta_group == 2) return 1;
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("TDIST_GEMM_CTA_GROUP");
+    env = e ? atoi(e) : 0;
+  }
+  if (env == 1) return 0;
+  if (env == 2) return 1;
+  return 0;  // default until the pair kernel has been validated on every shape class: single-CTA tiles
+}
+
 static double g_last_cost = 0;
 static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
   static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64, 32};
@@ -177,11 +254,21 @@ int tdist_gemm(const tdist_gemm_args* a, void* stream) {
   p.block_expert = a->block_expert;
   p.ctx.world = 1;
   const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
+  p.group_m = a->group_m > 0 ? a->group_m : 8;
+  p.num_comm_ctas = 0;
+  if (a->block_expert == nullptr && !a->transpose_out && want_cta_pair(a)) {
+    const int pairs = sms / 2;
+    const int ptiles_m = (a->M + 2 * kBlockM - 1) / (2 * kBlockM);
+    const int bn2 = pick_block_n2(ptiles_m, a->N, pairs, a->block_n);
+    const int ptiles = ptiles_m * ((a->N + bn2 - 1) / bn2);
+    if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
+    if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn2 / 2) != 0) return -1;
+    const int use_pairs = ptiles < pairs ? ptiles : pairs;
+    return dispatch2(p, bn2, 2 * use_pairs, static_cast<cudaStream_t>(stream));
+  }
   const int tiles_m = (a->M + kBlockM - 1) / kBlockM;
   const int bn = pick_block_n(tiles_m, a->N, sms, a->block_n);
   const int tiles = tiles_m * ((a->N + bn - 1) / bn);
-  p.group_m = a->group_m > 0 ? a->group_m : 8;
-  p.num_comm_ctas = 0;
   if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
   const int b_rows = a->block_expert != nullptr ? a->N * (a->num_experts > 0 ? a->num_experts : 1) : a->N;
   if (make_tmap(&p.tma_b, a->b, b_rows, a->K, a->ldb, bn) != 0) return -1;
@@ -267,6 +354,39 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
   } else {
     set_error("gemm_fused: unknown mode");
     return -1;
+  }
+  if ((f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS) && want_cta_pair(a) && p.rows_per_rank >= 2 * kBlockM) {
+    // CTA-pair kernel: 256-row tiles on cluster pairs. Push CTAs (AG) are launched in pairs as well.
+    const int ptiles_m = ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * W;
+    if (f->mode == TDIST_GEMM_AG && W > 1) {
+      if (f->num_comm_ctas < 0) {
+        // largest even push-CTA count that does not add a GEMM wave
+        long best_waves = -1;
+        comm = 12;
+        for (int c2 = 12; c2 <= 32; c2 += 4) {
+          const int prs = (sms - c2) / 2;
+          const int bnc = pick_block_n2(ptiles_m, a->N, prs, a->block_n);
+          const long tl = long(ptiles_m) * ((a->N + bnc - 1) / bnc);
+          const long cost = ((tl + prs - 1) / prs) * bnc;
+          if (best_waves < 0 || cost <= best_waves) {
+            best_waves = cost;
+            comm = c2;
+          }
+        }
+      }
+      comm = (comm + 1) / 2 * 2;
+    }
+    p.num_comm_ctas = comm;
+    const int pairs = (sms - comm) / 2;
+    if (pairs < 1) {
+      set_error("gemm_fused: no SMs left for the GEMM");
+      return -1;
+    }
+    const int bn2 = pick_block_n2(ptiles_m, a->N, pairs, a->block_n);
+    if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn2 / 2) != 0) return -1;
+    const long ptiles = long(ptiles_m) * ((a->N + bn2 - 1) / bn2);
+    const int use_pairs = (f->mode == TDIST_GEMM_RS) ? pairs : int(ptiles < pairs ? ptiles : pairs);
+    return dispatch2(p, bn2, comm + 2 * use_pairs, static_cast<cudaStream_t>(stream));
   }
   p.num_comm_ctas = comm;
   const int gemm_ctas_max = sms - comm;

@@ -109,8 +109,16 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int t, int 
     const int step = t / per_shard;
     const int r = t - step * per_shard;
     tc.shard = (p.ctx.rank + step + (p.mode == GEMM_RS ? 1 : 0)) % W;
-    tc.blk = r / tiles_n;
-    tc.n_blk = r % tiles_n;
+    // inside a shard: group_m row blocks per column sweep, so that a B tile is reused group_m times from L2
+    // (with few ranks a shard is many row blocks and B does not fit in L2)
+    const int gm = p.group_m;
+    const int per_group = gm * tiles_n;
+    const int g = r / per_group;
+    const int first_m = g * gm;
+    const int rows = min(gm, bps - first_m);
+    const int rr = r - g * per_group;
+    tc.blk = first_m + rr % rows;
+    tc.n_blk = rr / rows;
     tc.row0 = tc.shard * p.rows_per_rank + tc.blk * kBlockM;
     tc.row_end = (tc.shard + 1) * p.rows_per_rank;
   } else {

@@ -106,6 +106,7 @@ typedef struct tdist_gemm_args {
    * negative = padding block (skipped). NULL = ordinary GEMM. (allgather_group_gemm.py:534-608, moe_reduce_rs.py:166-244) */
   const int* block_expert;
   int num_experts;
+  int cta_group; /* 0 = auto, 1 = one CTA per 128-row tile, 2 = CTA pairs on 256-row tiles (tcgen05 cta_group::2) */
 } tdist_gemm_args;
 
 /* C = A * B^T (kernels/nvidia/allgather_gemm.py:656-720 gemm_persistent) */

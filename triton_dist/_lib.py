@@ -57,6 +57,7 @@ class GemmArgs(ctypes.Structure):
         ("transpose_out", ctypes.c_int),
         ("block_expert", ctypes.c_void_p),
         ("num_experts", ctypes.c_int),
+        ("cta_group", ctypes.c_int),
     ]
 
 

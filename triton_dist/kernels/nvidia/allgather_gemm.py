@@ -28,10 +28,10 @@ from .allgather import AllGatherMethod, get_auto_all_gather_method
 
 
 def _gemm_args(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, M: int, N: int, K: int, block_n: int = 0, group_m: int = 0,
-               num_sms: int = 0, transpose_out: bool = False) -> _lib.GemmArgs:
+               num_sms: int = 0, transpose_out: bool = False, cta_group: int = 0) -> _lib.GemmArgs:
     return _lib.GemmArgs(a=a.data_ptr(), b=b.data_ptr(), c=c.data_ptr(), M=M, N=N, K=K, lda=a.stride(0), ldb=b.stride(0),
                          ldc=c.stride(0), dtype=_lib.dtype_code(a.dtype), block_n=block_n, group_m=group_m, num_sms=num_sms,
-                         transpose_out=int(transpose_out))
+                         transpose_out=int(transpose_out), block_expert=None, num_experts=0, cta_group=cta_group)
 
 
 def _check_operands(a: torch.Tensor, b: torch.Tensor) -> None:
@@ -42,7 +42,7 @@ def _check_operands(a: torch.Tensor, b: torch.Tensor) -> None:
 
 
 def gemm_persistent(a: torch.Tensor, b: torch.Tensor, ctx=None, out: Optional[torch.Tensor] = None, block_n: int = 0,
-                    num_sms: int = 0, **_ignored) -> torch.Tensor:
+                    num_sms: int = 0, cta_group: int = 0, **_ignored) -> torch.Tensor:
     """C = A @ B^T on the tcgen05 engine (single GPU; reference :656-688)."""
     _check_operands(a, b)
     M, K = a.shape
@@ -56,7 +56,7 @@ def gemm_persistent(a: torch.Tensor, b: torch.Tensor, ctx=None, out: Optional[to
     if M <= 64 and N >= 128 and M % 8 == 0:
         args = _gemm_args(b, a, out, N, M, K, block_n=block_n, num_sms=num_sms, transpose_out=True)
     else:
-        args = _gemm_args(a, b, out, M, N, K, block_n=block_n, num_sms=num_sms)
+        args = _gemm_args(a, b, out, M, N, K, block_n=block_n, num_sms=num_sms, cta_group=cta_group)
     _lib.check(_lib.lib().tdist_gemm(ctypes.byref(args), _lib.stream_ptr()), "gemm")
     return out
 
@@ -80,7 +80,8 @@ class AllGatherGEMMTensorParallelContext:
     BLOCK_K: int = 64
     GROUP_SIZE_M: int = 8
     stages: int = 4
-    num_comm_sms: int = -1  # CTAs that push the local shard to the peers (-1 = default 16)
+    num_comm_sms: int = -1  # CTAs that push the local shard to the peers (-1 = chosen so that no GEMM wave is added)
+    cta_group: int = 0  # 0 auto, 1 single-CTA tiles, 2 CTA pairs
     all_gather_method: AllGatherMethod = AllGatherMethod.Auto
     for_correctness: bool = False
     ag_intranode_stream: Optional["torch.cuda.Stream"] = None
@@ -160,7 +161,7 @@ def ag_gemm(a: torch.Tensor, b: torch.Tensor, ctx: AllGatherGEMMTensorParallelCo
     if ctx.for_correctness:  # shake out ordering bugs: random skew between ranks
         torch.cuda._sleep(int(torch.randint(0, 2_000_000, (1,)).item()))
     heap = _symm.get_heap()
-    args = _gemm_args(a, b, out, M, N, K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_SIZE_M)
+    args = _gemm_args(a, b, out, M, N, K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_SIZE_M, cta_group=ctx.cta_group)
     st = ctx.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=1, ws=ctx.symm_workspace.data_ptr(), out=None, flags=st.flags_ptr, flags2=None,
                        counters=None, phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=ctx.num_comm_sms, ar_one_shot=0,

@@ -38,7 +38,9 @@ class MoEAllGatherGroupGEMMTensorParallelContext:
         heap = _symm.get_heap()
         self.native = isinstance(heap, _symm.SymmetricHeap)
         self.symm_ag = heap.alloc((self.num_ranks, self.max_ntokens // self.num_ranks, self.hidden), self.dtype, zero=False)
-        self.symm_ids = heap.alloc((self.num_ranks, self.max_ntokens // self.num_ranks, self.topk), torch.int32, zero=False)
+        # per-rank id slot padded to a multiple of 16 bytes (the all-gather moves 16-byte vectors)
+        self.ids_per_rank = (self.max_ntokens // self.num_ranks * self.topk + 3) // 4 * 4
+        self.symm_ids = heap.alloc((self.num_ranks, self.ids_per_rank), torch.int32, zero=True)
         self.ag_ctx = _ag.create_fast_allgather_context(self.rank, 0, self.num_ranks, 1,
                                                         max_buffer_size=max(4 * self.symm_ag.numel() * self.symm_ag.element_size(), 1 << 20))
 
@@ -65,13 +67,13 @@ def ag_group_gemm(x: torch.Tensor, w: torch.Tensor, topk_ids: torch.Tensor, ctx:
     m_loc = x.shape[0]
     assert m_loc * W <= ctx.max_ntokens and m_loc == ctx.max_ntokens // W, "token count must match the context (max_ntokens / W per rank)"
     ctx.symm_ag[r].copy_(x)
-    ctx.symm_ids[r].copy_(topk_ids.to(torch.int32))
+    ctx.symm_ids[r, :m_loc * ctx.topk].copy_(topk_ids.to(torch.int32).reshape(-1))
     if W > 1:
         mode = "push_multimem" if x.is_cuda else "pull"
         _ag.fast_allgather(ctx.symm_ag, ctx.ag_ctx, mode=mode)
         _ag.fast_allgather(ctx.symm_ids, ctx.ag_ctx, mode=mode)
     full_x = ctx.symm_ag.view(W * m_loc, -1)
-    full_ids = ctx.symm_ids.view(W * m_loc, -1)
+    full_ids = ctx.symm_ids[:, :m_loc * ctx.topk].reshape(W * m_loc, ctx.topk)
     sort = moe_align_sort(full_ids, ctx.num_experts)
     a_sorted = moe_gather_rows(full_x, sort)
     y = grouped_gemm(a_sorted, w, sort)

@@ -122,6 +122,6 @@ def grouped_gemm(a_sorted: torch.Tensor, w: torch.Tensor, sort: MoESortResult, o
     assert a_sorted.is_contiguous() and w.is_contiguous()
     args = _lib.GemmArgs(a=a_sorted.data_ptr(), b=w.data_ptr(), c=out.data_ptr(), M=sort.max_rows, N=N, K=K, lda=K, ldb=K, ldc=N,
                          dtype=_lib.dtype_code(a_sorted.dtype), block_n=0, group_m=1, num_sms=0, transpose_out=0,
-                         block_expert=sort.block_expert.data_ptr(), num_experts=E)
+                         block_expert=sort.block_expert.data_ptr(), num_experts=E, cta_group=1)
     _lib.check(_lib.lib().tdist_gemm(ctypes.byref(args), _lib.stream_ptr()), "grouped_gemm")
     return out

@@ -125,6 +125,14 @@ def decode_section(rank: int, world: int, steps: int):
            "weight_bytes_per_token_per_rank": wbytes, "hbm_floor_ms_of_" + pk["source"]: round(floor, 4),
            "fraction_of_hbm_floor": round(floor / ms, 3), "launches_per_token": 1, "graph": info,
            "reference_published_ms_8xH800": 7.41 if world == 8 else None}
+    try:  # per-op-type timeline of one token (in-kernel task stamps), outside the timed region
+        builder.enable_profiling(True)
+        step()
+        torch.cuda.synchronize()
+        out["task_profile"] = builder.profile_summary()
+        builder.enable_profiling(False)
+    except Exception as e:  # noqa: BLE001
+        out["task_profile"] = f"unavailable: {e}"
     mega.finalize()
     del dense
     torch.cuda.empty_cache()

@@ -142,7 +142,9 @@ static int dispatch2(const GemmParams& p, int bn, int grid, cudaStream_t s) {
 // because each CTA only stages half of B (see gemm_sm100_2cta.cuh), so the model is dominated by wave quantisation.
 static int pick_block_n2(int ptiles_m, int N, int pairs, int forced) {
   static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64};
-  static const double eff[] = {1.0, 0.99, 0.97, 0.95, 0.92, 0.88, 0.84, 0.70};
+  // relative mainloop efficiency measured on B200 (M=8192 N=14336 K=4096, profiles/README.md): like the single-CTA
+  // kernel, narrow tiles re-read the A operand from shared memory more often per FLOP
+  static const double eff[] = {1.0, 0.78, 0.68, 0.56, 0.44, 0.42, 0.36, 0.25};
   if (forced > 0)
     for (int c : cands)
       if (c == forced) return c;
@@ -171,7 +173,10 @@ static int want_cta_pair(const tdist_gemm_args* a) {
   }
   if (env == 1) return 0;
   if (env == 2) return 1;
-  return 0;  // default until the pair kernel has been validated on every shape class: single-CTA tiles
+  // default: 256-row pair tiles (each CTA stages half of B, 6 pipeline stages instead of 4: cuBLAS-level throughput)
+  // whenever a full pair tile of rows exists; callers still fall back to single-CTA tiles for grouped / transposed /
+  // all-reduce GEMMs
+  return a->M >= 2 * kBlockM;
 }
 
 static double g_last_cost = 0;
@@ -296,6 +301,15 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
   const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
   int comm = f->num_comm_ctas;
   int tiles_m;
+  if (W == 1 && (f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS)) {
+    // a single rank has nothing to gather or scatter: run the plain GEMM straight from / into the caller's tensors
+    tdist_gemm_args g = *a;
+    if (f->mode == TDIST_GEMM_RS) {
+      g.c = f->out;
+      g.ldc = a->N;
+    }
+    return tdist_gemm(&g, stream);
+  }
   if (f->mode == TDIST_GEMM_AG) {
     // a->a = own shard [M/W, K]; f->ws = symmetric workspace [2][M][K]; a->M = full M
     if (a->M % W != 0) {

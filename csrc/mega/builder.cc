@@ -35,17 +35,24 @@ struct Builder {
   uint32_t* d_scoreboard = nullptr;
   uint32_t* d_step = nullptr;
   KernelParams params;
-  int max_tasks = 0, total_tasks = 0, smem_bytes = 0;
+  int max_tasks = 0, total_tasks = 0, smem_bytes = 0, ring_offset = 0, ring_stages = 0;
+  uint64_t* d_trace = nullptr;
+  StreamEntry* d_streams = nullptr;
+  void* d_tmaps = nullptr;
+  int* d_stream_len = nullptr;
+  int max_streams = 1;
 };
 
 static int tiles_of(const OpArgs& a, int type, int num_ctas, int* cols_per_tile) {
   *cols_per_tile = 0;
   switch (type) {
     case OP_LINEAR: {
-      // columns per tile: enough tiles to cover every CTA ~2x when the matrix is big, never less than 16 columns
-      // (one per warp) so that each warp streams whole rows
-      int cpt = (a.N + 2 * num_ctas - 1) / (2 * num_ctas);
-      cpt = std::max(16, (cpt + 15) / 16 * 16);
+      // The kernel spreads a tile's weights evenly over all threads whatever its shape, so the only thing that
+      // matters is that every CTA gets the same number of bytes: one tile per CTA per wave, at most 256 columns per
+      // tile (bounds the per-tile column-sum array), at least 4 columns (one 16 KB chunk is ~1-4 rows).
+      const int waves = std::max(1, (a.N + num_ctas * 256 - 1) / (num_ctas * 256));
+      int tiles = std::min(waves * num_ctas, std::max(1, a.N / 4));
+      int cpt = (a.N + tiles - 1) / tiles;
       *cols_per_tile = cpt;
       return (a.N + cpt - 1) / cpt;
     }
@@ -66,10 +73,16 @@ static int tiles_of(const OpArgs& a, int type, int num_ctas, int* cols_per_tile)
 
 static int smem_of(const OpArgs& a, int type) {
   switch (type) {
-    case OP_LINEAR: return a.M * a.K * 2 + 256;
+    case OP_LINEAR: {
+      // activations [M][kboxes * kbox + 8] bf16, norm weight [K] bf16 when fused, block sums [2][nblk][256] fp32,
+      // cross-warp partials [2][16 warps][128] fp32, block_sum scratch
+      const LinearGeom ge = linear_geom(a.cols_per_tile, a.K);
+      const int xpitch = ge.kboxes * ge.kbox + 8;
+      return a.M * xpitch * 2 + (a.in2 != nullptr ? a.K * 2 : 0) + 2 * ge.nblk * 256 * 4 + 2 * (kThreads / 32) * 128 * 4 + 256;
+    }
     case OP_RMS_NORM: return a.K * 4 + 256;
     case OP_ATTN_SPLIT: {
-      const int g = std::min(8, a.i0 / std::max(a.i1, 1));
+      const int g = std::min(4, a.i0 / std::max(a.i1, 1));  // the kernel runs at most 4 heads per pass
       return (kThreads / 16) * g * (2 + 128) * 4;
     }
     case OP_ARGMAX: return 1024;
@@ -120,8 +133,8 @@ int tdist_mega_add_op(void* h, int type, const tdist_mega_op* d, int dep0, int d
   a.i0 = d->i[0]; a.i1 = d->i[1]; a.i2 = d->i[2]; a.i3 = d->i[3]; a.i4 = d->i[4]; a.i5 = d->i[5];
   a.l0 = d->l[0]; a.l1 = d->l[1]; a.l2 = d->l[2];
   a.f0 = d->f[0]; a.f1 = d->f[1];
-  if (type == OP_LINEAR && (a.M < 1 || a.M > 8 || a.K % 8 != 0)) {
-    set_error("mega linear: need 1 <= M <= 8 rows and K % 8 == 0");
+  if (type == OP_LINEAR && (a.M < 1 || a.M > 8 || a.K % 16 != 0)) {
+    set_error("mega linear: need 1 <= M <= 8 rows and K % 16 == 0");
     return -1;
   }
   if (type == OP_ALLREDUCE || type == OP_BARRIER) a.i0 = b->num_ar_ops++;
@@ -167,11 +180,78 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
       ++cursor;
     }
   }
-  if (smem > 200 * 1024) {
-    set_error("mega: an op needs more than 200 KB of shared memory (batch * K too large)");
+  // static weight-stream table: one entry per linear task of every CTA, in queue order (see mega.h StreamEntry), and
+  // one TMA descriptor per linear op
+  std::vector<int> tmap_of(n_ops, -1);
+  std::vector<CUtensorMap> tmaps;
+  {
+    const DriverApi& d = driver();
+    for (int o = 0; o < n_ops; ++o) {
+      if (b->types[o] != OP_LINEAR) continue;
+      const OpArgs& a = b->ops[o];
+      if (!d.ok) {
+        set_error("CUDA driver not available: " + d.err);
+        return -1;
+      }
+      const LinearGeom ge = linear_geom(a.cols_per_tile, a.K);
+      const uint64_t rows = (a.i0 & 1) ? uint64_t(a.N) * 2 : uint64_t(a.N);
+      cuuint64_t dims[2] = {cuuint64_t(a.K), rows};
+      cuuint64_t strides[1] = {cuuint64_t(a.K) * 2};
+      cuuint32_t box[2] = {64u, cuuint32_t(ge.R)};
+      cuuint32_t estr[2] = {1, 1};
+      CUtensorMap tm;
+      CUresult rc = d.cuTensorMapEncodeTiled(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(a.in1), dims, strides,
+                                             box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (rc != CUDA_SUCCESS) {
+        set_error("mega: cuTensorMapEncodeTiled failed for a linear weight (needs a 16-byte aligned [N, K] bf16 matrix): " +
+                  cu_err(rc));
+        return -1;
+      }
+      tmap_of[o] = int(tmaps.size());
+      tmaps.push_back(tm);
+    }
+  }
+  if (!tmaps.empty()) {
+    TDIST_RT_TRY(cudaMalloc(&b->d_tmaps, tmaps.size() * sizeof(CUtensorMap)));
+    TDIST_RT_TRY(cudaMemcpy(b->d_tmaps, tmaps.data(), tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+  }
+  std::vector<std::vector<StreamEntry>> streams(b->num_ctas);
+  int max_streams = 1;
+  for (int c = 0; c < b->num_ctas; ++c) {
+    uint32_t first = 0;
+    for (const Task& k : queues[c]) {
+      if (k.type != OP_LINEAR) continue;
+      const OpArgs& a = b->ops[k.op];
+      const LinearGeom ge = linear_geom(a.cols_per_tile, a.K);
+      StreamEntry e;
+      memset(&e, 0, sizeof(e));
+      e.tmap = static_cast<const CUtensorMap*>(b->d_tmaps) + tmap_of[k.op];
+      e.row0 = uint32_t(k.tile) * uint32_t(a.cols_per_tile);
+      e.pair_rows = (a.i0 & 1) ? uint32_t(a.N) : 0u;
+      e.R = uint8_t(ge.R);
+      e.nblk = uint8_t(ge.nblk);
+      e.kbox = uint16_t(ge.kbox);
+      e.kboxes = uint32_t(ge.kboxes);
+      e.total = ((a.i0 & 1) ? 2u : 1u) * uint32_t(ge.nblk) * uint32_t(ge.kboxes);
+      e.first = first;
+      first += e.total;
+      streams[c].push_back(e);
+    }
+    max_streams = std::max(max_streams, int(streams[c].size()));
+  }
+  // dynamic shared memory = [per-task scratch, max over ops][weight ring][ring barriers][2 task slots][stream table]
+  const int aux_bytes = 256 + 2 * 192 + max_streams * int(sizeof(StreamEntry));
+  const int ring_offset = (smem + 1023) / 1024 * 1024;  // 1024 B: the 128 B TMA swizzle is a function of the address
+  int stages = (kSmemLimit - 2048 - ring_offset - aux_bytes) / kStageBytes;  // 2 KB: static shared memory of the task bodies
+  stages = std::min(stages, kMaxRingStages);
+  if (stages < 2) {
+    set_error("mega: an op needs too much shared memory to leave room for the weight ring (batch * K too large)");
     return -1;
   }
-  b->smem_bytes = smem;
+  b->ring_offset = ring_offset;
+  b->ring_stages = stages;
+  b->smem_bytes = ring_offset + stages * kStageBytes + aux_bytes;
   b->total_tasks = cursor;
   b->max_tasks = 1;
   for (auto& q : queues) b->max_tasks = std::max(b->max_tasks, int(q.size()));
@@ -182,6 +262,18 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
     lens[c] = int(queues[c].size());
     std::copy(queues[c].begin(), queues[c].end(), flat.begin() + size_t(c) * b->max_tasks);
   }
+  std::vector<StreamEntry> sflat(size_t(b->num_ctas) * max_streams);
+  std::vector<int> slens(b->num_ctas);
+  memset(static_cast<void*>(sflat.data()), 0, sflat.size() * sizeof(StreamEntry));
+  for (int c = 0; c < b->num_ctas; ++c) {
+    slens[c] = int(streams[c].size());
+    std::copy(streams[c].begin(), streams[c].end(), sflat.begin() + size_t(c) * max_streams);
+  }
+  TDIST_RT_TRY(cudaMalloc(&b->d_streams, sflat.size() * sizeof(StreamEntry)));
+  TDIST_RT_TRY(cudaMalloc(&b->d_stream_len, slens.size() * sizeof(int)));
+  TDIST_RT_TRY(cudaMemcpy(b->d_streams, sflat.data(), sflat.size() * sizeof(StreamEntry), cudaMemcpyHostToDevice));
+  TDIST_RT_TRY(cudaMemcpy(b->d_stream_len, slens.data(), slens.size() * sizeof(int), cudaMemcpyHostToDevice));
+  b->max_streams = max_streams;
   TDIST_RT_TRY(cudaMalloc(&b->d_queues, flat.size() * sizeof(Task)));
   TDIST_RT_TRY(cudaMalloc(&b->d_queue_len, lens.size() * sizeof(int)));
   TDIST_RT_TRY(cudaMalloc(&b->d_ops, b->ops.size() * sizeof(OpArgs)));
@@ -200,6 +292,12 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
   b->params.step_state = b->d_step;
   b->params.ar_flags = ar_flags;
   b->params.max_tasks = b->max_tasks;
+  b->params.ring_offset = b->ring_offset;
+  b->params.ring_stages = b->ring_stages;
+  b->params.trace = nullptr;
+  b->params.streams = b->d_streams;
+  b->params.stream_len = b->d_stream_len;
+  b->params.max_streams = b->max_streams;
   if (ctx != nullptr) {
     for (int i = 0; i < TDIST_MAX_RANKS; ++i) b->params.ctx.base[i] = ctx->base[i];
     b->params.ctx.mc_base = ctx->mc_base;
@@ -233,6 +331,40 @@ int tdist_mega_info(void* h, int* out6) {
   return 0;
 }
 
+// Per-task timeline (the counterpart of the reference's intra-kernel profiler): when enabled, thread 0 of every CTA
+// stamps %globaltimer at the start and end of each task of the NEXT launches. get_trace copies the stamps of the last
+// launch to the host as [num_ctas][max_tasks][6] nanosecond values: begin, end, and for linear tasks dependencies
+// satisfied / activations staged / weight stream consumed (0 = not stamped).
+int tdist_mega_set_trace(void* h, int enable) {
+  Builder* b = static_cast<Builder*>(h);
+  if (!b->compiled) {
+    set_error("mega: compile() first");
+    return -1;
+  }
+  if (enable && b->d_trace == nullptr) {
+    const size_t bytes = size_t(b->num_ctas) * b->max_tasks * kTraceWords * sizeof(uint64_t);
+    TDIST_RT_TRY(cudaMalloc(&b->d_trace, bytes));
+    TDIST_RT_TRY(cudaMemset(b->d_trace, 0, bytes));
+  }
+  b->params.trace = enable ? b->d_trace : nullptr;
+  return 0;
+}
+
+int tdist_mega_get_trace(void* h, unsigned long long* out, size_t cap_words) {
+  Builder* b = static_cast<Builder*>(h);
+  if (!b->compiled || b->d_trace == nullptr) {
+    set_error("mega: tracing was not enabled");
+    return -1;
+  }
+  const size_t words = size_t(b->num_ctas) * b->max_tasks * kTraceWords;
+  if (cap_words < words) {
+    set_error("mega: trace buffer too small");
+    return -1;
+  }
+  TDIST_RT_TRY(cudaMemcpy(out, b->d_trace, words * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 // tiles of op `idx` (after add_op) — lets the Python side size the symmetric flag area and check schedules
 int tdist_mega_op_tiles(void* h, int idx) {
   Builder* b = static_cast<Builder*>(h);
@@ -263,6 +395,10 @@ int tdist_mega_destroy(void* h) {
     cudaFree(b->d_ops);
     cudaFree(b->d_scoreboard);
     cudaFree(b->d_step);
+    if (b->d_trace) cudaFree(b->d_trace);
+    cudaFree(b->d_streams);
+    if (b->d_tmaps) cudaFree(b->d_tmaps);
+    cudaFree(b->d_stream_len);
   }
   delete b;
   return 0;

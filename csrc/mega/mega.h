@@ -46,6 +46,7 @@ struct OpArgs {
   float f0, f1;                // eps, scale
   int tiles;                   // number of tiles of this op
   int cols_per_tile;           // LINEAR: output columns per tile
+  int pad_[2];                 // sizeof == 160 (copied to shared memory as 10 x int4)
 };
 
 // Fixed-size task record (the reference's INT_PER_TASK words, core/scheduler.py:40-62).
@@ -60,6 +61,37 @@ struct Task {
   int out_slot;  // scoreboard slot this task increments when done
 };
 
+// Geometry of the weight stream of one LINEAR tile (identical on host and device): the tile's cols_per_tile rows of
+// W are cut into nblk row blocks of R <= 32 rows, K into kboxes boxes of kbox <= 256 elements; one stage = one box.
+struct LinearGeom {
+  int nblk, R, kbox, kboxes;
+};
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline LinearGeom linear_geom(int cols_per_tile, int K) {
+  LinearGeom g;
+  g.nblk = (cols_per_tile + 31) / 32;
+  g.R = (cols_per_tile + g.nblk - 1) / g.nblk;
+  g.kbox = 256;  // always whole boxes: the TMA zero-fills beyond K and the staged activations are zero padded
+  g.kboxes = (K + g.kbox - 1) / g.kbox;
+  return g;
+}
+
+// One entry per LINEAR task of a CTA's queue, in queue order. Stages are numbered consecutively over all linear
+// tasks of the CTA, per task in the order (blob, row block, k box).
+struct StreamEntry {
+  const void* tmap;     // device copy of the op's CUtensorMap: W as [rows, K] bf16, box {64, R}, 128 B swizzle
+  uint32_t row0;        // first row of the tile (c_beg)
+  uint32_t pair_rows;   // silu pairing: row offset of the "up" half (N), else 0
+  uint8_t R, nblk;      // R <= 32, nblk <= 8
+  uint16_t kbox;
+  uint32_t kboxes;
+  uint32_t first;       // id of the task's first stage
+  uint32_t total;       // stages of the task = blobs * nblk * kboxes
+};
+static_assert(sizeof(StreamEntry) == 32, "StreamEntry is copied as 2 x int4");
+
 struct KernelParams {
   const Task* queues;      // [num_ctas][max_tasks]
   const int* queue_len;    // [num_ctas]
@@ -69,10 +101,22 @@ struct KernelParams {
   uint32_t* ar_flags;      // symmetric: cross-rank flags [num_ar_ops * kMaxArTiles][TDIST_MAX_RANKS] + barrier rows
   SymmCtx ctx;
   int max_tasks;
+  int ring_offset;         // byte offset of the weight ring in dynamic shared memory (behind every op's scratch area)
+  int ring_stages;         // chunks in the ring
+  const StreamEntry* streams;  // [num_ctas][max_streams]
+  const int* stream_len;       // [num_ctas]
+  int max_streams;
+  uint64_t* trace;         // optional [num_ctas][max_tasks][kTraceWords] globaltimer stamps per task (nullptr = off)
 };
 
 constexpr int kThreads = 512;
 constexpr int kMaxArTiles = 32;
+constexpr int kTraceWords = 6;         // per task: begin, end, [linear: deps satisfied, activations staged, stream consumed], spare
+constexpr int kStageBytes = 32 * 256 * 2;          // ring slot: up to 32 rows x 256 k-elements (one 2-D TMA box)
+constexpr int kMaxRingStages = 12;
+constexpr int kPrefetchStages = 0;     // L2 prefetch distance beyond the ring (stages); 0 = off (measured: no gain)
+constexpr int kSubBoxes = 4;           // TMA boxes of 64 k-elements per 256-element stage
+constexpr int kSmemLimit = 232448;     // 227 KB opt-in limit per CTA on sm_100
 
 }  // namespace mega
 }  // namespace tdist

@@ -58,46 +58,164 @@ __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t
   }
 }
 
-// ------------------------------------------------------------------ LINEAR (GEMV, M <= 8)
+// ------------------------------------------------------------------ LINEAR (skinny GEMM, M <= 8 rows)
 // i0 bit0: silu pairing (W = [2I, K], out = silu(gate) * up, N = I); i1: ldy; i2: out parity stride (bytes, 0 = none)
-template <int MAXM>
-__device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* smem, uint32_t step, const uint32_t* sb,
-                                            const Task& t, uint32_t dep_target0, uint32_t dep_target1) {
-  constexpr int UN = 8;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nwarps = kThreads >> 5;
-  const int K = a.K, kv = K >> 3;
-  const bool pair = (a.i0 & 1) != 0;
-  const bf16* W = static_cast<const bf16*>(a.in1);
-  const int c_beg = tile * a.cols_per_tile, c_end = min(c_beg + a.cols_per_tile, a.N);
-  bf16* xs = reinterpret_cast<bf16*>(smem);            // [M][K] normalised activations
-  float* scratch = reinterpret_cast<float*>(smem + size_t(a.M) * K * 2);
+//
+// Decode linears are weight-streaming: every weight byte is used once, so the job is to keep HBM busy with as few
+// instructions and as few copy requests per byte as possible. The weights of a tile (cols_per_tile consecutive rows
+// of W[N, K]) are cut into row blocks of R <= 32 rows and every block into STAGES of R rows x 256 k-elements
+// (<= 16 KB). One stage is four 2-D TMA requests (cp.async.bulk.tensor, box {64, R} of a per-op tensor map, 128 B
+// swizzle so that ldmatrix is bank-conflict free) into a ring in shared memory, completed on one mbarrier. Stages
+// are consumed with mma.sync.m16n8k16
+// (bf16 x bf16 -> fp32): the weight rows are the M dimension of the MMA, the batch (<= 8 activation rows) is its N
+// dimension, so one ldmatrix + one MMA retire 512 B of weights and a batch of 8 costs the same as a batch of 1. The
+// 16 warps split the stage as (2 row groups) x (16 k-slices); each keeps one fp32 accumulator tile for the current
+// row block and the partials are summed through shared memory once per block (one __syncthreads per block).
+// (An unswizzled {256, R} box was measured first: its 8-way conflicted ldmatrix cost ~1000 shared-memory wavefronts
+// per stage, as long as the HBM time of the stage.)
+//
+// Producer: the stages of ALL linear tasks of this CTA form one sequence numbered from 0 (static table built by the
+// host, mega.h StreamEntry, copied to shared memory at kernel start); stage s is issued by lane 0 of warp (s mod 16)
+// as soon as that warp has itself consumed stage s - ring_stages and every warp has released the slot. Weights
+// never depend on activations, so the stream simply runs ahead: the first ring-full of the NEXT linear task is in
+// flight while the current task drains, while small tasks (attention, norms) execute and while the scoreboard wait
+// spins.
+struct RingView {
+  uint8_t* buf;     // stages * kStageBytes
+  uint64_t* full;   // [stages] : 1 arrival (+ tx bytes)
+  uint64_t* empty;  // [stages] : one arrival per warp
+  int stages;
+};
 
-  // (1) first batch of weight loads for this warp's first column: issued before the dependency wait
-  int4 wpre[UN];
-  const int c_first = c_beg + warp;
-  if (c_first < c_end) {
-    const bf16* wr = W + size_t(c_first) * K;
+struct Issuer {           // warp-uniform
+  uint32_t next_own;      // next stage id this warp is responsible for
+  uint32_t e_idx;         // stream-table entry containing next_own
+  uint32_t e_first, e_total;
+  // second cursor kPrefetchStages further ahead: L2 prefetch of the same boxes. Loaded HBM latency on B200 is several
+  // microseconds, so full bandwidth needs ~200 KB per SM in flight - more than the ring can hold; the prefetches keep
+  // that many bytes in flight towards L2 and the ring loads then hit L2.
+  uint32_t pf_own, pf_idx, pf_first, pf_total;
+};
+
+__device__ __forceinline__ void stage_coords(const StreamEntry& e, uint32_t stage, int& c0, int& c1) {
+  uint32_t q = stage - e.first;
+  const uint32_t per_blob = uint32_t(e.nblk) * e.kboxes;
+  const bool second = q >= per_blob;
+  if (second) q -= per_blob;
+  const uint32_t blk = q / e.kboxes, kb = q - blk * e.kboxes;
+  c0 = int(kb * e.kbox);
+  c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);
+}
+
+// Warp-collective, called from converged code. Never blocks: a slot still being read is retried on the next call.
+__device__ __forceinline__ void try_issue(Issuer& is, const RingView& r, const StreamEntry* tab, uint32_t n_ent,
+                                          uint32_t cons) {
+  const int lane = threadIdx.x & 31;
+  while (kPrefetchStages > 0 && is.pf_own < cons + uint32_t(r.stages) + kPrefetchStages) {
+    while (is.pf_idx < n_ent && is.pf_own >= is.pf_first + is.pf_total) {
+      ++is.pf_idx;
+      if (is.pf_idx < n_ent) {
+        is.pf_first = tab[is.pf_idx].first;
+        is.pf_total = tab[is.pf_idx].total;
+      }
+    }
+    if (is.pf_idx >= n_ent) {
+      is.pf_own = 0xfffffff0u;
+      break;
+    }
+    if (lane == 0) {
+      const StreamEntry e = tab[is.pf_idx];
+      int c0, c1;
+      stage_coords(e, is.pf_own, c0, c1);
 #pragma unroll
-    for (int u = 0; u < UN; ++u) {
-      const int kk = lane + u * 32;
-      wpre[u] = kk < kv ? ptx::ld_nc_v4(wr + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
+      for (int j = 0; j < kSubBoxes; ++j) ptx::tma_prefetch_2d(e.tmap, c0 + 64 * j, c1);
+    }
+    is.pf_own += kThreads / 32;
+  }
+  if (is.next_own >= cons + uint32_t(r.stages)) return;  // ring distance (also the cheap common early-out)
+  while (is.e_idx < n_ent && is.next_own >= is.e_first + is.e_total) {
+    ++is.e_idx;
+    if (is.e_idx < n_ent) {
+      is.e_first = tab[is.e_idx].first;
+      is.e_total = tab[is.e_idx].total;
     }
   }
-  // (2) dependencies
+  if (is.e_idx >= n_ent) {
+    is.next_own = 0xfffffff0u;  // nothing left to issue, ever
+    return;
+  }
+  const uint32_t S = uint32_t(r.stages);
+  const uint32_t round = is.next_own / S, slot = is.next_own - round * S;
+  uint32_t free_ = lane == 0 ? uint32_t(ptx::mbar_test_wait(&r.empty[slot], (round & 1u) ^ 1u)) : 0u;
+  free_ = __shfl_sync(0xffffffffu, free_, 0);
+  if (!free_) return;
+  if (lane == 0) {
+    const StreamEntry e = tab[is.e_idx];
+    int c0, c1;
+    stage_coords(e, is.next_own, c0, c1);
+    // one stage = kSubBoxes TMA boxes of {64 k-elements (one 128 B swizzle row), R rows}, 1024 B-aligned one after another
+    ptx::mbar_arrive_expect_tx(&r.full[slot], uint32_t(e.R) * 128u * kSubBoxes);
+    const uint32_t sub_pitch = ((uint32_t(e.R) + 7u) & ~7u) * 128u;
+#pragma unroll
+    for (int j = 0; j < kSubBoxes; ++j)
+      ptx::tma_load_2d(r.buf + size_t(slot) * kStageBytes + j * sub_pitch, e.tmap, &r.full[slot], c0 + 64 * j, c1);
+  }
+  is.next_own += kThreads / 32;
+}
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&a)[4], const void* smem_ptr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3])
+               : "r"(ptx::smem_u32(smem_ptr)));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* smem, uint32_t step, const uint32_t* sb,
+                                            const Task& t, uint32_t dep_target0, uint32_t dep_target1, const RingView& r,
+                                            Issuer& is, uint32_t& cons, uint32_t& slot, uint32_t& par,
+                                            const StreamEntry* tab, uint32_t n_ent, uint64_t* tr) {
+  constexpr int kWarps = kThreads / 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int K = a.K, kv = K >> 3, M = a.M, cpt = a.cols_per_tile;
+  const bool pair = (a.i0 & 1) != 0;
+  const int c_beg = tile * cpt, c_end = min(c_beg + cpt, a.N);
+  const int ncols = c_end - c_beg;
+  const LinearGeom ge = linear_geom(cpt, K);                                  // same split as the host (StreamEntry)
+  const int xpitch = ge.kboxes * ge.kbox + 8;                                 // elements: zero padded to whole k boxes, +16 B
+  bf16* xs = reinterpret_cast<bf16*>(smem);                                  // [M][xpitch] (normalised) activations
+  const bf16* nw = static_cast<const bf16*>(a.in2);
+  bf16* nws = xs + size_t(M) * xpitch;                                        // [K] norm weight (only when fused)
+  float* acc = reinterpret_cast<float*>(nws + (nw != nullptr ? K : 0));       // [2][nblk][2][16][8] block sums
+  float* red = acc + 2 * size_t(ge.nblk) * 256;                               // [2][kWarps][16][8] partials
+  float* scratch = red + 2 * kWarps * 128;                                    // 32 floats for block_sum
+
+  // (1) this task's first stages are normally in flight already (see try_issue). Everything that does not depend on
+  // the producer op is done before the scoreboard wait: norm weight into shared memory, zero padding of x.
+  if (nw != nullptr)
+    for (int i = threadIdx.x; i < kv; i += kThreads)
+      *reinterpret_cast<int4*>(nws + size_t(i) * 8) = ptx::ld_nc_v4(nw + size_t(i) * 8);
+  for (int m = 0; m < M; ++m)
+    for (int i = K + threadIdx.x; i < xpitch; i += kThreads) xs[size_t(m) * xpitch + i] = __float2bfloat16(0.f);
+  // (2) wait for the activations
   if (threadIdx.x == 0) {
     wait_slot(sb, t.dep0, dep_target0);
     wait_slot(sb, t.dep1, dep_target1);
+    if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
   }
   __syncthreads();
   // (3) stage x (optionally RMS-normalised) in shared memory
   const bf16* x = static_cast<const bf16*>(a.in0);
-  const bf16* nw = static_cast<const bf16*>(a.in2);
-  for (int m = 0; m < a.M; ++m) {
+  const float eps = a.f0;
+  for (int m = 0; m < M; ++m) {
     float ss = 0.f;
     for (int i = threadIdx.x; i < kv; i += kThreads) {
       const int4 raw = ptx::ld_v4(x + size_t(m) * K + size_t(i) * 8);
-      *reinterpret_cast<int4*>(xs + size_t(m) * K + size_t(i) * 8) = raw;
+      *reinterpret_cast<int4*>(xs + size_t(m) * xpitch + size_t(i) * 8) = raw;
       if (nw != nullptr) {
         float f[8];
         unpack8(raw, f);
@@ -107,79 +225,107 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
     }
     if (nw != nullptr) {
       const float tot = block_sum(ss, scratch);
-      const float inv = rsqrtf(tot / K + a.f0);
+      const float inv = rsqrtf(tot / K + eps);
       for (int i = threadIdx.x; i < kv; i += kThreads) {
         float f[8], w[8];
-        unpack8(*reinterpret_cast<const int4*>(xs + size_t(m) * K + size_t(i) * 8), f);
-        unpack8(ptx::ld_nc_v4(nw + size_t(i) * 8), w);
+        unpack8(*reinterpret_cast<const int4*>(xs + size_t(m) * xpitch + size_t(i) * 8), f);
+        unpack8(*reinterpret_cast<const int4*>(nws + size_t(i) * 8), w);
 #pragma unroll
         for (int j = 0; j < 8; ++j) f[j] = __bfloat162float(__float2bfloat16(f[j] * inv)) * w[j];  // round like the unfused norm
-        *reinterpret_cast<int4*>(xs + size_t(m) * K + size_t(i) * 8) = pack8(f);
+        *reinterpret_cast<int4*>(xs + size_t(m) * xpitch + size_t(i) * 8) = pack8(f);
       }
     }
   }
   __syncthreads();
-  // (4) stream the weights
-  char* out_base = static_cast<char*>(a.out0) + (a.i2 ? size_t(step & 1) * a.i2 : 0);
-  bf16* y = reinterpret_cast<bf16*>(out_base);
-  const bf16* bias = static_cast<const bf16*>(a.in3);
-  for (int c = c_first; c < c_end; c += nwarps) {
-    float acc[MAXM], acc2[MAXM];
-#pragma unroll
-    for (int m = 0; m < MAXM; ++m) acc[m] = acc2[m] = 0.f;
-    const int passes = pair ? 2 : 1;
-    for (int ps = 0; ps < passes; ++ps) {
-      const bf16* wr = W + size_t(ps == 0 ? c : c + a.N) * K;
-      for (int k0 = lane; k0 < kv; k0 += 32 * UN) {
-        int4 wv[UN];
-        if (c == c_first && ps == 0 && k0 == lane) {
-#pragma unroll
-          for (int u = 0; u < UN; ++u) wv[u] = wpre[u];
-        } else {
-#pragma unroll
-          for (int u = 0; u < UN; ++u) {
-            const int kk = k0 + u * 32;
-            wv[u] = kk < kv ? ptx::ld_nc_v4(wr + size_t(kk) * 8) : make_int4(0, 0, 0, 0);
-          }
+  if (threadIdx.x == 0 && tr != nullptr) tr[3] = ptx::globaltimer();  // activations staged
+
+  // (4) consume the weight stream with tensor-core MMAs
+  const int rg = warp & 1, ks = warp >> 1;  // this warp: row group (16 rows) and k-slices ks, ks + 8 of every stage
+  // A fragment addressing (ldmatrix.x4): lane l supplies row (l & 7) + 8 * ((l >> 3) & 1), k offset 8 * (l >> 4).
+  // Stage layout: kSubBoxes boxes of [R rows][128 B], 16-byte chunks XOR-swizzled with (row & 7) by the TMA.
+  const uint32_t a_row = uint32_t(rg * 16 + (lane & 7) + ((lane >> 3) & 1) * 8);
+  const uint32_t sub_pitch = ((uint32_t(ge.R) + 7u) & ~7u) * 128u;
+  // B fragment: this lane holds x[n = lane / 4][k0 + 2 (lane % 4) + {0, 1}] and the same at k0 + 8
+  const int bn = lane >> 2;
+  const bf16* xb = xs + size_t(bn < M ? bn : 0) * xpitch + (lane & 3) * 2;
+  const bool b_on = bn < M;
+  const bool rg_on = rg * 16 < ge.R;
+  int rbuf = 0;
+  for (int blob = 0; blob < (pair ? 2 : 1); ++blob) {
+    for (int blk = 0; blk < ge.nblk; ++blk) {
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int kb = 0; kb < ge.kboxes; ++kb) {
+        // refill what the ring allows, then wait for this stage (still trying: the stage may be this warp's to issue)
+        for (;;) {
+          try_issue(is, r, tab, n_ent, cons);
+          uint32_t ok = lane == 0 ? uint32_t(ptx::mbar_test_wait(&r.full[slot], par)) : 0u;
+          ok = __shfl_sync(0xffffffffu, ok, 0);
+          if (ok) break;
         }
+        const uint8_t* sbuf = r.buf + size_t(slot) * kStageBytes;
+        if (rg_on) {
 #pragma unroll
-        for (int u = 0; u < UN; ++u) {
-          const int kk = k0 + u * 32;
-          if (kk >= kv) break;
-          float wf[8];
-          unpack8(wv[u], wf);
-#pragma unroll
-          for (int m = 0; m < MAXM; ++m) {
-            if (m < a.M) {
-              float xf[8];
-              unpack8(*reinterpret_cast<const int4*>(xs + size_t(m) * K + size_t(kk) * 8), xf);
-              float s = 0.f;
-#pragma unroll
-              for (int i = 0; i < 8; ++i) s = fmaf(wf[i], xf[i], s);
-              if (ps == 0)
-                acc[m] += s;
-              else
-                acc2[m] += s;
+          for (int it = 0; it < 2; ++it) {
+            const int sl = ks + 8 * it;
+            const int k0 = kb * ge.kbox + sl * 16;
+            if (sl * 16 < ge.kbox && k0 < K) {
+              uint32_t af[4];
+              const uint32_t chunk = uint32_t((sl & 3) * 2 + (lane >> 4)) ^ (a_row & 7u);
+              ldmatrix_x4(af, sbuf + (sl >> 2) * sub_pitch + a_row * 128u + chunk * 16u);
+              uint32_t b0 = *reinterpret_cast<const uint32_t*>(xb + k0);
+              uint32_t b1 = *reinterpret_cast<const uint32_t*>(xb + k0 + 8);
+              if (!b_on) b0 = b1 = 0u;
+              mma_bf16_16816(d, af, b0, b1);
             }
           }
         }
-      }
-    }
-#pragma unroll
-    for (int m = 0; m < MAXM; ++m) {
-      if (m < a.M) {
-        float g = ptx::warp_reduce_sum(acc[m]);
-        if (pair) {
-          const float u = ptx::warp_reduce_sum(acc2[m]);
-          // round gate/up to bf16 first: matches the unfused fc1 -> silu_mul sequence bit for bit in the common case
-          g = __bfloat162float(__float2bfloat16(g));
-          const float uu = __bfloat162float(__float2bfloat16(u));
-          g = g / (1.f + __expf(-g)) * uu;
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&r.empty[slot]);
+        ++cons;
+        if (++slot == uint32_t(r.stages)) {
+          slot = 0;
+          par ^= 1u;
         }
-        if (bias != nullptr) g += __bfloat162float(bias[c]);
-        if (lane == 0) y[size_t(m) * a.i1 + c] = __float2bfloat16(g);
       }
+      // block done: sum the 8 partial tiles of each row group. d[0..1] = (row lane/4, n 2*(lane%4)+{0,1}), d[2..3] = row + 8.
+      float* rb = red + size_t(rbuf) * kWarps * 128 + warp * 128;
+      *reinterpret_cast<float2*>(rb + (lane >> 2) * 8 + (lane & 3) * 2) = make_float2(d[0], d[1]);
+      *reinterpret_cast<float2*>(rb + ((lane >> 2) + 8) * 8 + (lane & 3) * 2) = make_float2(d[2], d[3]);
+      __syncthreads();
+      if (threadIdx.x < 256) {
+        const int g2 = threadIdx.x >> 7, idx = threadIdx.x & 127;
+        const float* rs = red + size_t(rbuf) * kWarps * 128 + g2 * 128 + idx;  // warps g2, g2 + 2, ...
+        float sum = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWarps / 2; ++w) sum += rs[w * 256];
+        acc[((size_t(blob) * ge.nblk + blk) * 2 + g2) * 128 + idx] = sum;  // [(blob, block, row group)][row][n]
+      }
+      rbuf ^= 1;  // the next block's partials go to the other buffer; its barrier orders the reuse of this one
     }
+  }
+  try_issue(is, r, tab, n_ent, cons);  // keep the next linear task's stream moving during the epilogue
+  __syncthreads();
+  if (threadIdx.x == 0 && tr != nullptr) tr[4] = ptx::globaltimer();  // weight stream consumed
+
+  // (5) epilogue: activation pairing, bias, store
+  char* out_base = static_cast<char*>(a.out0) + (a.i2 ? size_t(step & 1) * a.i2 : 0);
+  bf16* y = reinterpret_cast<bf16*>(out_base);
+  const bf16* bias = static_cast<const bf16*>(a.in3);
+  const int ldy = a.i1;
+  for (int idx = threadIdx.x; idx < ncols * M; idx += kThreads) {
+    const int m = idx / ncols, c = idx - m * ncols;
+    const int blk = c / ge.R, rr = c - blk * ge.R;
+    const size_t off = (size_t(blk) * 2 + (rr >> 4)) * 128 + (rr & 15) * 8 + m;
+    float v = acc[off];
+    if (pair) {
+      const float u = acc[size_t(ge.nblk) * 256 + off];
+      // round gate/up to bf16 first: matches the unfused fc1 -> silu_mul sequence bit for bit in the common case
+      v = __bfloat162float(__float2bfloat16(v));
+      const float uu = __bfloat162float(__float2bfloat16(u));
+      v = v / (1.f + __expf(-v)) * uu;
+    }
+    if (bias != nullptr) v += __bfloat162float(bias[c_beg + c]);
+    y[size_t(m) * ldy + c_beg + c] = __float2bfloat16(v);
   }
 }
 
@@ -544,27 +690,88 @@ __device__ __forceinline__ void argmax_body(const OpArgs& a, int tile, uint8_t* 
 }
 
 // ------------------------------------------------------------------ the interpreter
+// Task records and op arguments live in global memory; a decode step streams gigabytes of weights through L2, so by
+// the time a CTA reaches task i + 1 both are usually cold (two dependent DRAM round trips on the critical path of
+// every task). They are therefore prefetched one task ahead by 12 threads into a double-buffered shared-memory slot,
+// published by the __syncthreads that ends every task.
+struct TaskSlot {
+  OpArgs a;   // 160 bytes = 10 x int4
+  Task t;     // 32 bytes = 2 x int4
+};
+static_assert(sizeof(OpArgs) == 160 && sizeof(Task) == 32 && sizeof(TaskSlot) == 192, "TaskSlot layout");
+
 __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant__ KernelParams p) {
-  extern __shared__ __align__(16) uint8_t smem[];
+  extern __shared__ __align__(1024) uint8_t smem[];
   const PhaseState ps{p.step_state, p.step_state + 1};
   const uint32_t base = phase_begin(ps);
   const uint32_t step = base + 1;
   const int n = p.queue_len[blockIdx.x];
   const Task* q = p.queues + size_t(blockIdx.x) * p.max_tasks;
+  // weight ring (behind the per-task scratch area), its barriers, the task slots and the stream table
+  RingView r;
+  r.buf = smem + p.ring_offset;
+  r.stages = p.ring_stages;
+  r.full = reinterpret_cast<uint64_t*>(r.buf + size_t(r.stages) * kStageBytes);
+  r.empty = r.full + r.stages;
+  TaskSlot* slots = reinterpret_cast<TaskSlot*>(r.buf + size_t(r.stages) * kStageBytes + 256);
+  StreamEntry* tab = reinterpret_cast<StreamEntry*>(slots + 2);
+  const uint32_t n_ent = uint32_t(p.stream_len[blockIdx.x]);
+  {
+    const int4* src = reinterpret_cast<const int4*>(p.streams + size_t(blockIdx.x) * p.max_streams);
+    int4* dst = reinterpret_cast<int4*>(tab);
+    for (uint32_t i = threadIdx.x; i < n_ent * (sizeof(StreamEntry) / 16); i += kThreads) dst[i] = src[i];
+  }
+  int4 pf = make_int4(0, 0, 0, 0);
+  int op_next = 0;  // op index of task i + 1 (threads 0..9)
+  if (n > 0) {
+    if (threadIdx.x < 10) {
+      pf = reinterpret_cast<const int4*>(p.ops + q[0].op)[threadIdx.x];
+      if (n > 1) op_next = q[1].op;
+    } else if (threadIdx.x < 12) {
+      pf = reinterpret_cast<const int4*>(q)[threadIdx.x - 10];
+    }
+    if (threadIdx.x < 12) reinterpret_cast<int4*>(&slots[0])[threadIdx.x] = pf;
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < r.stages; ++s) {
+      ptx::mbar_init(&r.full[s], 1);
+      ptx::mbar_init(&r.empty[s], kThreads / 32);
+    }
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  Issuer is;
+  is.next_own = threadIdx.x >> 5;
+  is.e_idx = 0;
+  is.e_first = 0;
+  is.e_total = n_ent > 0 ? tab[0].total : 0;
+  is.pf_own = (threadIdx.x >> 5) + uint32_t(r.stages) / (kThreads / 32) * (kThreads / 32);  // first stage >= ring size owned by this warp
+  if (is.pf_own < uint32_t(r.stages)) is.pf_own += kThreads / 32;
+  is.pf_idx = 0;
+  is.pf_first = 0;
+  is.pf_total = is.e_total;
+  uint32_t cons = 0, slot = 0, par = 0;
+  uint64_t* trace = p.trace != nullptr ? p.trace + (size_t(blockIdx.x) * p.max_tasks) * kTraceWords : nullptr;
   for (int i = 0; i < n; ++i) {
-    const Task t = q[i];
-    const OpArgs& a = p.ops[t.op];
+    const Task t = slots[i & 1].t;
+    const OpArgs& a = slots[i & 1].a;
     const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1 = step * uint32_t(t.dep1_cnt);
+    uint64_t* tr = trace != nullptr ? trace + size_t(i) * kTraceWords : nullptr;
+    if (threadIdx.x == 0 && tr != nullptr) tr[0] = ptx::globaltimer();
+    try_issue(is, r, tab, n_ent, cons);  // keep the weight stream moving (warp-collective)
+    // start fetching task i + 1 (its op index was read one task earlier, so the two loads are not chained)
+    int op_next2 = 0;
+    if (i + 1 < n) {
+      if (threadIdx.x < 10) {
+        pf = reinterpret_cast<const int4*>(p.ops + op_next)[threadIdx.x];
+        if (i + 2 < n) op_next2 = q[i + 2].op;
+      } else if (threadIdx.x < 12) {
+        pf = reinterpret_cast<const int4*>(q + i + 1)[threadIdx.x - 10];
+      }
+    }
     if (t.type == OP_LINEAR) {
-      // waits for its dependencies inside (after issuing the first weight loads)
-      if (a.M <= 1)
-        linear_body<1>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
-      else if (a.M <= 2)
-        linear_body<2>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
-      else if (a.M <= 4)
-        linear_body<4>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
-      else
-        linear_body<8>(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1);
+      // waits for its dependencies inside (its weight stream is normally already in flight)
+      linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, is, cons, slot, par, tab, n_ent, tr);
     } else {
       if (threadIdx.x == 0) {
         wait_slot(p.scoreboard, t.dep0, tgt0);
@@ -581,10 +788,9 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
           int done = 0;
           while (done < g) {
             const int rem = g - done;
-            if (rem >= 8) {
-              attn_split_body<8>(a, t.tile, smem, g, done);
-              done += 8;
-            } else if (rem >= 4) {
+            // (at most 4 heads per pass: the cross-group reduction buffer of 8 would take 133 KB of shared memory
+            // away from the weight ring; the second pass re-reads this split's K/V from L2)
+            if (rem >= 4) {
               attn_split_body<4>(a, t.tile, smem, g, done);
               done += 4;
             } else if (rem >= 2) {
@@ -608,10 +814,15 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
         default: break;
       }
     }
+    if (i + 1 < n && threadIdx.x < 12) reinterpret_cast<int4*>(&slots[(i + 1) & 1])[threadIdx.x] = pf;
+    op_next = op_next2;
     __syncthreads();
-    if (threadIdx.x == 0 && t.out_slot >= 0) {
-      __threadfence();
-      atomicAdd(p.scoreboard + t.out_slot, 1u);
+    if (threadIdx.x == 0) {
+      if (t.out_slot >= 0) {
+        __threadfence();
+        atomicAdd(p.scoreboard + t.out_slot, 1u);
+      }
+      if (tr != nullptr) tr[1] = ptx::globaltimer();
     }
   }
   phase_end(ps, base, 1);

@@ -243,6 +243,11 @@ int tdist_mega_compile(void* builder, const tdist_symm_ctx* ctx, uint32_t* ar_fl
 int tdist_mega_run(void* builder, void* stream);
 int tdist_mega_info(void* builder, int* out6); /* ops, tasks, max queue length, smem bytes, CTAs, #cross-rank ops */
 int tdist_mega_op_tiles(void* builder, int op_index);
+/* per-task timeline: stamp globaltimer at the start/end of every task of the following launches; get_trace copies
+ * [num_ctas][max_tasks][6] uint64 nanosecond stamps of the last launch to the host (begin, end, linear tasks:
+ * dependencies satisfied, activations staged, weight stream consumed, spare) */
+int tdist_mega_set_trace(void* builder, int enable);
+int tdist_mega_get_trace(void* builder, unsigned long long* out, size_t cap_words);
 int tdist_mega_get_queue(void* builder, int cta, int* out_8ints_per_task, int cap);
 int tdist_mega_destroy(void* builder);
 

@@ -58,3 +58,16 @@ for (M, N, K) in [(8192, 14336, 4096), (8192, 4096, 14336), (8192, 1792, 4096), 
                 print(f"M={M} N={N} K={K} tdist cg={cg} bn={bn:3d}: {t:.4f} ms {fl / t / 1e9:.0f} TFLOP/s", flush=True)
             except Exception:
                 traceback.print_exc()
+
+print("== gemv bandwidth", flush=True)
+from triton_dist.kernels.nvidia.elementwise import gemv  # noqa: E402
+
+for (N, K) in [(25600, 5120), (5120, 25600), (151936, 5120), (8192, 8192)]:
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) * 0.02
+    for M in (1, 4):
+        x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+        y = gemv(x, w)
+        ref = x.float() @ w.float().t()
+        err = (y.float() - ref).abs().max().item()
+        t = timeit(lambda: gemv(x, w), flush=flush)
+        print(f"gemv M={M} N={N} K={K}: {t * 1e3:.1f} us {N * K * 2 / t / 1e9:.2f} TB/s err {err:.3g}", flush=True)

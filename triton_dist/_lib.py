@@ -166,6 +166,8 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_mega_info", [vp, P(i32 * 6)])
     sig("tdist_mega_op_tiles", [vp, i32])
     sig("tdist_mega_get_queue", [vp, i32, vp, i32])
+    sig("tdist_mega_set_trace", [vp, i32])
+    sig("tdist_mega_get_trace", [vp, vp, sz])
     sig("tdist_mega_destroy", [vp])
     sig("tdist_gemm", [P(GemmArgs), vp])
     sig("tdist_gemm_fused", [P(GemmArgs), P(FusedArgs), vp])

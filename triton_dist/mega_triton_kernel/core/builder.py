@@ -268,6 +268,64 @@ class ModelBuilder:
             return
         _lib.check(_lib.lib().tdist_mega_run(self._handle, _lib.stream_ptr(stream)), "mega_run")
 
+    # ------------------------------------------------------------------ per-task timeline
+    OP_NAMES = ["linear", "rms_norm", "silu_mul", "add", "qk_norm_rope_kv", "attn_split", "attn_combine", "allreduce", "barrier",
+                "prefetch", "embedding", "argmax"]
+
+    def enable_profiling(self, on: bool = True):
+        """Stamp %globaltimer at the start and end of every task of the following launches (thread 0 of each CTA).
+
+        The reference profiles its megakernel from outside with torch.profiler (test/models/bench_qwen3.py:34); a
+        persistent kernel is one opaque launch there, so this build records the task timeline inside the kernel."""
+        assert self._compiled, "compile() first"
+        if self.native:
+            _lib.check(_lib.lib().tdist_mega_set_trace(self._handle, 1 if on else 0), "mega_set_trace")
+
+    def get_trace(self):
+        """Returns a list of (cta, index, op, type_name, tile, begin_ns, end_ns, phases) of the last profiled launch;
+        ``phases`` = (deps_satisfied_ns, staged_ns, consumed_ns) for linear tasks (zeros otherwise)."""
+        import numpy as np
+        info = self.info()
+        ctas, mq = info["ctas"], info["max_queue"]
+        buf = np.zeros(ctas * mq * 6, dtype=np.uint64)
+        torch.cuda.synchronize()
+        _lib.check(_lib.lib().tdist_mega_get_trace(self._handle, buf.ctypes.data, buf.size), "mega_get_trace")
+        buf = buf.reshape(ctas, mq, 6)
+        out = []
+        q = (ctypes.c_int * (8 * mq))()
+        for c in range(ctas):
+            n = _lib.lib().tdist_mega_get_queue(self._handle, c, q, mq)
+            for i in range(max(n, 0)):
+                op, typ, tile = q[8 * i], q[8 * i + 1], q[8 * i + 2]
+                out.append((c, i, op, self.OP_NAMES[typ], tile, int(buf[c, i, 0]), int(buf[c, i, 1]),
+                            (int(buf[c, i, 2]), int(buf[c, i, 3]), int(buf[c, i, 4]))))
+        return out
+
+    def dump_trace(self, path: str):
+        """Write the last profiled launch as a chrome://tracing JSON (one row per CTA)."""
+        import json
+        ev = self.get_trace()
+        t0 = min((e[5] for e in ev if e[5] > 0), default=0)
+        js = [{"name": f"{e[3]}#{e[2]}", "ph": "X", "pid": self.rank, "tid": e[0], "ts": (e[5] - t0) / 1e3,
+               "dur": max(e[6] - e[5], 0) / 1e3, "args": {"tile": e[4], "queue_index": e[1]}} for e in ev if e[5] > 0]
+        with open(path, "w") as f:
+            json.dump({"traceEvents": js, "displayTimeUnit": "ns"}, f)
+        return path
+
+    def profile_summary(self) -> dict:
+        """Per op type: summed busy time over CTAs (us) and count, plus the span of the whole launch."""
+        ev = [e for e in self.get_trace() if e[5] > 0]
+        if not ev:
+            return {}
+        span = (max(e[6] for e in ev) - min(e[5] for e in ev)) / 1e3
+        agg: dict = {}
+        for e in ev:
+            d = agg.setdefault(e[3], [0.0, 0])
+            d[0] += (e[6] - e[5]) / 1e3
+            d[1] += 1
+        ctas = self.info()["ctas"]
+        return {"span_us": span, "per_type": {k: {"busy_us_per_cta": v[0] / ctas, "tasks": v[1]} for k, v in agg.items()}}
+
     def finalize(self):
         if self.native and self._handle:
             _lib.lib().tdist_mega_destroy(self._handle)

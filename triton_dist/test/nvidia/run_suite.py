@@ -1,5 +1,5 @@
 """Run a named group of distributed checks in one torchrun launch.
-    torchrun --nproc-per-node N -m triton_dist.test.nvidia.run_suite --suite core|moe|models|all"""
+    torchrun --nproc-per-node N -m triton_dist.test.nvidia.run_suite --suite core|moe|models|mega|all"""
 import argparse
 import os
 import sys
@@ -37,12 +37,17 @@ def cases(suite: str, world: int):
         (M + "test_qwen3", []),
         (M + "test_qwen3", ["--unfused"]),
     ]
-    return {"core": core, "moe": moe, "models": models, "all": core + moe + models}[suite]
+    mega = [
+        ("triton_dist.mega_triton_kernel.test.ops.test_ops", []),
+        (M + "test_qwen3", []),
+        (M + "test_qwen3", ["--unfused"]),
+    ]
+    return {"core": core, "moe": moe, "models": models, "mega": mega, "all": core + moe + models + mega[:1]}[suite]
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--suite", default="all", choices=["core", "moe", "models", "all"])
+    ap.add_argument("--suite", default="all", choices=["core", "moe", "models", "mega", "all"])
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     ok = run_suite(cases(args.suite, world))

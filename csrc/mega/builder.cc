@@ -74,16 +74,16 @@ static int tiles_of(const OpArgs& a, int type, int num_ctas, int* cols_per_tile)
 static int smem_of(const OpArgs& a, int type) {
   switch (type) {
     case OP_LINEAR: {
-      // activations [M][kboxes * kbox + 8] bf16, norm weight [K] bf16 when fused, block sums [2][nblk][256] fp32,
-      // cross-warp partials [2][16 warps][128] fp32, block_sum scratch
+      // activations [M][kboxes * kstage + 8] bf16, norm weight [K] bf16 when fused, block sums [2][nblk][32][M] fp32,
+      // cross-warp partials [2][16 warps][32][M] fp32, block_sum scratch
       const LinearGeom ge = linear_geom(a.cols_per_tile, a.K);
-      const int xpitch = ge.kboxes * ge.kbox + 8;
-      return a.M * xpitch * 2 + (a.in2 != nullptr ? a.K * 2 : 0) + 2 * ge.nblk * 256 * 4 + 2 * (kThreads / 32) * 128 * 4 + 256;
+      const int xpitch = ge.kboxes * ge.kstage + 8;
+      return a.M * xpitch * 2 + (a.in2 != nullptr ? a.K * 2 : 0) + 2 * ge.nblk * 32 * a.M * 4 + 2 * (kThreads / 32) * 32 * a.M * 4 + 256;
     }
     case OP_RMS_NORM: return a.K * 4 + 256;
     case OP_ATTN_SPLIT: {
-      const int g = std::min(4, a.i0 / std::max(a.i1, 1));  // the kernel runs at most 4 heads per pass
-      return (kThreads / 16) * g * (2 + 128) * 4;
+      const int g = std::min(8, a.i0 / std::max(a.i1, 1));
+      return (kThreads / 32) * g * (2 + 128) * 4 + g * 128 * 4;  // per-warp (max, sum, out[128]) for g heads + scaled q
     }
     case OP_ARGMAX: return 1024;
   }
@@ -133,8 +133,8 @@ int tdist_mega_add_op(void* h, int type, const tdist_mega_op* d, int dep0, int d
   a.i0 = d->i[0]; a.i1 = d->i[1]; a.i2 = d->i[2]; a.i3 = d->i[3]; a.i4 = d->i[4]; a.i5 = d->i[5];
   a.l0 = d->l[0]; a.l1 = d->l[1]; a.l2 = d->l[2];
   a.f0 = d->f[0]; a.f1 = d->f[1];
-  if (type == OP_LINEAR && (a.M < 1 || a.M > 8 || a.K % 16 != 0)) {
-    set_error("mega linear: need 1 <= M <= 8 rows and K % 16 == 0");
+  if (type == OP_LINEAR && (a.M < 1 || a.M > 8 || a.K % 64 != 0)) {
+    set_error("mega linear: need 1 <= M <= 8 rows and K % 64 == 0");
     return -1;
   }
   if (type == OP_ALLREDUCE || type == OP_BARRIER) a.i0 = b->num_ar_ops++;
@@ -195,12 +195,14 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
       }
       const LinearGeom ge = linear_geom(a.cols_per_tile, a.K);
       const uint64_t rows = (a.i0 & 1) ? uint64_t(a.N) * 2 : uint64_t(a.N);
-      cuuint64_t dims[2] = {cuuint64_t(a.K), rows};
-      cuuint64_t strides[1] = {cuuint64_t(a.K) * 2};
-      cuuint32_t box[2] = {64u, cuuint32_t(ge.R)};
-      cuuint32_t estr[2] = {1, 1};
+      // 3-D view of the row-major [rows, K] matrix: dim0 = k % 64 (contiguous), dim1 = row (stride K * 2 bytes),
+      // dim2 = k / 64 (stride 128 bytes). A box {64, R, nsub} lands in shared memory as [slab][row][128 B].
+      cuuint64_t dims[3] = {64, rows, cuuint64_t(a.K / 64)};
+      cuuint64_t strides[2] = {cuuint64_t(a.K) * 2, 128};
+      cuuint32_t box[3] = {64u, cuuint32_t(ge.R), cuuint32_t(ge.nsub)};
+      cuuint32_t estr[3] = {1, 1, 1};
       CUtensorMap tm;
-      CUresult rc = d.cuTensorMapEncodeTiled(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(a.in1), dims, strides,
+      CUresult rc = d.cuTensorMapEncodeTiled(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(a.in1), dims, strides,
                                              box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       if (rc != CUDA_SUCCESS) {
@@ -231,7 +233,7 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
       e.pair_rows = (a.i0 & 1) ? uint32_t(a.N) : 0u;
       e.R = uint8_t(ge.R);
       e.nblk = uint8_t(ge.nblk);
-      e.kbox = uint16_t(ge.kbox);
+      e.kstage = uint16_t(ge.kstage);
       e.kboxes = uint32_t(ge.kboxes);
       e.total = ((a.i0 & 1) ? 2u : 1u) * uint32_t(ge.nblk) * uint32_t(ge.kboxes);
       e.first = first;
@@ -241,9 +243,11 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
     max_streams = std::max(max_streams, int(streams[c].size()));
   }
   // dynamic shared memory = [per-task scratch, max over ops][weight ring][ring barriers][2 task slots][stream table]
-  const int aux_bytes = 256 + 2 * 192 + max_streams * int(sizeof(StreamEntry));
+  // (+4 KB: ldmatrix always reads 16 / 32 lines per slab, i.e. up to 31 lines past the last slab of a buffer; those
+  // accumulator rows are never used, but the read must stay inside the allocation)
+  const int aux_bytes = 256 + 2 * 192 + max_streams * int(sizeof(StreamEntry)) + 4096;
   const int ring_offset = (smem + 1023) / 1024 * 1024;  // 1024 B: the 128 B TMA swizzle is a function of the address
-  int stages = (kSmemLimit - 2048 - ring_offset - aux_bytes) / kStageBytes;  // 2 KB: static shared memory of the task bodies
+  int stages = (kSmemLimit - 2048 - ring_offset - aux_bytes) / kSlotBytes;  // 2 KB: static shared memory of the task bodies
   stages = std::min(stages, kMaxRingStages);
   if (stages < 2) {
     set_error("mega: an op needs too much shared memory to leave room for the weight ring (batch * K too large)");
@@ -251,7 +255,7 @@ int tdist_mega_compile(void* h, const tdist_symm_ctx* ctx, uint32_t* ar_flags) {
   }
   b->ring_offset = ring_offset;
   b->ring_stages = stages;
-  b->smem_bytes = ring_offset + stages * kStageBytes + aux_bytes;
+  b->smem_bytes = ring_offset + stages * kSlotBytes + aux_bytes;
   b->total_tasks = cursor;
   b->max_tasks = 1;
   for (auto& q : queues) b->max_tasks = std::max(b->max_tasks, int(q.size()));
@@ -342,7 +346,7 @@ int tdist_mega_set_trace(void* h, int enable) {
     return -1;
   }
   if (enable && b->d_trace == nullptr) {
-    const size_t bytes = size_t(b->num_ctas) * b->max_tasks * kTraceWords * sizeof(uint64_t);
+    const size_t bytes = (size_t(b->num_ctas) * b->max_tasks * kTraceWords + size_t(b->num_ctas) * (kThreads / 32) * 4) * sizeof(uint64_t);
     TDIST_RT_TRY(cudaMalloc(&b->d_trace, bytes));
     TDIST_RT_TRY(cudaMemset(b->d_trace, 0, bytes));
   }
@@ -356,7 +360,7 @@ int tdist_mega_get_trace(void* h, unsigned long long* out, size_t cap_words) {
     set_error("mega: tracing was not enabled");
     return -1;
   }
-  const size_t words = size_t(b->num_ctas) * b->max_tasks * kTraceWords;
+  const size_t words = size_t(b->num_ctas) * b->max_tasks * kTraceWords + size_t(b->num_ctas) * (kThreads / 32) * 4;
   if (cap_words < words) {
     set_error("mega: trace buffer too small");
     return -1;

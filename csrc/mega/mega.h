@@ -62,30 +62,39 @@ struct Task {
 };
 
 // Geometry of the weight stream of one LINEAR tile (identical on host and device): the tile's cols_per_tile rows of
-// W are cut into nblk row blocks of R <= 32 rows, K into kboxes boxes of kbox <= 256 elements; one stage = one box.
+// W are cut into nblk row blocks of R <= kStageRows rows, K into kboxes extents of kstage = 64 * nsub elements; one
+// stage = one (row block, k extent) = one TMA box {64, R, nsub} of the 3-D view [k % 64][row][k / 64] of W.
+constexpr int kStageRows = 24;
 struct LinearGeom {
-  int nblk, R, kbox, kboxes;
+  int nblk, R, nsub, kstage, kboxes;
 };
 #ifdef __CUDACC__
 __host__ __device__
 #endif
 inline LinearGeom linear_geom(int cols_per_tile, int K) {
   LinearGeom g;
-  g.nblk = (cols_per_tile + 31) / 32;
+  g.nblk = (cols_per_tile + kStageRows - 1) / kStageRows;
   g.R = (cols_per_tile + g.nblk - 1) / g.nblk;
-  g.kbox = 256;  // always whole boxes: the TMA zero-fills beyond K and the staged activations are zero padded
-  g.kboxes = (K + g.kbox - 1) / g.kbox;
+  // a stage buffer holds kStageRows * 4 lines of 128 B, a stage nsub slabs of R lines (64 k-elements each): short row
+  // blocks get proportionally longer k extents, so that a stage is always ~12 KB (4 slabs = 256 k for R = 24,
+  // 12 slabs = 768 k for R = 8).
+  g.nsub = (kStageRows * 4) / g.R;
+  if (g.nsub > 12) g.nsub = 12;
+  const int need = (K + 63) / 64;  // never more slabs than K has
+  if (g.nsub > need) g.nsub = need;
+  g.kstage = g.nsub * 64;
+  g.kboxes = (K + g.kstage - 1) / g.kstage;
   return g;
 }
 
 // One entry per LINEAR task of a CTA's queue, in queue order. Stages are numbered consecutively over all linear
 // tasks of the CTA, per task in the order (blob, row block, k box).
 struct StreamEntry {
-  const void* tmap;     // device copy of the op's CUtensorMap: W as [rows, K] bf16, box {64, R}, 128 B swizzle
+  const void* tmap;     // device copy of the op's CUtensorMap: W as [64][rows][K / 64] bf16, box {64, R, nsub}, 128 B swizzle
   uint32_t row0;        // first row of the tile (c_beg)
   uint32_t pair_rows;   // silu pairing: row offset of the "up" half (N), else 0
-  uint8_t R, nblk;      // R <= 32, nblk <= 8
-  uint16_t kbox;
+  uint8_t R, nblk;      // R <= kStageRows, nblk <= 11
+  uint16_t kstage;      // k-elements per stage (64 * number of boxes)
   uint32_t kboxes;
   uint32_t first;       // id of the task's first stage
   uint32_t total;       // stages of the task = blobs * nblk * kboxes
@@ -112,10 +121,9 @@ struct KernelParams {
 constexpr int kThreads = 512;
 constexpr int kMaxArTiles = 32;
 constexpr int kTraceWords = 6;         // per task: begin, end, [linear: deps satisfied, activations staged, stream consumed], spare
-constexpr int kStageBytes = 32 * 256 * 2;          // ring slot: up to 32 rows x 256 k-elements (one 2-D TMA box)
-constexpr int kMaxRingStages = 12;
+constexpr int kSlotBytes = kStageRows * 256 * 2;   // stage buffer: up to 24 rows x 256 k-elements (four {64, R} TMA boxes)
+constexpr int kMaxRingStages = 16;     // one stage buffer per warp at most
 constexpr int kPrefetchStages = 0;     // L2 prefetch distance beyond the ring (stages); 0 = off (measured: no gain)
-constexpr int kSubBoxes = 4;           // TMA boxes of 64 k-elements per 256-element stage
 constexpr int kSmemLimit = 232448;     // 227 KB opt-in limit per CTA on sm_100
 
 }  // namespace mega

@@ -61,41 +61,45 @@ __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t
 // ------------------------------------------------------------------ LINEAR (skinny GEMM, M <= 8 rows)
 // i0 bit0: silu pairing (W = [2I, K], out = silu(gate) * up, N = I); i1: ldy; i2: out parity stride (bytes, 0 = none)
 //
-// Decode linears are weight-streaming: every weight byte is used once, so the job is to keep HBM busy with as few
-// instructions and as few copy requests per byte as possible. The weights of a tile (cols_per_tile consecutive rows
-// of W[N, K]) are cut into row blocks of R <= 32 rows and every block into STAGES of R rows x 256 k-elements
-// (<= 16 KB). One stage is four 2-D TMA requests (cp.async.bulk.tensor, box {64, R} of a per-op tensor map, 128 B
-// swizzle so that ldmatrix is bank-conflict free) into a ring in shared memory, completed on one mbarrier. Stages
-// are consumed with mma.sync.m16n8k16
-// (bf16 x bf16 -> fp32): the weight rows are the M dimension of the MMA, the batch (<= 8 activation rows) is its N
-// dimension, so one ldmatrix + one MMA retire 512 B of weights and a batch of 8 costs the same as a batch of 1. The
-// 16 warps split the stage as (2 row groups) x (16 k-slices); each keeps one fp32 accumulator tile for the current
-// row block and the partials are summed through shared memory once per block (one __syncthreads per block).
-// (An unswizzled {256, R} box was measured first: its 8-way conflicted ldmatrix cost ~1000 shared-memory wavefronts
-// per stage, as long as the HBM time of the stage.)
+// Decode linears are weight-streaming: every weight byte is used once, so the job is to keep as many bytes in flight
+// from HBM as shared memory can hold (loaded HBM latency on B200 is several microseconds: full bandwidth needs
+// ~200 KB per SM in flight) with as few instructions and copy requests per byte as possible.
 //
-// Producer: the stages of ALL linear tasks of this CTA form one sequence numbered from 0 (static table built by the
-// host, mega.h StreamEntry, copied to shared memory at kernel start); stage s is issued by lane 0 of warp (s mod 16)
-// as soon as that warp has itself consumed stage s - ring_stages and every warp has released the slot. Weights
-// never depend on activations, so the stream simply runs ahead: the first ring-full of the NEXT linear task is in
-// flight while the current task drains, while small tasks (attention, norms) execute and while the scoreboard wait
-// spins.
-struct RingView {
-  uint8_t* buf;     // stages * kStageBytes
-  uint64_t* full;   // [stages] : 1 arrival (+ tx bytes)
-  uint64_t* empty;  // [stages] : one arrival per warp
-  int stages;
+// The weights of a tile (cols_per_tile consecutive rows of W[N, K]) are cut into row blocks of R <= 24 rows and every
+// block into STAGES of R rows x (256 .. 768) k-elements (~12 KB whatever R is). One stage is ONE TMA request
+// (cp.async.bulk.tensor.3d on the view [k % 64][row][k / 64] of W, box {64, R, nsub}, 128 B swizzle so that
+// ldmatrix is bank-conflict free) completed on one mbarrier. The stages of ALL linear tasks of this CTA form one sequence numbered from 0 (static table built by the
+// host, mega.h StreamEntry, copied to shared memory at kernel start).
+//
+// Shared memory holds `slots` stage buffers and warp w (< slots) OWNS buffer w: it consumes stage s = w (mod slots)
+// and, as soon as its ldmatrix reads are done, issues stage s + slots into the same buffer itself. There is no
+// producer warp, no empty barrier and no coupling between warps inside a row block; weights never depend on
+// activations, so the stream runs ahead across task boundaries on its own: the first stages of the NEXT linear task
+// are in flight while the current task's epilogue runs, while small tasks (attention, norms) execute and while the
+// scoreboard wait spins.
+//
+// A stage is consumed with mma.sync.m16n8k16 (bf16 x bf16 -> fp32): the weight rows are the M dimension of the MMA,
+// the batch (<= 8 activation rows) is its N dimension, so one ldmatrix + one MMA retire 512 B of weights and a batch
+// of 8 costs the same as a batch of 1. Each warp keeps fp32 accumulator tiles for the current row block; the warps'
+// partials are summed through shared memory once per block (one __syncthreads per block).
+// (Measured on the way here: per-row 1-D bulk copies are limited by the TMA request rate, an unswizzled {256, R} box
+// by 8-way conflicted ldmatrix, and a ring shared by all warps by the per-stage handshake latency.)
+struct Ring {
+  uint8_t* buf;      // slots * kSlotBytes
+  uint64_t* full;    // [slots] : 1 arrival (+ tx bytes)
+  const StreamEntry* tab;
+  uint32_t n_ent;
+  uint32_t slots;
+  // per-warp stream cursor (warp-uniform registers)
+  uint32_t issued;   // id of the stage in flight / next to be consumed by this warp (0xffffffff: none)
+  uint32_t e_idx, e_first, e_total;  // table entry containing `issued`
+  uint32_t uses;     // completed uses of this warp's buffer (mbarrier parity)
+  // optional per-warp cycle accounting of the linear main loop (KernelParams::trace != nullptr):
+  // [0] waiting for a stage to land, [1] ldmatrix + MMA, [2] issuing the next stage, [3] block-end barrier + sum
+  bool prof;
+  uint32_t cyc[4];
 };
-
-struct Issuer {           // warp-uniform
-  uint32_t next_own;      // next stage id this warp is responsible for
-  uint32_t e_idx;         // stream-table entry containing next_own
-  uint32_t e_first, e_total;
-  // second cursor kPrefetchStages further ahead: L2 prefetch of the same boxes. Loaded HBM latency on B200 is several
-  // microseconds, so full bandwidth needs ~200 KB per SM in flight - more than the ring can hold; the prefetches keep
-  // that many bytes in flight towards L2 and the ring loads then hit L2.
-  uint32_t pf_own, pf_idx, pf_first, pf_total;
-};
+__device__ __forceinline__ uint32_t clk() { return uint32_t(clock64()); }
 
 __device__ __forceinline__ void stage_coords(const StreamEntry& e, uint32_t stage, int& c0, int& c1) {
   uint32_t q = stage - e.first;
@@ -103,64 +107,36 @@ __device__ __forceinline__ void stage_coords(const StreamEntry& e, uint32_t stag
   const bool second = q >= per_blob;
   if (second) q -= per_blob;
   const uint32_t blk = q / e.kboxes, kb = q - blk * e.kboxes;
-  c0 = int(kb * e.kbox);
+  c0 = int(kb * uint32_t(e.kstage));
   c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);
 }
 
-// Warp-collective, called from converged code. Never blocks: a slot still being read is retried on the next call.
-__device__ __forceinline__ void try_issue(Issuer& is, const RingView& r, const StreamEntry* tab, uint32_t n_ent,
-                                          uint32_t cons) {
-  const int lane = threadIdx.x & 31;
-  while (kPrefetchStages > 0 && is.pf_own < cons + uint32_t(r.stages) + kPrefetchStages) {
-    while (is.pf_idx < n_ent && is.pf_own >= is.pf_first + is.pf_total) {
-      ++is.pf_idx;
-      if (is.pf_idx < n_ent) {
-        is.pf_first = tab[is.pf_idx].first;
-        is.pf_total = tab[is.pf_idx].total;
-      }
-    }
-    if (is.pf_idx >= n_ent) {
-      is.pf_own = 0xfffffff0u;
-      break;
-    }
-    if (lane == 0) {
-      const StreamEntry e = tab[is.pf_idx];
-      int c0, c1;
-      stage_coords(e, is.pf_own, c0, c1);
-#pragma unroll
-      for (int j = 0; j < kSubBoxes; ++j) ptx::tma_prefetch_2d(e.tmap, c0 + 64 * j, c1);
-    }
-    is.pf_own += kThreads / 32;
-  }
-  if (is.next_own >= cons + uint32_t(r.stages)) return;  // ring distance (also the cheap common early-out)
-  while (is.e_idx < n_ent && is.next_own >= is.e_first + is.e_total) {
-    ++is.e_idx;
-    if (is.e_idx < n_ent) {
-      is.e_first = tab[is.e_idx].first;
-      is.e_total = tab[is.e_idx].total;
+// Issue stage `stage` into this warp's buffer (warp-collective; lane 0 talks to the TMA). The caller guarantees that
+// the warp's previous reads of the buffer are complete.
+__device__ __forceinline__ void issue_stage(Ring& r, uint32_t stage) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  while (r.e_idx < r.n_ent && stage >= r.e_first + r.e_total) {
+    ++r.e_idx;
+    if (r.e_idx < r.n_ent) {
+      r.e_first = r.tab[r.e_idx].first;
+      r.e_total = r.tab[r.e_idx].total;
     }
   }
-  if (is.e_idx >= n_ent) {
-    is.next_own = 0xfffffff0u;  // nothing left to issue, ever
+  if (r.e_idx >= r.n_ent) {
+    r.issued = 0xffffffffu;  // the stream is finished for this warp
     return;
   }
-  const uint32_t S = uint32_t(r.stages);
-  const uint32_t round = is.next_own / S, slot = is.next_own - round * S;
-  uint32_t free_ = lane == 0 ? uint32_t(ptx::mbar_test_wait(&r.empty[slot], (round & 1u) ^ 1u)) : 0u;
-  free_ = __shfl_sync(0xffffffffu, free_, 0);
-  if (!free_) return;
+  r.issued = stage;
   if (lane == 0) {
-    const StreamEntry e = tab[is.e_idx];
+    const StreamEntry e = r.tab[r.e_idx];
     int c0, c1;
-    stage_coords(e, is.next_own, c0, c1);
-    // one stage = kSubBoxes TMA boxes of {64 k-elements (one 128 B swizzle row), R rows}, 1024 B-aligned one after another
-    ptx::mbar_arrive_expect_tx(&r.full[slot], uint32_t(e.R) * 128u * kSubBoxes);
-    const uint32_t sub_pitch = ((uint32_t(e.R) + 7u) & ~7u) * 128u;
-#pragma unroll
-    for (int j = 0; j < kSubBoxes; ++j)
-      ptx::tma_load_2d(r.buf + size_t(slot) * kStageBytes + j * sub_pitch, e.tmap, &r.full[slot], c0 + 64 * j, c1);
+    stage_coords(e, stage, c0, c1);
+    ptx::fence_proxy_async_shared();  // order the generic-proxy reads of the old contents before the async-proxy writes
+    // ONE request: box {64 k, R rows, nsub k-slabs} of the 3-D view [k % 64][row][k / 64]; lands as [slab][row][128 B]
+    const int nsub = e.kstage >> 6;
+    ptx::mbar_arrive_expect_tx(&r.full[warp], uint32_t(e.R) * 128u * uint32_t(nsub));
+    ptx::tma_load_3d(r.buf + size_t(warp) * kSlotBytes, e.tmap, &r.full[warp], 0, c1, c0 >> 6);
   }
-  is.next_own += kThreads / 32;
 }
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&a)[4], const void* smem_ptr) {
@@ -176,9 +152,8 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 }
 
 __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* smem, uint32_t step, const uint32_t* sb,
-                                            const Task& t, uint32_t dep_target0, uint32_t dep_target1, const RingView& r,
-                                            Issuer& is, uint32_t& cons, uint32_t& slot, uint32_t& par,
-                                            const StreamEntry* tab, uint32_t n_ent, uint64_t* tr) {
+                                            const Task& t, uint32_t dep_target0, uint32_t dep_target1, Ring& r,
+                                            uint32_t& stage_base, uint64_t* tr) {
   constexpr int kWarps = kThreads / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int K = a.K, kv = K >> 3, M = a.M, cpt = a.cols_per_tile;
@@ -186,16 +161,17 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
   const int c_beg = tile * cpt, c_end = min(c_beg + cpt, a.N);
   const int ncols = c_end - c_beg;
   const LinearGeom ge = linear_geom(cpt, K);                                  // same split as the host (StreamEntry)
-  const int xpitch = ge.kboxes * ge.kbox + 8;                                 // elements: zero padded to whole k boxes, +16 B
+  const int xpitch = ge.kboxes * ge.kstage + 8;                               // elements: zero padded to whole stages, +16 B
   bf16* xs = reinterpret_cast<bf16*>(smem);                                  // [M][xpitch] (normalised) activations
   const bf16* nw = static_cast<const bf16*>(a.in2);
   bf16* nws = xs + size_t(M) * xpitch;                                        // [K] norm weight (only when fused)
-  float* acc = reinterpret_cast<float*>(nws + (nw != nullptr ? K : 0));       // [2][nblk][2][16][8] block sums
-  float* red = acc + 2 * size_t(ge.nblk) * 256;                               // [2][kWarps][16][8] partials
-  float* scratch = red + 2 * kWarps * 128;                                    // 32 floats for block_sum
+  float* acc = reinterpret_cast<float*>(nws + (nw != nullptr ? K : 0));       // [2][nblk][2][16][M] block sums
+  const int tile_vals = 32 * M;                                               // (2 row groups x 16 rows) x M per block
+  float* red = acc + 2 * size_t(ge.nblk) * tile_vals;                         // [2][kWarps][2][16][M] partials
+  float* scratch = red + 2 * kWarps * tile_vals;                              // 32 floats for block_sum
 
-  // (1) this task's first stages are normally in flight already (see try_issue). Everything that does not depend on
-  // the producer op is done before the scoreboard wait: norm weight into shared memory, zero padding of x.
+  // (1) everything that does not depend on the producer op is done before the scoreboard wait: norm weight into
+  // shared memory, zero padding of x. (This task's first stages are already in flight, see Ring.)
   if (nw != nullptr)
     for (int i = threadIdx.x; i < kv; i += kThreads)
       *reinterpret_cast<int4*>(nws + size_t(i) * 8) = ptx::ld_nc_v4(nw + size_t(i) * 8);
@@ -240,70 +216,101 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
   if (threadIdx.x == 0 && tr != nullptr) tr[3] = ptx::globaltimer();  // activations staged
 
   // (4) consume the weight stream with tensor-core MMAs
-  const int rg = warp & 1, ks = warp >> 1;  // this warp: row group (16 rows) and k-slices ks, ks + 8 of every stage
   // A fragment addressing (ldmatrix.x4): lane l supplies row (l & 7) + 8 * ((l >> 3) & 1), k offset 8 * (l >> 4).
-  // Stage layout: kSubBoxes boxes of [R rows][128 B], 16-byte chunks XOR-swizzled with (row & 7) by the TMA.
-  const uint32_t a_row = uint32_t(rg * 16 + (lane & 7) + ((lane >> 3) & 1) * 8);
-  const uint32_t sub_pitch = ((uint32_t(ge.R) + 7u) & ~7u) * 128u;
+  // Buffer layout: [nsub slabs][R rows][128 B], the 16-byte chunks of every 128 B line XOR-swizzled with (line & 7)
+  // by the TMA (line = slab * R + row; the buffer is 1024 B aligned).
+  const uint32_t a_row = uint32_t((lane & 7) + ((lane >> 3) & 1) * 8);  // row inside a 16-row group
+  const uint32_t a_hi = uint32_t(lane >> 4);                            // which 16-byte half of the k-slice
+  const uint8_t* sbuf = r.buf + size_t(warp) * kSlotBytes;
   // B fragment: this lane holds x[n = lane / 4][k0 + 2 (lane % 4) + {0, 1}] and the same at k0 + 8
   const int bn = lane >> 2;
   const bf16* xb = xs + size_t(bn < M ? bn : 0) * xpitch + (lane & 3) * 2;
-  const bool b_on = bn < M;
-  const bool rg_on = rg * 16 < ge.R;
+  const uint32_t bmask = bn < M ? 0xffffffffu : 0u;  // batch rows beyond M contribute zeros
+  const bool two_groups = ge.R > 16;
+  const bool consumer = uint32_t(warp) < r.slots;
   int rbuf = 0;
+  uint32_t blk_first = stage_base;  // id of the first stage of the current (blob, row block)
   for (int blob = 0; blob < (pair ? 2 : 1); ++blob) {
-    for (int blk = 0; blk < ge.nblk; ++blk) {
-      float d[4] = {0.f, 0.f, 0.f, 0.f};
-      for (int kb = 0; kb < ge.kboxes; ++kb) {
-        // refill what the ring allows, then wait for this stage (still trying: the stage may be this warp's to issue)
-        for (;;) {
-          try_issue(is, r, tab, n_ent, cons);
-          uint32_t ok = lane == 0 ? uint32_t(ptx::mbar_test_wait(&r.full[slot], par)) : 0u;
-          ok = __shfl_sync(0xffffffffu, ok, 0);
-          if (ok) break;
-        }
-        const uint8_t* sbuf = r.buf + size_t(slot) * kStageBytes;
-        if (rg_on) {
+    for (int blk = 0; blk < ge.nblk; ++blk, blk_first += ge.kboxes) {
+      // two accumulator tiles per row group (even / odd k-slices): halves the dependent-MMA chain
+      float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+      float d0b[4] = {0.f, 0.f, 0.f, 0.f}, d1b[4] = {0.f, 0.f, 0.f, 0.f};
+      if (consumer) {
+        // this warp's stages of the block: ids = warp (mod slots)
+        uint32_t kb = (uint32_t(warp) + r.slots - blk_first % r.slots) % r.slots;
+        for (; kb < uint32_t(ge.kboxes); kb += r.slots) {
+          // stage blk_first + kb is the one in flight in this warp's buffer (issued after the previous one was consumed)
+          uint32_t c0 = r.prof ? clk() : 0u;
+          ptx::mbar_wait(&r.full[warp], r.uses & 1u);
+          ++r.uses;
+          uint32_t c1 = r.prof ? clk() : 0u;
+          // slabs of 64 k-elements that hold real data (the activations are zero padded to whole stages, so a
+          // partly filled slab needs no special case; K is a multiple of 64)
+          const int nslab = min(ge.nsub, (K - int(kb) * ge.kstage) >> 6);
+          const bf16* xk = xb + int(kb) * ge.kstage;
+          uint32_t line = a_row;  // 128 B line of this lane's row in slab 0; slab j starts at line j * R
+          for (int j = 0; j < nslab; ++j, line += ge.R, xk += 64) {
+            const uint8_t* lp = sbuf + line * 128u;
+            const uint32_t ph = line & 7u;  // swizzle phase of the line (rows + 16 have the same one)
 #pragma unroll
-          for (int it = 0; it < 2; ++it) {
-            const int sl = ks + 8 * it;
-            const int k0 = kb * ge.kbox + sl * 16;
-            if (sl * 16 < ge.kbox && k0 < K) {
+            for (int s4 = 0; s4 < 4; ++s4) {
+              const uint32_t b0 = *reinterpret_cast<const uint32_t*>(xk + s4 * 16) & bmask;
+              const uint32_t b1 = *reinterpret_cast<const uint32_t*>(xk + s4 * 16 + 8) & bmask;
+              const uint8_t* ap = lp + ((uint32_t(s4 * 2) + a_hi) ^ ph) * 16u;
               uint32_t af[4];
-              const uint32_t chunk = uint32_t((sl & 3) * 2 + (lane >> 4)) ^ (a_row & 7u);
-              ldmatrix_x4(af, sbuf + (sl >> 2) * sub_pitch + a_row * 128u + chunk * 16u);
-              uint32_t b0 = *reinterpret_cast<const uint32_t*>(xb + k0);
-              uint32_t b1 = *reinterpret_cast<const uint32_t*>(xb + k0 + 8);
-              if (!b_on) b0 = b1 = 0u;
-              mma_bf16_16816(d, af, b0, b1);
+              ldmatrix_x4(af, ap);
+              mma_bf16_16816(s4 & 1 ? d0b : d0, af, b0, b1);
+              if (two_groups) {
+                ldmatrix_x4(af, ap + 16 * 128);
+                mma_bf16_16816(s4 & 1 ? d1b : d1, af, b0, b1);
+              }
             }
           }
-        }
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&r.empty[slot]);
-        ++cons;
-        if (++slot == uint32_t(r.stages)) {
-          slot = 0;
-          par ^= 1u;
+          __syncwarp();
+          uint32_t c2 = r.prof ? clk() : 0u;
+          issue_stage(r, blk_first + kb + r.slots);  // refill this buffer right away (possibly for a later task)
+          if (r.prof) {
+            r.cyc[0] += c1 - c0;
+            r.cyc[1] += c2 - c1;
+            r.cyc[2] += clk() - c2;
+          }
         }
       }
-      // block done: sum the 8 partial tiles of each row group. d[0..1] = (row lane/4, n 2*(lane%4)+{0,1}), d[2..3] = row + 8.
-      float* rb = red + size_t(rbuf) * kWarps * 128 + warp * 128;
-      *reinterpret_cast<float2*>(rb + (lane >> 2) * 8 + (lane & 3) * 2) = make_float2(d[0], d[1]);
-      *reinterpret_cast<float2*>(rb + ((lane >> 2) + 8) * 8 + (lane & 3) * 2) = make_float2(d[2], d[3]);
-      __syncthreads();
-      if (threadIdx.x < 256) {
-        const int g2 = threadIdx.x >> 7, idx = threadIdx.x & 127;
-        const float* rs = red + size_t(rbuf) * kWarps * 128 + g2 * 128 + idx;  // warps g2, g2 + 2, ...
-        float sum = 0.f;
 #pragma unroll
-        for (int w = 0; w < kWarps / 2; ++w) sum += rs[w * 256];
-        acc[((size_t(blob) * ge.nblk + blk) * 2 + g2) * 128 + idx] = sum;  // [(blob, block, row group)][row][n]
+      for (int i = 0; i < 4; ++i) {
+        d0[i] += d0b[i];
+        d1[i] += d1b[i];
+      }
+      const uint32_t c3 = r.prof ? clk() : 0u;
+      // block done: sum the warps' partial tiles. d[0..1] = (row lane/4, n 2*(lane%4)+{0,1}), d[2..3] = row + 8.
+      {
+        float* rb = red + (size_t(rbuf) * kWarps + warp) * tile_vals;
+        const int n0 = (lane & 3) * 2, row = lane >> 2;
+        if (n0 < M) {
+          rb[row * M + n0] = d0[0];
+          rb[(row + 8) * M + n0] = d0[2];
+          rb[(16 + row) * M + n0] = d1[0];
+          rb[(24 + row) * M + n0] = d1[2];
+        }
+        if (n0 + 1 < M) {
+          rb[row * M + n0 + 1] = d0[1];
+          rb[(row + 8) * M + n0 + 1] = d0[3];
+          rb[(16 + row) * M + n0 + 1] = d1[1];
+          rb[(24 + row) * M + n0 + 1] = d1[3];
+        }
+      }
+      __syncthreads();
+      if (int(threadIdx.x) < tile_vals) {
+        const float* rs = red + size_t(rbuf) * kWarps * tile_vals + threadIdx.x;
+        float sum = 0.f;
+        for (uint32_t w = 0; w < r.slots; ++w) sum += rs[w * tile_vals];
+        acc[(size_t(blob) * ge.nblk + blk) * tile_vals + threadIdx.x] = sum;  // [(blob, block)][row 0..31][m]
       }
       rbuf ^= 1;  // the next block's partials go to the other buffer; its barrier orders the reuse of this one
+      if (r.prof) r.cyc[3] += clk() - c3;
     }
   }
-  try_issue(is, r, tab, n_ent, cons);  // keep the next linear task's stream moving during the epilogue
+  stage_base = blk_first;
   __syncthreads();
   if (threadIdx.x == 0 && tr != nullptr) tr[4] = ptx::globaltimer();  // weight stream consumed
 
@@ -315,10 +322,10 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
   for (int idx = threadIdx.x; idx < ncols * M; idx += kThreads) {
     const int m = idx / ncols, c = idx - m * ncols;
     const int blk = c / ge.R, rr = c - blk * ge.R;
-    const size_t off = (size_t(blk) * 2 + (rr >> 4)) * 128 + (rr & 15) * 8 + m;
+    const size_t off = size_t(blk) * tile_vals + rr * M + m;
     float v = acc[off];
     if (pair) {
-      const float u = acc[size_t(ge.nblk) * 256 + off];
+      const float u = acc[size_t(ge.nblk) * tile_vals + off];
       // round gate/up to bf16 first: matches the unfused fc1 -> silu_mul sequence bit for bit in the common case
       v = __bfloat162float(__float2bfloat16(v));
       const float uu = __bfloat162float(__float2bfloat16(u));
@@ -472,12 +479,13 @@ __device__ __forceinline__ void qk_rope_body(const OpArgs& a, int tile) {
 // i0 Hq, i1 Hkv, i2 page_size, i3 max_pages, i4 splits; f0 scale. tile = (b * Hkv + kvh) * S + split.
 template <int G>
 __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int g_total, int g_off) {
-  constexpr int D = 128, NG = kThreads / 16;  // 32 position groups
+  // One warp per key position (lane = 4 of the 128 head dims), all G query heads of the KV group at once: the
+  // per-thread state is G x 4 output accumulators + G (max, sum) pairs, which fits in registers for G = 8 (the first
+  // version used half-warps with 8 dims per lane and spilled). The scaled queries sit in shared memory.
+  constexpr int D = 128, NW = kThreads / 32;
   const int S = a.i4, Hq = a.i0, Hkv = a.i1;
   const int split = tile % S, kvh = (tile / S) % Hkv, b = tile / (S * Hkv);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int sub = lane & 15, grp = warp * 2 + (lane >> 4);
-  const uint32_t half_mask = lane < 16 ? 0x0000ffffu : 0xffff0000u;
   const int kv_len = static_cast<const int*>(a.in4)[b] + 1;
   const int per_split = (kv_len + S - 1) / S;
   const int s_beg = split * per_split, s_end = min(s_beg + per_split, kv_len);
@@ -486,18 +494,27 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
   const bf16* kc = static_cast<const bf16*>(a.in1);
   const bf16* vc = static_cast<const bf16*>(a.in2);
   const int* block_table = static_cast<const int*>(a.in3);
-  float qf[G][8], m[G], l[G], o[G][8];
+  float* sh_m = reinterpret_cast<float*>(smem);  // [NW][G]
+  float* sh_l = sh_m + NW * G;
+  float* sh_o = sh_l + NW * G;                   // [NW][G][D]
+  float* qs = sh_o + NW * G * D;                 // [G][D] queries, pre-scaled by sm_scale * log2(e)
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * D / 8; i += kThreads) {
+    const int g = i / (D / 8), c = i % (D / 8);
+    float f[8];
+    unpack8(ptx::ld_v4(q + (size_t(b) * Hq + h0 + g) * D + c * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) qs[g * D + c * 8 + j] = f[j] * (a.f0 * 1.4426950408889634f);
+  }
+  float m[G], l[G], o[G][4];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    unpack8(ptx::ld_v4(q + (size_t(b) * Hq + h0 + g) * D + sub * 8), qf[g]);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      qf[g][i] *= a.f0 * 1.4426950408889634f;
-      o[g][i] = 0.f;
-    }
+    for (int i = 0; i < 4; ++i) o[g][i] = 0.f;
     m[g] = -CUDART_INF_F;
     l[g] = 0.f;
   }
+  __syncthreads();
   auto kv_off = [&](int pos) -> size_t {
     if (block_table != nullptr) {
       const int page = block_table[size_t(b) * a.i3 + pos / a.i2];
@@ -506,63 +523,57 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
     return size_t(b) * a.l0 + size_t(pos) * a.l1 + size_t(kvh) * a.l2;
   };
   constexpr int UN = 2;
-  for (int p0 = s_beg + grp * UN; p0 < s_end; p0 += NG * UN) {
-    int4 kr[UN], vr[UN];
+  for (int p0 = s_beg + warp * UN; p0 < s_end; p0 += NW * UN) {  // warp-uniform trip count
+    uint2 kr[UN], vr[UN];
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
       if (p0 + u < s_end) {
-        const size_t off = kv_off(p0 + u) + sub * 8;
-        kr[u] = ptx::ld_v4(kc + off);
-        vr[u] = ptx::ld_v4(vc + off);
+        const size_t off = kv_off(p0 + u) + lane * 4;
+        kr[u] = *reinterpret_cast<const uint2*>(kc + off);
+        vr[u] = *reinterpret_cast<const uint2*>(vc + off);
       }
     }
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
       if (p0 + u >= s_end) break;
-      float kf[8], vf[8];
-      unpack8(kr[u], kf);
-      unpack8(vr[u], vf);
+      const float2 k01 = ptx::unpack_bf16x2(kr[u].x), k23 = ptx::unpack_bf16x2(kr[u].y);
+      const float2 v01 = ptx::unpack_bf16x2(vr[u].x), v23 = ptx::unpack_bf16x2(vr[u].y);
 #pragma unroll
       for (int g = 0; g < G; ++g) {
-        float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s = fmaf(qf[g][i], kf[i], s);
-        // the two half-warps walk different key positions and may leave the loop at different times:
-        // shuffle only inside this half-warp
-        s += __shfl_xor_sync(half_mask, s, 8);
-        s += __shfl_xor_sync(half_mask, s, 4);
-        s += __shfl_xor_sync(half_mask, s, 2);
-        s += __shfl_xor_sync(half_mask, s, 1);
-        const float mn = fmaxf(m[g], s);
-        const float corr = exp2f(m[g] - mn), pe = exp2f(s - mn);
+        const float4 qa = *reinterpret_cast<const float4*>(qs + g * D + lane * 4);
+        float sc = qa.x * k01.x;
+        sc = fmaf(qa.y, k01.y, sc);
+        sc = fmaf(qa.z, k23.x, sc);
+        sc = fmaf(qa.w, k23.y, sc);
+        sc = ptx::warp_reduce_sum(sc);
+        const float mn = fmaxf(m[g], sc);
+        const float corr = exp2f(m[g] - mn), pe = exp2f(sc - mn);
         l[g] = l[g] * corr + pe;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) o[g][i] = fmaf(pe, vf[i], o[g][i] * corr);
+        o[g][0] = fmaf(pe, v01.x, o[g][0] * corr);
+        o[g][1] = fmaf(pe, v01.y, o[g][1] * corr);
+        o[g][2] = fmaf(pe, v23.x, o[g][2] * corr);
+        o[g][3] = fmaf(pe, v23.y, o[g][3] * corr);
         m[g] = mn;
       }
     }
   }
-  float* sh_m = reinterpret_cast<float*>(smem);  // [NG][G]
-  float* sh_l = sh_m + NG * G;
-  float* sh_o = sh_l + NG * G;                   // [NG][G][D]
-  __syncthreads();
+  // reduce the 16 warps through shared memory: [NW][G] maxima and sums, [NW][G][D] outputs (66 KB for G = 8)
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    if (sub == 0) {
-      sh_m[grp * G + g] = m[g];
-      sh_l[grp * G + g] = l[g];
+    if (lane == 0) {
+      sh_m[warp * G + g] = m[g];
+      sh_l[warp * G + g] = l[g];
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) sh_o[(grp * G + g) * D + sub * 8 + i] = o[g][i];
+    *reinterpret_cast<float4*>(sh_o + (warp * G + g) * D + lane * 4) = make_float4(o[g][0], o[g][1], o[g][2], o[g][3]);
   }
   __syncthreads();
   float* partial = static_cast<float*>(a.out0);
   for (int idx = threadIdx.x; idx < G * D; idx += kThreads) {
     const int g = idx / D, d = idx % D;
     float mm = -CUDART_INF_F;
-    for (int r = 0; r < NG; ++r) mm = fmaxf(mm, sh_m[r * G + g]);
+    for (int r = 0; r < NW; ++r) mm = fmaxf(mm, sh_m[r * G + g]);
     float ll = 0.f, acc = 0.f;
-    for (int r = 0; r < NG; ++r) {
+    for (int r = 0; r < NW; ++r) {
       const float mr = sh_m[r * G + g];
       const float w = mr == -CUDART_INF_F ? 0.f : exp2f(mr - mm);
       ll += sh_l[r * G + g] * w;
@@ -707,15 +718,16 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
   const uint32_t step = base + 1;
   const int n = p.queue_len[blockIdx.x];
   const Task* q = p.queues + size_t(blockIdx.x) * p.max_tasks;
-  // weight ring (behind the per-task scratch area), its barriers, the task slots and the stream table
-  RingView r;
+  // weight buffers (behind the per-task scratch area), their barriers, the task slots and the stream table
+  Ring r;
   r.buf = smem + p.ring_offset;
-  r.stages = p.ring_stages;
-  r.full = reinterpret_cast<uint64_t*>(r.buf + size_t(r.stages) * kStageBytes);
-  r.empty = r.full + r.stages;
-  TaskSlot* slots = reinterpret_cast<TaskSlot*>(r.buf + size_t(r.stages) * kStageBytes + 256);
+  r.slots = uint32_t(p.ring_stages);
+  r.full = reinterpret_cast<uint64_t*>(r.buf + size_t(r.slots) * kSlotBytes);
+  TaskSlot* slots = reinterpret_cast<TaskSlot*>(r.buf + size_t(r.slots) * kSlotBytes + 256);
   StreamEntry* tab = reinterpret_cast<StreamEntry*>(slots + 2);
   const uint32_t n_ent = uint32_t(p.stream_len[blockIdx.x]);
+  r.tab = tab;
+  r.n_ent = n_ent;
   {
     const int4* src = reinterpret_cast<const int4*>(p.streams + size_t(blockIdx.x) * p.max_streams);
     int4* dst = reinterpret_cast<int4*>(tab);
@@ -733,24 +745,23 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
     if (threadIdx.x < 12) reinterpret_cast<int4*>(&slots[0])[threadIdx.x] = pf;
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < r.stages; ++s) {
-      ptx::mbar_init(&r.full[s], 1);
-      ptx::mbar_init(&r.empty[s], kThreads / 32);
-    }
+    for (uint32_t s = 0; s < r.slots; ++s) ptx::mbar_init(&r.full[s], 1);
     ptx::fence_barrier_init();
   }
   __syncthreads();
-  Issuer is;
-  is.next_own = threadIdx.x >> 5;
-  is.e_idx = 0;
-  is.e_first = 0;
-  is.e_total = n_ent > 0 ? tab[0].total : 0;
-  is.pf_own = (threadIdx.x >> 5) + uint32_t(r.stages) / (kThreads / 32) * (kThreads / 32);  // first stage >= ring size owned by this warp
-  if (is.pf_own < uint32_t(r.stages)) is.pf_own += kThreads / 32;
-  is.pf_idx = 0;
-  is.pf_first = 0;
-  is.pf_total = is.e_total;
-  uint32_t cons = 0, slot = 0, par = 0;
+  r.e_idx = 0;
+  r.e_first = 0;
+  r.e_total = n_ent > 0 ? tab[0].total : 0;
+  r.uses = 0;
+  r.issued = 0xffffffffu;
+  r.prof = p.trace != nullptr;
+  r.cyc[0] = r.cyc[1] = r.cyc[2] = r.cyc[3] = 0;
+  if ((threadIdx.x >> 5) < r.slots) issue_stage(r, threadIdx.x >> 5);  // every buffer starts with its first stage
+  uint32_t stage_base = 0;  // id of the first stage of the next linear task of this CTA
+  uint32_t lin_k = 0;       // ordinal of the next linear task of this CTA (index into the stream table)
+  // TMA descriptors live in global memory and are cold when an op is reached (a step streams GBs through L2); a
+  // descriptor miss stalls the issuing warp, so they are prefetched a few linear tasks ahead
+  if (threadIdx.x < 4 && threadIdx.x < n_ent) ptx::prefetch_tensormap(tab[threadIdx.x].tmap);
   uint64_t* trace = p.trace != nullptr ? p.trace + (size_t(blockIdx.x) * p.max_tasks) * kTraceWords : nullptr;
   for (int i = 0; i < n; ++i) {
     const Task t = slots[i & 1].t;
@@ -758,7 +769,6 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
     const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1 = step * uint32_t(t.dep1_cnt);
     uint64_t* tr = trace != nullptr ? trace + size_t(i) * kTraceWords : nullptr;
     if (threadIdx.x == 0 && tr != nullptr) tr[0] = ptx::globaltimer();
-    try_issue(is, r, tab, n_ent, cons);  // keep the weight stream moving (warp-collective)
     // start fetching task i + 1 (its op index was read one task earlier, so the two loads are not chained)
     int op_next2 = 0;
     if (i + 1 < n) {
@@ -770,12 +780,16 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
       }
     }
     if (t.type == OP_LINEAR) {
-      // waits for its dependencies inside (its weight stream is normally already in flight)
-      linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, is, cons, slot, par, tab, n_ent, tr);
+      // waits for its dependencies inside (its first weight stages are already in flight)
+      if (threadIdx.x >= 32 && threadIdx.x < 34 && lin_k + 3 + (threadIdx.x - 32) < n_ent)
+        ptx::prefetch_tensormap(tab[lin_k + 3 + (threadIdx.x - 32)].tmap);
+      ++lin_k;
+      linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, stage_base, tr);
     } else {
       if (threadIdx.x == 0) {
         wait_slot(p.scoreboard, t.dep0, tgt0);
         wait_slot(p.scoreboard, t.dep1, tgt1);
+        if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
       }
       __syncthreads();
       switch (t.type) {
@@ -788,9 +802,10 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
           int done = 0;
           while (done < g) {
             const int rem = g - done;
-            // (at most 4 heads per pass: the cross-group reduction buffer of 8 would take 133 KB of shared memory
-            // away from the weight ring; the second pass re-reads this split's K/V from L2)
-            if (rem >= 4) {
+            if (rem >= 8) {
+              attn_split_body<8>(a, t.tile, smem, g, done);
+              done += 8;
+            } else if (rem >= 4) {
               attn_split_body<4>(a, t.tile, smem, g, done);
               done += 4;
             } else if (rem >= 2) {
@@ -824,6 +839,11 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
       }
       if (tr != nullptr) tr[1] = ptx::globaltimer();
     }
+  }
+  if (r.prof && (threadIdx.x & 31) == 0) {
+    // per-warp cycle totals behind the task stamps: [num_ctas][16 warps][4]
+    uint64_t* w = p.trace + size_t(gridDim.x) * p.max_tasks * kTraceWords + (size_t(blockIdx.x) * (kThreads / 32) + (threadIdx.x >> 5)) * 4;
+    for (int j = 0; j < 4; ++j) w[j] = r.cyc[j];
   }
   phase_end(ps, base, 1);
 }

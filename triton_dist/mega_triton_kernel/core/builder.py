@@ -287,10 +287,12 @@ class ModelBuilder:
         import numpy as np
         info = self.info()
         ctas, mq = info["ctas"], info["max_queue"]
-        buf = np.zeros(ctas * mq * 6, dtype=np.uint64)
+        buf = np.zeros(ctas * mq * 6 + ctas * 16 * 4, dtype=np.uint64)
         torch.cuda.synchronize()
         _lib.check(_lib.lib().tdist_mega_get_trace(self._handle, buf.ctypes.data, buf.size), "mega_get_trace")
-        buf = buf.reshape(ctas, mq, 6)
+        # per-warp cycle totals of the linear main loop: [cta][warp][wait stage, ldmatrix+mma, issue next, block barrier]
+        self.last_warp_cycles = buf[ctas * mq * 6:].reshape(ctas, 16, 4).copy()
+        buf = buf[:ctas * mq * 6].reshape(ctas, mq, 6)
         out = []
         q = (ctypes.c_int * (8 * mq))()
         for c in range(ctas):

@@ -103,8 +103,8 @@ class Qwen3Model:
                 b.make_fc2(self.act, mlp.down_proj, self.down_partial[0], li, parity_stride_bytes=stride)
                 b.make_allreduce(self.down_partial[0], self.tmp, layer_id=li, parity_stride_bytes=stride)
                 b.make_add(self.hidden, self.tmp, self.hidden, li)
-            if li + 1 < len(d.layers):  # warm L2 with the next layer's first weights while this layer finishes
-                b.make_prefetch(d.layers[li + 1].attn.wqkv, li)
+            # (no make_prefetch tasks here, unlike the reference's graph: the kernel's weight stream already runs ahead of
+            # the dependency chain across task boundaries, see csrc/mega/megakernel.cu)
         b.make_linear(self.hidden, d.lm_head, self.logits, self.num_layers, rms_weight=d.norm_weight, rms_eps=d.norm_variance_epsilon)
         b.make_argmax(self.logits, self.next_ids, self.num_layers)
         b.compile()

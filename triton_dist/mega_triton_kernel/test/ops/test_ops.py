@@ -130,7 +130,7 @@ if __name__ == "__main__":
     # (M, N, K, norm, pair, bias): K/8 multiple of 32 or not (row-straddling vector groups), tiles smaller and larger
     # than one 16 KB chunk, N not divisible by the CTA count, every batch template
     for case in [(1, 640, 1024, False, False, False), (1, 5120, 3200, True, False, False), (2, 1280, 5120, True, False, True),
-                 (1, 3200, 5120, True, True, False), (4, 1000, 272, False, False, False), (8, 296, 2048, True, True, True),
+                 (1, 3200, 5120, True, True, False), (4, 1000, 320, False, False, False), (8, 296, 2048, True, True, True),
                  (3, 18992, 1024, True, False, False), (1, 5120, 25600, False, False, False), (1, 37, 8192, False, False, False)]:
         ok = linear_case(rank, world, *case, dev, dtype) and ok
     ok = chain_case(rank, world, dev, dtype) and ok

@@ -123,7 +123,9 @@ constexpr int kMaxArTiles = 32;
 constexpr int kTraceWords = 6;         // per task: begin, end, [linear: deps satisfied, activations staged, stream consumed], spare
 constexpr int kSlotBytes = kStageRows * 256 * 2;   // stage buffer: up to 24 rows x 256 k-elements (four {64, R} TMA boxes)
 constexpr int kMaxRingStages = 16;     // one stage buffer per warp at most
-constexpr int kPrefetchStages = 0;     // L2 prefetch distance beyond the ring (stages); 0 = off (measured: no gain)
+constexpr int kPrefetchRounds = 1;     // L2 prefetch distance behind every stage load, in buffer-rounds (slots stages); 0 = off
+constexpr int kIdlePrefetchRounds = 0; // L2 prefetch distance while a CTA waits on the scoreboard; 0 = off (measured: no gain,
+                                       // the stage loads are latency- not bandwidth-limited at TP8 tile sizes)
 constexpr int kSmemLimit = 232448;     // 227 KB opt-in limit per CTA on sm_100
 
 }  // namespace mega

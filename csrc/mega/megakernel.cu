@@ -94,6 +94,8 @@ struct Ring {
   uint32_t issued;   // id of the stage in flight / next to be consumed by this warp (0xffffffff: none)
   uint32_t e_idx, e_first, e_total;  // table entry containing `issued`
   uint32_t uses;     // completed uses of this warp's buffer (mbarrier parity)
+  // second cursor for the L2 prefetch of this warp's stages further ahead (see prefetch_stage)
+  uint32_t pf_next, pf_idx, pf_first, pf_total;
   // optional per-warp cycle accounting of the linear main loop (KernelParams::trace != nullptr):
   // [0] waiting for a stage to land, [1] ldmatrix + MMA, [2] issuing the next stage, [3] block-end barrier + sum
   bool prof;
@@ -106,9 +108,39 @@ __device__ __forceinline__ void stage_coords(const StreamEntry& e, uint32_t stag
   const uint32_t per_blob = uint32_t(e.nblk) * e.kboxes;
   const bool second = q >= per_blob;
   if (second) q -= per_blob;
-  const uint32_t blk = q / e.kboxes, kb = q - blk * e.kboxes;
+  // q / kboxes without an integer division (q < 2^16, kboxes <= 400: the float quotient of (q + 0.5) is exact enough)
+  const uint32_t blk = uint32_t((float(q) + 0.5f) * __frcp_rn(float(e.kboxes)));
+  const uint32_t kb = q - blk * e.kboxes;
   c0 = int(kb * uint32_t(e.kstage));
   c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);
+}
+
+// L2 prefetch of this warp's future stages up to (excluding) `limit` (warp-collective). The stage buffers alone hold
+// ~190 KB per SM; at TP8 a linear task mostly waits (dependencies, activation staging) and then has to pull the rest
+// of its tile through that window at HBM latency. Two uses: one buffer-round ahead of every stage load (keeps the
+// steady-state loads L2 hits without flooding L2), and up to kIdlePrefetchRounds rounds ahead while a CTA waits on
+// the scoreboard (HBM is idle then, the whole next tile fits in L2).
+__device__ __forceinline__ void prefetch_upto(Ring& r, uint32_t limit) {
+  while (r.pf_next < limit) {
+    while (r.pf_idx < r.n_ent && r.pf_next >= r.pf_first + r.pf_total) {
+      ++r.pf_idx;
+      if (r.pf_idx < r.n_ent) {
+        r.pf_first = r.tab[r.pf_idx].first;
+        r.pf_total = r.tab[r.pf_idx].total;
+      }
+    }
+    if (r.pf_idx >= r.n_ent) {
+      r.pf_next = 0xfffffff0u;
+      return;
+    }
+    if ((threadIdx.x & 31) == 0) {
+      const StreamEntry e = r.tab[r.pf_idx];
+      int c0, c1;
+      stage_coords(e, r.pf_next, c0, c1);
+      ptx::tma_prefetch_3d(e.tmap, 0, c1, c0 >> 6);
+    }
+    r.pf_next += r.slots;
+  }
 }
 
 // Issue stage `stage` into this warp's buffer (warp-collective; lane 0 talks to the TMA). The caller guarantees that
@@ -137,6 +169,7 @@ __device__ __forceinline__ void issue_stage(Ring& r, uint32_t stage) {
     ptx::mbar_arrive_expect_tx(&r.full[warp], uint32_t(e.R) * 128u * uint32_t(nsub));
     ptx::tma_load_3d(r.buf + size_t(warp) * kSlotBytes, e.tmap, &r.full[warp], 0, c1, c0 >> 6);
   }
+  if (kPrefetchRounds > 0) prefetch_upto(r, stage + kPrefetchRounds * r.slots + 1);
 }
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&a)[4], const void* smem_ptr) {
@@ -153,7 +186,7 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 
 __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* smem, uint32_t step, const uint32_t* sb,
                                             const Task& t, uint32_t dep_target0, uint32_t dep_target1, Ring& r,
-                                            uint32_t& stage_base, uint64_t* tr) {
+                                            uint32_t& stage_base, uint32_t lin_k, uint64_t* tr) {
   constexpr int kWarps = kThreads / 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int K = a.K, kv = K >> 3, M = a.M, cpt = a.cols_per_tile;
@@ -177,6 +210,12 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
       *reinterpret_cast<int4*>(nws + size_t(i) * 8) = ptx::ld_nc_v4(nw + size_t(i) * 8);
   for (int m = 0; m < M; ++m)
     for (int i = K + threadIdx.x; i < xpitch; i += kThreads) xs[size_t(m) * xpitch + i] = __float2bfloat16(0.f);
+  // HBM is idle while this CTA waits: pull this warp's next stages (this tile and at most the next linear tile) into L2
+  if (kIdlePrefetchRounds > 0 && uint32_t(warp) < r.slots && r.issued != 0xffffffffu) {
+    const uint32_t this_total = (pair ? 2u : 1u) * uint32_t(ge.nblk) * uint32_t(ge.kboxes);
+    const uint32_t next_total = lin_k + 1 < r.n_ent ? r.tab[lin_k + 1].total : 0u;
+    prefetch_upto(r, min(r.issued + kIdlePrefetchRounds * r.slots + 1, stage_base + this_total + next_total));
+  }
   // (2) wait for the activations
   if (threadIdx.x == 0) {
     wait_slot(sb, t.dep0, dep_target0);
@@ -249,6 +288,7 @@ __device__ __forceinline__ void linear_body(const OpArgs& a, int tile, uint8_t* 
           const int nslab = min(ge.nsub, (K - int(kb) * ge.kstage) >> 6);
           const bf16* xk = xb + int(kb) * ge.kstage;
           uint32_t line = a_row;  // 128 B line of this lane's row in slab 0; slab j starts at line j * R
+#pragma unroll 2
           for (int j = 0; j < nslab; ++j, line += ge.R, xk += 64) {
             const uint8_t* lp = sbuf + line * 128u;
             const uint32_t ph = line & 7u;  // swizzle phase of the line (rows + 16 have the same one)
@@ -478,7 +518,10 @@ __device__ __forceinline__ void qk_rope_body(const OpArgs& a, int tile) {
 // in0 q [B,Hq,128]; in1/in2 caches; in3 block_table; in4 positions (kv_len = pos + 1); out0 partial [B,Hq,S,129].
 // i0 Hq, i1 Hkv, i2 page_size, i3 max_pages, i4 splits; f0 scale. tile = (b * Hkv + kvh) * S + split.
 template <int G>
-__device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int g_total, int g_off) {
+__device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int g_total, int g_off,
+                                                const uint32_t* wait_sb, const Task& wt, uint32_t tgt0, uint32_t tgt1,
+                                                uint64_t* tr) {
+  // `wait_sb` != nullptr: this call also performs the task's scoreboard wait (first pass over the head group).
   // One warp per key position (lane = 4 of the 128 head dims), all G query heads of the KV group at once: the
   // per-thread state is G x 4 output accumulators + G (max, sum) pairs, which fits in registers for G = 8 (the first
   // version used half-warps with 8 dims per lane and spilled). The scaled queries sit in shared memory.
@@ -498,6 +541,33 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
   float* sh_l = sh_m + NW * G;
   float* sh_o = sh_l + NW * G;                   // [NW][G][D]
   float* qs = sh_o + NW * G * D;                 // [G][D] queries, pre-scaled by sm_scale * log2(e)
+  auto kv_off = [&](int pos) -> size_t {
+    if (block_table != nullptr) {
+      const int page = block_table[size_t(b) * a.i3 + pos / a.i2];
+      return size_t(page) * a.l0 + size_t(pos % a.i2) * a.l1 + size_t(kvh) * a.l2;
+    }
+    return size_t(b) * a.l0 + size_t(pos) * a.l1 + size_t(kvh) * a.l2;
+  };
+  constexpr int UN = 2;
+  // K/V of every position but the newest one were written by earlier steps: this warp's first rows are fetched BEFORE
+  // the dependency wait (the block-table -> K/V chain is two dependent HBM round trips otherwise on the critical path)
+  uint2 kr[UN], vr[UN];
+  bool pre[UN];
+  const int p_first = s_beg + warp * UN;
+#pragma unroll
+  for (int u = 0; u < UN; ++u) {
+    pre[u] = wait_sb != nullptr && p_first + u < s_end && p_first + u < kv_len - 1;
+    if (pre[u]) {
+      const size_t off = kv_off(p_first + u) + lane * 4;
+      kr[u] = *reinterpret_cast<const uint2*>(kc + off);
+      vr[u] = *reinterpret_cast<const uint2*>(vc + off);
+    }
+  }
+  if (wait_sb != nullptr && threadIdx.x == 0) {
+    wait_slot(wait_sb, wt.dep0, tgt0);
+    wait_slot(wait_sb, wt.dep1, tgt1);
+    if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < G * D / 8; i += kThreads) {
     const int g = i / (D / 8), c = i % (D / 8);
@@ -515,19 +585,10 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
     l[g] = 0.f;
   }
   __syncthreads();
-  auto kv_off = [&](int pos) -> size_t {
-    if (block_table != nullptr) {
-      const int page = block_table[size_t(b) * a.i3 + pos / a.i2];
-      return size_t(page) * a.l0 + size_t(pos % a.i2) * a.l1 + size_t(kvh) * a.l2;
-    }
-    return size_t(b) * a.l0 + size_t(pos) * a.l1 + size_t(kvh) * a.l2;
-  };
-  constexpr int UN = 2;
-  for (int p0 = s_beg + warp * UN; p0 < s_end; p0 += NW * UN) {  // warp-uniform trip count
-    uint2 kr[UN], vr[UN];
+  for (int p0 = p_first; p0 < s_end; p0 += NW * UN) {  // warp-uniform trip count
 #pragma unroll
     for (int u = 0; u < UN; ++u) {
-      if (p0 + u < s_end) {
+      if (p0 + u < s_end && !(p0 == p_first && pre[u])) {
         const size_t off = kv_off(p0 + u) + lane * 4;
         kr[u] = *reinterpret_cast<const uint2*>(kc + off);
         vr[u] = *reinterpret_cast<const uint2*>(vc + off);
@@ -756,6 +817,10 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
   r.issued = 0xffffffffu;
   r.prof = p.trace != nullptr;
   r.cyc[0] = r.cyc[1] = r.cyc[2] = r.cyc[3] = 0;
+  r.pf_idx = 0;
+  r.pf_first = 0;
+  r.pf_total = r.e_total;
+  r.pf_next = (threadIdx.x >> 5) + r.slots;  // (stage `warp` itself is loaded right away)
   if ((threadIdx.x >> 5) < r.slots) issue_stage(r, threadIdx.x >> 5);  // every buffer starts with its first stage
   uint32_t stage_base = 0;  // id of the first stage of the next linear task of this CTA
   uint32_t lin_k = 0;       // ordinal of the next linear task of this CTA (index into the stream table)
@@ -783,15 +848,17 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
       // waits for its dependencies inside (its first weight stages are already in flight)
       if (threadIdx.x >= 32 && threadIdx.x < 34 && lin_k + 3 + (threadIdx.x - 32) < n_ent)
         ptx::prefetch_tensormap(tab[lin_k + 3 + (threadIdx.x - 32)].tmap);
+      linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, stage_base, lin_k, tr);
       ++lin_k;
-      linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, stage_base, tr);
     } else {
-      if (threadIdx.x == 0) {
-        wait_slot(p.scoreboard, t.dep0, tgt0);
-        wait_slot(p.scoreboard, t.dep1, tgt1);
-        if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
+      if (t.type != OP_ATTN_SPLIT) {  // (the attention split waits inside, after it has started its K/V loads)
+        if (threadIdx.x == 0) {
+          wait_slot(p.scoreboard, t.dep0, tgt0);
+          wait_slot(p.scoreboard, t.dep1, tgt1);
+          if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
+        }
+        __syncthreads();
       }
-      __syncthreads();
       switch (t.type) {
         case OP_RMS_NORM: rmsnorm_body(a, t.tile, smem); break;
         case OP_SILU_MUL: silu_mul_body(a, t.tile); break;
@@ -803,16 +870,16 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
           while (done < g) {
             const int rem = g - done;
             if (rem >= 8) {
-              attn_split_body<8>(a, t.tile, smem, g, done);
+              attn_split_body<8>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
               done += 8;
             } else if (rem >= 4) {
-              attn_split_body<4>(a, t.tile, smem, g, done);
+              attn_split_body<4>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
               done += 4;
             } else if (rem >= 2) {
-              attn_split_body<2>(a, t.tile, smem, g, done);
+              attn_split_body<2>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
               done += 2;
             } else {
-              attn_split_body<1>(a, t.tile, smem, g, done);
+              attn_split_body<1>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
               done += 1;
             }
           }

@@ -215,6 +215,9 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
 // grid after its GEMM work, so the tail runs at full HBM bandwidth.
 template <typename Tag>
 __device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epoch) {
+  // Work unit = (128-row block j of my segment, 128-column slice): units are independent, so the tail is not a chain
+  // of (flag wait -> barrier -> one load round trip) per block any more (measured: ~3 us per block, 32 blocks at
+  // TP2). Every thread keeps W x 4 sixteen-byte loads in flight.
   const int W = p.ctx.world;
   const int bps = blocks_per_shard(p);
   const int parity = (epoch >> 1) & 1;
@@ -222,18 +225,47 @@ __device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epo
   const int4* scat = reinterpret_cast<const int4*>(static_cast<const char*>(p.c) + size_t(parity) * W * seg_elems * 2);
   int4* out = static_cast<int4*>(p.out);
   const size_t seg_vecs = seg_elems / 8;
-  for (int j = 0; j < bps; ++j) {
-    // flags layout (RS): [W src][bps], written by src when its block j of my segment is complete
-    if (threadIdx.x < W) wait_ge_sys(p.flags + threadIdx.x * bps + j, epoch);
-    __syncthreads();
+  const int row_vecs = p.N / 8;                 // 16-byte vectors per row
+  constexpr int kSliceVecs = 16;                // 128 columns
+  const int slices = (row_vecs + kSliceVecs - 1) / kSliceVecs;
+  const int units = bps * slices;
+  int last_j = -1;
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int j = u / slices, sl = u - j * slices;
+    if (j != last_j) {
+      // flags layout (RS): [W src][bps], written by src when its block j of my segment is complete
+      if (threadIdx.x < W) wait_ge_sys(p.flags + threadIdx.x * bps + j, epoch);
+      __syncthreads();
+      last_j = j;
+    }
     const int rows = min(kBlockM, p.rows_per_rank - j * kBlockM);
-    const size_t blk_vecs = size_t(rows) * p.N / 8;
-    const size_t base = size_t(j) * kBlockM * p.N / 8;
-    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < blk_vecs; i += size_t(gridDim.x) * blockDim.x) {
-      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 1
-      for (int s = 0; s < W; ++s) Pack<Tag>::add(acc, ptx::ld_v4(scat + size_t(s) * seg_vecs + base + i));
-      out[base + i] = Pack<Tag>::cvt(acc);
+    const int v0 = sl * kSliceVecs, nv = min(kSliceVecs, row_vecs - v0);
+    const int total = rows * nv;
+    constexpr int kBatch = 4;
+    for (int i0 = threadIdx.x; i0 < total; i0 += blockDim.x * kBatch) {
+      size_t off[kBatch];
+      float acc[kBatch][8];
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        const int i = i0 + b * blockDim.x;
+        const int r = i / nv, c = i - r * nv;
+        off[b] = (size_t(j) * kBlockM + r) * row_vecs + v0 + c;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[b][e] = 0.f;
+      }
+#pragma unroll 2
+      for (int sidx = 0; sidx < W; ++sidx) {
+        int4 v[kBatch];
+#pragma unroll
+        for (int b = 0; b < kBatch; ++b)
+          if (i0 + b * blockDim.x < total) v[b] = ptx::ld_v4(scat + size_t(sidx) * seg_vecs + off[b]);
+#pragma unroll
+        for (int b = 0; b < kBatch; ++b)
+          if (i0 + b * blockDim.x < total) Pack<Tag>::add(acc[b], v[b]);
+      }
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b)
+        if (i0 + b * blockDim.x < total) out[off[b]] = Pack<Tag>::cvt(acc[b]);
     }
   }
 }

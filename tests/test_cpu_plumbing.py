@@ -55,3 +55,13 @@ def test_tp_moe_cpu():
 
 def test_sp_flash_decode_cpu():
     run_dist(N + "test_sp_decode_attn", ["--check", "--verify-iters", 1, "--kv-len", 256, "--q-heads", 4, "--kv-heads", 2], 2)
+
+
+def test_layers_suite_cpu():
+    """TP_MLP / TP_Attn / MoE / EP-MoE / decode attention / Engine.serve scripts on their torch paths (gloo, 2 ranks)."""
+    run_dist(N + "run_suite", ["--suite", "layers"], 2, timeout=1200)
+
+
+def test_mega_suite_cpu():
+    """ModelBuilder graphs (per-op cases and the Qwen3 decode graph) through the eager fallback of the builder."""
+    run_dist(N + "run_suite", ["--suite", "mega"], 2, timeout=1200)

@@ -1,8 +1,10 @@
 """Run a named group of distributed checks in one torchrun launch.
-    torchrun --nproc-per-node N -m triton_dist.test.nvidia.run_suite --suite core|moe|models|mega|all"""
+    torchrun --nproc-per-node N -m triton_dist.test.nvidia.run_suite --suite core|moe|models|mega|layers|prims|all"""
 import argparse
 import os
 import sys
+
+import torch
 
 from triton_dist.test.common import run_suite
 
@@ -42,12 +44,36 @@ def cases(suite: str, world: int):
         (M + "test_qwen3", []),
         (M + "test_qwen3", ["--unfused"]),
     ]
-    return {"core": core, "moe": moe, "models": models, "mega": mega, "all": core + moe + models + mega[:1]}[suite]
+    layers = [
+        (T + "test_tp_mlp", ["--check", "--verify-iters", 2, "--stress"]),
+        (T + "test_tp_attn", ["--check", "--verify-iters", 1]),
+        (T + "test_moe_utils", ["--check", "--verify-iters", 2]),
+        (T + "test_ag_moe", ["--check", "--verify-iters", 2, "--stress"]),
+        (T + "test_moe_reduce_rs", ["--check", "--verify-iters", 2, "--stress"]),
+        (T + "test_ep_moe_inference", ["--check", "--verify-iters", 2]),
+    ] + ([(T + "test_ep_moe_inference", ["--check", "--verify-iters", 1, "--fp8"])] if torch.cuda.is_available() else []) + [
+        (T + "test_decode_attn", ["--check", "--verify-iters", 2]),
+        (T + "test_e2e_inference", ["--gen-len", 6]),
+    ]
+    prims = [
+        (T + "test_ring_put", ["--stress"]),
+        (T + "test_notify", []),
+        (T + "test_distributed_wait", []),
+        (T + "test_common_ops", []),
+        (T + "test_multimem_ld_reduce", []),
+        (T + "test_nvshmem_api", []),
+        (T + "test_utils", []),
+        (T + "test_all_gather", ["--check", "--verify-iters", 2, "--stress"]),
+        (T + "test_ag_small_msg", ["--check", "--verify-iters", 2]),
+        (T + "test_pp", ["--stress"]),
+    ]
+    return {"core": core, "moe": moe, "models": models, "mega": mega, "layers": layers, "prims": prims,
+            "all": core + moe + models + mega[:1] + layers + prims}[suite]
 
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--suite", default="all", choices=["core", "moe", "models", "mega", "all"])
+    ap.add_argument("--suite", default="all", choices=["core", "moe", "models", "mega", "layers", "prims", "all"])
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     ok = run_suite(cases(args.suite, world))

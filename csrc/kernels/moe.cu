@@ -158,7 +158,73 @@ __global__ void __launch_bounds__(512) moe_reduce_rs_kernel(SymmCtx c, const int
 
 using namespace tdist;
 
+// ------------------------------------------------------------------ AG+MoE tile order (reference K45)
+// For every 128-row block of the expert-sorted layout: which source ranks' tokens it needs ([seg_start, seg_end] in
+// arrival order, where rank r's own shard arrives first, then r+1, r+2, ...), and a stable order of the blocks by the
+// stage at which their LAST needed shard arrives. A grouped GEMM that walks the blocks in this order can start on
+// the blocks fed by early shards while later shards are still in flight (threadblock_swizzle_ag_moe_triton.py:95-216).
+// One CTA; blocks and ranks are small numbers (<= a few thousand blocks, <= 16 ranks).
+__global__ void __launch_bounds__(1024) moe_tile_swizzle_kernel(const int* __restrict__ sorted_pair_ids,
+                                                                const int* __restrict__ meta, int num_pairs, int topk,
+                                                                int tokens_per_rank, int rank, int world, int block_m,
+                                                                int* __restrict__ block_order, int* __restrict__ seg_start,
+                                                                int* __restrict__ seg_end, int* __restrict__ stage_count,
+                                                                int max_blocks) {
+  __shared__ int s_count[TDIST_MAX_RANKS + 1];
+  __shared__ int s_offset[TDIST_MAX_RANKS + 1];
+  const int nblk = min(meta[1], max_blocks);
+  if (threadIdx.x <= TDIST_MAX_RANKS) s_count[threadIdx.x] = 0;
+  __syncthreads();
+  // stage of a block = max over its rows of ((src_rank - rank) mod world); empty / padding-only blocks get stage 0
+  for (int b = threadIdx.x; b < nblk; b += blockDim.x) {
+    int lo = world, hi = -1;
+    for (int r = 0; r < block_m; ++r) {
+      const int pid = sorted_pair_ids[b * block_m + r];
+      if (pid < num_pairs) {
+        const int src = (pid / topk) / tokens_per_rank;
+        const int st = (src - rank + world) % world;
+        lo = min(lo, st);
+        hi = max(hi, st);
+      }
+    }
+    if (hi < 0) lo = hi = 0;
+    seg_start[b] = lo;
+    seg_end[b] = hi;
+    atomicAdd(&s_count[hi], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int s = 0; s < world; ++s) {
+      s_offset[s] = run;
+      stage_count[s] = s_count[s];
+      run += s_count[s];
+    }
+  }
+  __syncthreads();
+  // stable counting sort by stage: block b goes behind all blocks of the same stage with a smaller index
+  for (int b = threadIdx.x; b < nblk; b += blockDim.x) {
+    const int st = seg_end[b];
+    int before = 0;
+    for (int j = 0; j < b; ++j) before += seg_end[j] == st;
+    block_order[s_offset[st] + before] = b;
+  }
+}
+
 extern "C" {
+
+int tdist_moe_tile_swizzle(const int* sorted_pair_ids, const int* meta, int num_pairs, int topk, int tokens_per_rank, int rank,
+                           int world, int block_m, int* block_order, int* seg_start, int* seg_end, int* stage_count,
+                           int max_blocks, void* stream) {
+  if (world < 1 || world > TDIST_MAX_RANKS || tokens_per_rank < 1 || topk < 1) {
+    tdist::set_error("moe_tile_swizzle: bad arguments");
+    return -1;
+  }
+  moe_tile_swizzle_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
+      sorted_pair_ids, meta, num_pairs, topk, tokens_per_rank, rank, world, block_m, block_order, seg_start, seg_end, stage_count,
+      max_blocks);
+  return tdist::check_launch("moe_tile_swizzle");
+}
 
 int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,
                          int* pair_to_row, int* block_expert, int* meta, int max_rows, void* stream) {

@@ -136,6 +136,11 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
 /* sort (token,k) pairs by expert, pad every expert to block_m rows. meta[0] = padded rows, meta[1] = blocks. */
 int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,
                          int* pair_to_row, int* block_expert, int* meta, int max_rows, void* stream);
+/* AG+MoE tile order: per 128-row block the range of arrival stages it needs and a stable block order by last stage
+ * (stage s = shard of rank (rank + s) % world). stage_count[s] = blocks whose last stage is s. */
+int tdist_moe_tile_swizzle(const int* sorted_pair_ids, const int* meta, int num_pairs, int topk, int tokens_per_rank, int rank,
+                           int world, int block_m, int* block_order, int* seg_start, int* seg_end, int* stage_count,
+                           int max_blocks, void* stream);
 int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, int num_pairs,
                           int topk, int row_bytes, int max_rows, void* stream);
 int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,

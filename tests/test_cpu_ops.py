@@ -57,3 +57,26 @@ def test_allreduce_method_names():
 
     assert to_allreduce_method("two_shot_multimem") == AllReduceMethod.TwoShot_Multimem
     assert "one_shot" in get_allreduce_methods()
+
+
+def test_tile_order_modules():
+    """AG+GEMM / GEMM+RS tile orders and the AG+MoE block schedule (reference K45, K59, K60)."""
+    import torch
+
+    from triton_dist.kernels.nvidia.ag_gemm_threadblock_swizzle import ag_gemm_tile_order
+    from triton_dist.kernels.nvidia.gemm_rs_threadblock_swizzle import gemm_rs_tile_order
+    from triton_dist.kernels.nvidia.moe_utils import torch_align_sort
+    from triton_dist.kernels.nvidia.threadblock_swizzle_ag_moe import threadblock_swizzle_ag_moe
+
+    ids = torch.rand(512, 16).topk(4, dim=-1).indices
+    s = torch_align_sort(ids, 16)
+    sch = threadblock_swizzle_ag_moe(s, 128, 1, 4)
+    nb = int(s.meta[1])
+    assert sorted(sch.block_order[:nb].tolist()) == list(range(nb))
+    e = sch.segment_end[sch.block_order[:nb].long()]
+    assert bool((e[1:] >= e[:-1]).all())
+    assert int(sch.stage_count.sum()) == nb
+    o = ag_gemm_tile_order(1024, 1024, 4, 1)
+    assert len(o) == len(set(o)) == (1024 // 128) * (1024 // 256) and o[0][0] == 1
+    o = gemm_rs_tile_order(1024, 1024, 4, 1)
+    assert o[0][0] == 2 and o[-1][0] == 1

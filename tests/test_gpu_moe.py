@@ -82,3 +82,25 @@ def test_distributed_layers_suite(world):
 def test_distributed_prims_suite(world):
     """ring put, notify, waits, barriers, multimem, heap API, host utils, copy-engine and small-message all-gathers, PP."""
     run_dist("triton_dist.test.nvidia.run_suite", ["--suite", "prims"], world, timeout=900)
+
+
+@pytest.mark.gpu
+def test_moe_tile_swizzle_native_vs_torch():
+    """AG+MoE block schedule: the native single-CTA kernel against the host restatement (reference K45)."""
+    import torch
+
+    from triton_dist.kernels.nvidia.moe_utils import moe_align_sort
+    from triton_dist.kernels.nvidia.threadblock_swizzle_ag_moe import (threadblock_swizzle_ag_moe,
+                                                                       torch_threadblock_swizzle_ag_moe)
+
+    torch.manual_seed(0)
+    ids = (torch.randn(1024, 32, device="cuda") + torch.linspace(-1, 1, 32, device="cuda")).topk(6, dim=-1).indices
+    s = moe_align_sort(ids, 32)
+    for rank in (0, 3):
+        got = threadblock_swizzle_ag_moe(s, 256, rank, 4)
+        ref = torch_threadblock_swizzle_ag_moe(s, 256, rank, 4)
+        nb = int(s.meta[1])
+        assert torch.equal(got.segment_start[:nb].cpu(), ref.segment_start.cpu())
+        assert torch.equal(got.segment_end[:nb].cpu(), ref.segment_end.cpu())
+        assert torch.equal(got.block_order[:nb].cpu(), ref.block_order.cpu())
+        assert torch.equal(got.stage_count.cpu(), ref.stage_count.cpu())

@@ -86,5 +86,10 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--clean", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--spin-limit", type=int, default=0, help="debug build: trap with a message after this many polls of one "
+                    "flag (-DTDIST_SPIN_LIMIT); 0 = normal build")
     a = ap.parse_args()
+    if a.spin_limit > 0:
+        COMMON.append(f"-DTDIST_SPIN_LIMIT={a.spin_limit}")
+        a.clean = True
     print(build(a.verbose, a.clean))

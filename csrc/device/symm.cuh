@@ -15,6 +15,7 @@
 // because ordering is explicit here: wait() ends in an acquire load, and the
 // data loads that follow it in program order are ordered after it.
 #pragma once
+#include <stdio.h>
 #include "ptx.cuh"
 
 #define TDIST_MAX_RANKS 16
@@ -66,13 +67,36 @@ __device__ __forceinline__ void notify(const SymmCtx& c, uint32_t* flag, int pee
 }
 __device__ __forceinline__ void notify_local(uint32_t* flag, uint32_t value) { ptx::st_release_sys(flag, value); }
 
+// Debug aid (the reference warns that a missed signal hangs forever, common_ops.py:58-60): building with
+// -DTDIST_SPIN_LIMIT=<iterations> (python build.py --spin-limit N) turns an endless spin into a device printf naming
+// the flag, the value seen and the value awaited, followed by a trap, so a protocol bug shows up as a CUDA error with a
+// message instead of a hung job. Off by default: the check costs a counter in every polling loop.
+#ifdef TDIST_SPIN_LIMIT
+#define TDIST_SPIN_GUARD_DECL unsigned long long tdist_spins_ = 0
+#define TDIST_SPIN_GUARD(flag, have, want)                                                                             \
+  if (++tdist_spins_ > static_cast<unsigned long long>(TDIST_SPIN_LIMIT)) {                                            \
+    printf("tdist: spin limit: flag %p holds %u, waiting for %u (block %d thread %d)\n", (const void*)(flag), (have),   \
+           (want), int(blockIdx.x), int(threadIdx.x));                                                                 \
+    __trap();                                                                                                          \
+  }
+#else
+#define TDIST_SPIN_GUARD_DECL
+#define TDIST_SPIN_GUARD(flag, have, want) (void)(have);
+#endif
+
 // Spin until *flag == value (acquire, system scope). One lane polls.
 __device__ __forceinline__ void wait_eq_sys(const uint32_t* flag, uint32_t value) {
-  while (ptx::ld_acquire_sys(flag) != value) {
+  TDIST_SPIN_GUARD_DECL;
+  uint32_t v;
+  while ((v = ptx::ld_acquire_sys(flag)) != value) {
+    TDIST_SPIN_GUARD(flag, v, value)
   }
 }
 __device__ __forceinline__ void wait_ge_sys(const uint32_t* flag, uint32_t value) {
-  while (static_cast<int32_t>(ptx::ld_acquire_sys(flag) - value) < 0) {
+  TDIST_SPIN_GUARD_DECL;
+  uint32_t v;
+  while (static_cast<int32_t>((v = ptx::ld_acquire_sys(flag)) - value) < 0) {
+    TDIST_SPIN_GUARD(flag, v, value)
   }
 }
 // Warp-collective wait on n consecutive flags (n <= 32): the first n lanes of

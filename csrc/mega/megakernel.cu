@@ -54,7 +54,10 @@ __device__ __forceinline__ float block_sum(float v, float* scratch) {
 
 __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t target) {
   if (slot < 0) return;
-  while (static_cast<int32_t>(ptx::ld_acquire_gpu(sb + slot) - target) < 0) {
+  TDIST_SPIN_GUARD_DECL;
+  uint32_t v;
+  while (static_cast<int32_t>((v = ptx::ld_acquire_gpu(sb + slot)) - target) < 0) {
+    TDIST_SPIN_GUARD(sb + slot, v, target)
   }
 }
 

@@ -1,5 +1,5 @@
 """Tutorial 1 — symmetric tensors, peer views and signals (the native equivalent of the reference's
-tutorials/01-distributed-notify-wait.py).  Run:  bash scripts/launch.sh tutorials/01-symmetric-heap-and-signals.py
+tutorials/01-distributed-notify-wait.py).  Run:  bash scripts/launch.sh tutorials/01-distributed-notify-wait.py
 
 Every rank allocates the SAME sequence of symmetric tensors; `symm_peer_view(t, p)` aliases rank p's copy through the
 VMM mapping, so a plain PyTorch copy into it is a one-sided put over NVLink. Signals are 32-bit flags in the same heap."""

@@ -1,5 +1,5 @@
-"""Tutorial 3 — expert-parallel inference step with token dispatch / combine (reference
-tutorials/04-deepseek-infer-all2all.py).  Run:  bash scripts/launch.sh tutorials/03-ep-dispatch-combine.py
+"""Tutorial 4 — expert-parallel inference step with token dispatch / combine (reference
+tutorials/04-deepseek-infer-all2all.py).  Run:  bash scripts/launch.sh tutorials/04-deepseek-infer-all2all.py
 
 Each rank owns E/W experts. dispatch() sends every (token, k) pair to the owner of its expert (optionally as fp8 with
 1x128 scales); the experts run as one grouped GEMM on the received rows; combine() brings the outputs back and applies

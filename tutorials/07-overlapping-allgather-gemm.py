@@ -1,5 +1,5 @@
-"""Tutorial 2 — a tensor-parallel MLP with AG+GEMM and GEMM+RS (reference tutorials/07-08: overlapping AllGather GEMM /
-GEMM ReduceScatter).  Run:  bash scripts/launch.sh tutorials/02-ag-gemm-and-gemm-rs.py
+"""Tutorial 7 — a tensor-parallel MLP with AG+GEMM and GEMM+RS (reference tutorials/07-08: overlapping AllGather GEMM /
+GEMM ReduceScatter).  Run:  bash scripts/launch.sh tutorials/07-overlapping-allgather-gemm.py
 
 Activations stay sharded on tokens between the two projections (Megatron sequence parallelism): the up-projection
 gathers them INSIDE the GEMM kernel, the down-projection scatters and reduces its output INSIDE the GEMM kernel."""

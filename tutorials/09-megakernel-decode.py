@@ -1,5 +1,5 @@
-"""Tutorial 4 — one-launch-per-token decoding with the megakernel (reference docs/mega_triton_kernel.md).
-Run:  RANDOM_PARAMS=1 bash scripts/launch.sh tutorials/04-megakernel-decode.py"""
+"""Tutorial 9 — one-launch-per-token decoding with the megakernel (reference docs/mega_triton_kernel.md).
+Run:  RANDOM_PARAMS=1 bash scripts/launch.sh tutorials/09-megakernel-decode.py"""
 import torch
 import torch.distributed as dist
 

@@ -81,23 +81,33 @@ __device__ __forceinline__ void notify_local(uint32_t* flag, uint32_t value) { p
   }
 #else
 #define TDIST_SPIN_GUARD_DECL
-#define TDIST_SPIN_GUARD(flag, have, want) (void)(have);
+#define TDIST_SPIN_GUARD(flag, have, want)
 #endif
 
 // Spin until *flag == value (acquire, system scope). One lane polls.
 __device__ __forceinline__ void wait_eq_sys(const uint32_t* flag, uint32_t value) {
+#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while ((v = ptx::ld_acquire_sys(flag)) != value) {
     TDIST_SPIN_GUARD(flag, v, value)
   }
+#else
+  while (ptx::ld_acquire_sys(flag) != value) {
+  }
+#endif
 }
 __device__ __forceinline__ void wait_ge_sys(const uint32_t* flag, uint32_t value) {
+#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while (static_cast<int32_t>((v = ptx::ld_acquire_sys(flag)) - value) < 0) {
     TDIST_SPIN_GUARD(flag, v, value)
   }
+#else
+  while (static_cast<int32_t>(ptx::ld_acquire_sys(flag) - value) < 0) {
+  }
+#endif
 }
 // Warp-collective wait on n consecutive flags (n <= 32): the first n lanes of
 // the warp each poll one flag, then the warp re-converges — this is exactly

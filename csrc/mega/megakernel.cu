@@ -54,11 +54,16 @@ __device__ __forceinline__ float block_sum(float v, float* scratch) {
 
 __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t target) {
   if (slot < 0) return;
+#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while (static_cast<int32_t>((v = ptx::ld_acquire_gpu(sb + slot)) - target) < 0) {
     TDIST_SPIN_GUARD(sb + slot, v, target)
   }
+#else
+  while (static_cast<int32_t>(ptx::ld_acquire_gpu(sb + slot) - target) < 0) {
+  }
+#endif
 }
 
 // ------------------------------------------------------------------ LINEAR (skinny GEMM, M <= 8 rows)

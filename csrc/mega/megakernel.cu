@@ -61,6 +61,7 @@ __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t
     TDIST_SPIN_GUARD(sb + slot, v, target)
   }
 #else
+  // (polling with ld.volatile + one trailing fence instead of ld.acquire was measured slower: 4.60 vs 4.27 ms/token)
   while (static_cast<int32_t>(ptx::ld_acquire_gpu(sb + slot) - target) < 0) {
   }
 #endif

@@ -60,7 +60,8 @@ static int tiles_of(const OpArgs& a, int type, int num_ctas, int* cols_per_tile)
     case OP_SILU_MUL: return std::max(1, std::min(num_ctas, int(((long long)a.M * a.N / 8 + kThreads - 1) / kThreads)));
     case OP_ADD: return std::max(1, std::min(num_ctas, int((a.N / 8 + kThreads - 1) / kThreads)));
     case OP_QK_NORM_ROPE_KV: return std::max(1, std::min(num_ctas, (a.M * (a.i0 + 2 * a.i1) + 15) / 16));
-    case OP_ATTN_SPLIT: return a.M * a.i1 * a.i4;
+    case OP_ATTN_SPLIT:
+    case OP_ATTN_FUSED: return a.M * a.i1 * a.i4;
     case OP_ATTN_COMBINE: return (a.M * a.i0 + 3) / 4;
     case OP_ALLREDUCE: return std::max(1, std::min(kMaxArTiles, int(((long long)a.N / 8 + 2 * kThreads - 1) / (2 * kThreads))));
     case OP_BARRIER: return 1;
@@ -81,7 +82,8 @@ static int smem_of(const OpArgs& a, int type) {
       return a.M * xpitch * 2 + (a.in2 != nullptr ? a.K * 2 : 0) + 2 * ge.nblk * 32 * a.M * 4 + 2 * (kThreads / 32) * 32 * a.M * 4 + 256;
     }
     case OP_RMS_NORM: return a.K * 4 + 256;
-    case OP_ATTN_SPLIT: {
+    case OP_ATTN_SPLIT:
+    case OP_ATTN_FUSED: {
       const int g = std::min(8, a.i0 / std::max(a.i1, 1));
       return (kThreads / 32) * g * (2 + 128) * 4 + g * 128 * 4;  // per-warp (max, sum, out[128]) for g heads + scaled q
     }
@@ -136,6 +138,13 @@ int tdist_mega_add_op(void* h, int type, const tdist_mega_op* d, int dep0, int d
   if (type == OP_LINEAR && (a.M < 1 || a.M > 8 || a.K % 64 != 0)) {
     set_error("mega linear: need 1 <= M <= 8 rows and K % 64 == 0");
     return -1;
+  }
+  if (type == OP_ATTN_FUSED) {
+    const int g = a.i1 > 0 ? a.i0 / a.i1 : 0;
+    if (g < 1 || g > 8 || a.i0 % std::max(a.i1, 1) != 0) {
+      set_error("mega fused attention: needs 1..8 query heads per KV head");
+      return -1;
+    }
   }
   if (type == OP_ALLREDUCE || type == OP_BARRIER) a.i0 = b->num_ar_ops++;
   int cpt = 0;

@@ -26,6 +26,7 @@ enum OpType : int {
   OP_PREFETCH = 9,     // L2 prefetch of a weight matrix (no dependency)
   OP_EMBEDDING = 10,
   OP_ARGMAX = 11,
+  OP_ATTN_FUSED = 12,  // qk-norm + RoPE + KV-cache write + split-KV attention + LSE combine in one task type
   OP_NUM_TYPES
 };
 

@@ -526,15 +526,26 @@ __device__ __forceinline__ void qk_rope_body(const OpArgs& a, int tile) {
 // ------------------------------------------------------------------ attention: split-KV decode (head_dim 128)
 // in0 q [B,Hq,128]; in1/in2 caches; in3 block_table; in4 positions (kv_len = pos + 1); out0 partial [B,Hq,S,129].
 // i0 Hq, i1 Hkv, i2 page_size, i3 max_pages, i4 splits; f0 scale. tile = (b * Hkv + kvh) * S + split.
-template <int G>
-__device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int g_total, int g_off,
+// FUSED (op ATTN_FUSED): the task also does what the reference runs as separate ops before and after it —
+//  * q-norm + RoPE of its G query heads straight from the qkv projection (each split recomputes them: 8 x 128 values),
+//    k-norm + RoPE + cache write of the NEW token by the split that owns the last position;
+//  * the LSE combine over the splits, by whichever split of the (batch, kv head) finishes last (a monotone arrival
+//    counter per (batch, kv head) behind the partial buffer; its value after step s is s * S).
+// That removes two scoreboard hops and two small tasks from every layer of the decode step.
+// FUSED operands: in0 qkv [B,(Hq+2Hkv)*128]; in5 cos_sin fp32 [max_pos,128]; out1 final out [B,Hq,128] bf16;
+// out2 q/k norm weights bf16 [2][128] or null; f1 norm eps; counters = uint32 [B*Hkv] behind out0's B*Hq*S*129 floats.
+// The number of query heads per pass (G <= 8) is a run-time value: one instantiation per FUSED instead of four keeps
+// the interpreter's code small (with eight instantiations the kernel grew from 190 KB to 360 KB of SASS and every
+// other task type, including the linear main loop, got measurably slower).
+template <bool FUSED>
+__device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8_t* smem, int G, int g_total, int g_off,
                                                 const uint32_t* wait_sb, const Task& wt, uint32_t tgt0, uint32_t tgt1,
-                                                uint64_t* tr) {
+                                                uint64_t* tr, uint32_t step) {
   // `wait_sb` != nullptr: this call also performs the task's scoreboard wait (first pass over the head group).
   // One warp per key position (lane = 4 of the 128 head dims), all G query heads of the KV group at once: the
   // per-thread state is G x 4 output accumulators + G (max, sum) pairs, which fits in registers for G = 8 (the first
   // version used half-warps with 8 dims per lane and spilled). The scaled queries sit in shared memory.
-  constexpr int D = 128, NW = kThreads / 32;
+  constexpr int D = 128, NW = kThreads / 32, GM = 8;
   const int S = a.i4, Hq = a.i0, Hkv = a.i1;
   const int split = tile % S, kvh = (tile / S) % Hkv, b = tile / (S * Hkv);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -572,22 +583,83 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
       vr[u] = *reinterpret_cast<const uint2*>(vc + off);
     }
   }
+  // FUSED: everything the q / k preparation needs except the projection itself is known before the producer op
+  // finishes (position, cos/sin row, norm weights): fetch it now, these loads are DRAM misses
+  const int f_heads = Hq + 2 * Hkv, f_pos = kv_len - 1;
+  const bool f_owner = s_beg <= f_pos && f_pos < s_end;
+  const int f_role = !FUSED ? 3 : warp < G ? 0 : (f_owner && warp == G) ? 1 : (f_owner && warp == G + 1) ? 2 : 3;
+  float4 f_cos = make_float4(0.f, 0.f, 0.f, 0.f), f_sin = f_cos;
+  uint2 f_nw = make_uint2(0u, 0u);
+  const bool f_has_nw = FUSED && a.out2 != nullptr;
+  if (FUSED && f_role < 2) {
+    const float* cs = static_cast<const float*>(a.in5) + size_t(f_pos) * D + (lane & 15) * 4;
+    f_cos = *reinterpret_cast<const float4*>(cs);
+    f_sin = *reinterpret_cast<const float4*>(cs + 64);
+    if (f_has_nw) f_nw = *reinterpret_cast<const uint2*>(static_cast<const bf16*>(a.out2) + f_role * D + lane * 4);
+  }
   if (wait_sb != nullptr && threadIdx.x == 0) {
     wait_slot(wait_sb, wt.dep0, tgt0);
     wait_slot(wait_sb, wt.dep1, tgt1);
     if (tr != nullptr) tr[2] = ptx::globaltimer();  // dependencies satisfied
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < G * D / 8; i += kThreads) {
-    const int g = i / (D / 8), c = i % (D / 8);
-    float f[8];
-    unpack8(ptx::ld_v4(q + (size_t(b) * Hq + h0 + g) * D + c * 8), f);
+  if (!FUSED) {
+    for (int i = threadIdx.x; i < G * D / 8; i += kThreads) {
+      const int g = i / (D / 8), c = i % (D / 8);
+      float f[8];
+      unpack8(ptx::ld_v4(q + (size_t(b) * Hq + h0 + g) * D + c * 8), f);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) qs[g * D + c * 8 + j] = f[j] * (a.f0 * 1.4426950408889634f);
+      for (int j = 0; j < 8; ++j) qs[g * D + c * 8 + j] = f[j] * (a.f0 * 1.4426950408889634f);
+    }
+  } else {
+    // warp g < G: query head h0 + g; warps G / G + 1 of the split that owns the newest position: its K / V head
+    const int heads = f_heads, pos = f_pos, role = f_role;
+    if (role < 3) {
+      const int h = role == 0 ? h0 + warp : role == 1 ? Hq + kvh : Hq + Hkv + kvh;
+      const uint2 raw = *reinterpret_cast<const uint2*>(static_cast<const bf16*>(a.in0) + (size_t(b) * heads + h) * D + lane * 4);
+      float f[4];
+      {
+        const float2 p0 = ptx::unpack_bf16x2(raw.x), p1 = ptx::unpack_bf16x2(raw.y);
+        f[0] = p0.x, f[1] = p0.y, f[2] = p1.x, f[3] = p1.y;
+      }
+      if (role < 2) {
+        if (f_has_nw) {
+          float ss = f[0] * f[0] + f[1] * f[1] + f[2] * f[2] + f[3] * f[3];
+          ss = ptx::warp_reduce_sum(ss);
+          const float inv = rsqrtf(ss / 128.f + a.f1);
+          const float2 wa = ptx::unpack_bf16x2(f_nw.x), wb = ptx::unpack_bf16x2(f_nw.y);
+          f[0] = __bfloat162float(__float2bfloat16(f[0] * inv)) * wa.x;
+          f[1] = __bfloat162float(__float2bfloat16(f[1] * inv)) * wa.y;
+          f[2] = __bfloat162float(__float2bfloat16(f[2] * inv)) * wb.x;
+          f[3] = __bfloat162float(__float2bfloat16(f[3] * inv)) * wb.y;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) f[i] = __bfloat162float(__float2bfloat16(f[i]));
+        }
+        const float cc[4] = {f_cos.x, f_cos.y, f_cos.z, f_cos.w}, sn[4] = {f_sin.x, f_sin.y, f_sin.z, f_sin.w};
+        float r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float other = __shfl_xor_sync(0xffffffffu, f[i], 16);
+          r[i] = lane < 16 ? f[i] * cc[i] - other * sn[i] : f[i] * cc[i] + other * sn[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f[i] = __bfloat162float(__float2bfloat16(r[i]));  // the unfused op stores bf16
+      }
+      if (role == 0) {
+        const float sc = a.f0 * 1.4426950408889634f;
+        *reinterpret_cast<float4*>(qs + warp * D + lane * 4) = make_float4(f[0] * sc, f[1] * sc, f[2] * sc, f[3] * sc);
+      } else {
+        uint2 packed;
+        packed.x = ptx::pack_bf16x2(f[0], f[1]);
+        packed.y = ptx::pack_bf16x2(f[2], f[3]);
+        bf16* dst = static_cast<bf16*>(const_cast<void*>(role == 1 ? a.in1 : a.in2)) + kv_off(pos) + lane * 4;
+        *reinterpret_cast<uint2*>(dst) = packed;
+      }
+    }
   }
-  float m[G], l[G], o[G][4];
+  float m[GM], l[GM], o[GM][4];
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
+  for (int g = 0; g < GM; ++g) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) o[g][i] = 0.f;
     m[g] = -CUDART_INF_F;
@@ -609,7 +681,8 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
       const float2 k01 = ptx::unpack_bf16x2(kr[u].x), k23 = ptx::unpack_bf16x2(kr[u].y);
       const float2 v01 = ptx::unpack_bf16x2(vr[u].x), v23 = ptx::unpack_bf16x2(vr[u].y);
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
+      for (int g = 0; g < GM; ++g) {
+        if (g >= G) break;
         const float4 qa = *reinterpret_cast<const float4*>(qs + g * D + lane * 4);
         float sc = qa.x * k01.x;
         sc = fmaf(qa.y, k01.y, sc);
@@ -629,7 +702,8 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
   }
   // reduce the 16 warps through shared memory: [NW][G] maxima and sums, [NW][G][D] outputs (66 KB for G = 8)
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
+  for (int g = 0; g < GM; ++g) {
+    if (g >= G) break;
     if (lane == 0) {
       sh_m[warp * G + g] = m[g];
       sh_l[warp * G + g] = l[g];
@@ -654,6 +728,51 @@ __device__ __forceinline__ void attn_split_body(const OpArgs& a, int tile, uint8
     if (d == 0) dst[D] = ll > 0.f ? (mm + log2f(ll)) * 0.6931471805599453f : -CUDART_INF_F;
   }
   __syncthreads();
+  if (FUSED) {
+    // arrival counter of this (batch, kv head): the split that brings it to step * S combines all S partials
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(partial + size_t(a.M) * Hq * S * (D + 1)) + (b * Hkv + kvh);
+    __shared__ int s_last;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_last = atomicAdd(cnt, 1u) + 1u == step * uint32_t(S);
+    }
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      bf16* outp = static_cast<bf16*>(a.out1);
+      // all loads of a (head, dim) pair are issued before any is used: one L2 round trip instead of 2 * S
+      constexpr int kMaxS = 16;
+      for (int idx = threadIdx.x; idx < G * D; idx += kThreads) {
+        const int g = idx / D, d = idx % D;
+        const float* base = partial + (size_t(b) * Hq + h0 + g) * S * (D + 1);
+        float den = 0.f, acc = 0.f, mx = -CUDART_INF_F;
+        for (int s0 = 0; s0 < S; s0 += kMaxS) {  // S <= 16 in practice: one pass
+          float lse[kMaxS], val[kMaxS];
+#pragma unroll
+          for (int j = 0; j < kMaxS; ++j) {
+            const bool on = s0 + j < S;
+            lse[j] = on ? __ldcg(base + size_t(s0 + j) * (D + 1) + D) : -CUDART_INF_F;
+            val[j] = on ? __ldcg(base + size_t(s0 + j) * (D + 1) + d) : 0.f;
+          }
+          float m2 = mx;
+#pragma unroll
+          for (int j = 0; j < kMaxS; ++j) m2 = fmaxf(m2, lse[j]);
+          const float resc = mx == -CUDART_INF_F ? 0.f : __expf(mx - m2);
+          den *= resc;
+          acc *= resc;
+#pragma unroll
+          for (int j = 0; j < kMaxS; ++j) {
+            const float w = lse[j] == -CUDART_INF_F ? 0.f : __expf(lse[j] - m2);
+            den += w;
+            acc += w * val[j];
+          }
+          mx = m2;
+        }
+        outp[(size_t(b) * Hq + h0 + g) * D + d] = __float2bfloat16(den > 0.f ? acc / den : 0.f);
+      }
+    }
+    __syncthreads();
+  }
 }
 
 // combine: in0 partial [B,Hq,S,129] -> out0 [B,Hq,128] bf16. tile = 4 (b,h) pairs.
@@ -860,7 +979,7 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
       linear_body(a, t.tile, smem, step, p.scoreboard, t, tgt0, tgt1, r, stage_base, lin_k, tr);
       ++lin_k;
     } else {
-      if (t.type != OP_ATTN_SPLIT) {  // (the attention split waits inside, after it has started its K/V loads)
+      if (t.type != OP_ATTN_SPLIT && t.type != OP_ATTN_FUSED) {  // (attention waits inside, after it has started its K/V loads)
         if (threadIdx.x == 0) {
           wait_slot(p.scoreboard, t.dep0, tgt0);
           wait_slot(p.scoreboard, t.dep1, tgt1);
@@ -875,25 +994,13 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
         case OP_QK_NORM_ROPE_KV: qk_rope_body(a, t.tile); break;
         case OP_ATTN_SPLIT: {
           const int g = a.i0 / a.i1;
-          int done = 0;
-          while (done < g) {
-            const int rem = g - done;
-            if (rem >= 8) {
-              attn_split_body<8>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
-              done += 8;
-            } else if (rem >= 4) {
-              attn_split_body<4>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
-              done += 4;
-            } else if (rem >= 2) {
-              attn_split_body<2>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
-              done += 2;
-            } else {
-              attn_split_body<1>(a, t.tile, smem, g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr);
-              done += 1;
-            }
-          }
+          for (int done = 0; done < g; done += 8)  // at most 8 query heads per pass over the split's K/V
+            attn_split_body<false>(a, t.tile, smem, min(8, g - done), g, done, done == 0 ? p.scoreboard : nullptr, t, tgt0, tgt1, tr, step);
           break;
         }
+        case OP_ATTN_FUSED:  // (the builder only emits this op for <= 8 query heads per KV head)
+          attn_split_body<true>(a, t.tile, smem, a.i0 / a.i1, a.i0 / a.i1, 0, p.scoreboard, t, tgt0, tgt1, tr, step);
+          break;
         case OP_ATTN_COMBINE: attn_combine_body(a, t.tile); break;
         case OP_ALLREDUCE: allreduce_body(p, a, t.tile, step); break;
         case OP_BARRIER:

@@ -90,3 +90,12 @@ print("linear main loop, cycles per warp summed over the step (CTA 0; wait-stage
 for w in range(16):
     print(f"  warp {w:2d}: " + "  ".join(f"{int(x):9d}" for x in wc[0, w]))
 print("  mean over CTAs and warps (us at 1.9 GHz):", [round(float(wc[:, :, j].mean()) / 1900, 1) for j in range(4)])
+# all tasks of one attention op in the middle of the model
+att = [k for k in keys if ops[k][0] in ("attn_fused", "attn_split")]
+if att:
+    k = att[len(att) // 2]
+    rows = sorted([e for e in t_all if e[2] == k], key=lambda e: e[6])
+    t0 = min(e[5] for e in rows)
+    print(f"tasks of op {k} ({ops[k][0]}): cta tile | begin +deps | end (us)")
+    for e in rows:
+        print(f"   cta {e[0]:3d} tile {e[4]:3d} | {(e[5] - t0) / 1e3:6.1f} +{(e[7][0] - e[5]) / 1e3:5.1f} | {(e[6] - t0) / 1e3:6.1f}")

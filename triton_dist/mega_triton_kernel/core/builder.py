@@ -23,7 +23,7 @@ from ...kernels.nvidia.flash_decode import torch_paged_decode
 from ...runtime import symm as _symm
 
 (OP_LINEAR, OP_RMS_NORM, OP_SILU_MUL, OP_ADD, OP_QK_NORM_ROPE_KV, OP_ATTN_SPLIT, OP_ATTN_COMBINE, OP_ALLREDUCE, OP_BARRIER,
- OP_PREFETCH, OP_EMBEDDING, OP_ARGMAX) = range(12)
+ OP_PREFETCH, OP_EMBEDDING, OP_ARGMAX, OP_ATTN_FUSED) = range(13)
 MAX_AR_TILES = 32
 NUM_KV_SPLITS_DEFAULT = 16
 
@@ -144,6 +144,44 @@ class ModelBuilder:
         self._add(OP_ATTN_SPLIT, [query, key_cache, value_cache, block_tables, kv_lens], [partial], M=B, ints=ints, longs=strides,
                   floats=[scale])
         return self._add(OP_ATTN_COMBINE, [partial], [output], M=B, ints=ints)
+
+    @staticmethod
+    def supports_fused_attn(num_q_heads: int, num_kv_heads: int) -> bool:
+        return num_kv_heads > 0 and num_q_heads % num_kv_heads == 0 and 1 <= num_q_heads // num_kv_heads <= 8
+
+    def make_attn_fused(self, qkv, key_cache, value_cache, block_tables, kv_lens, q_rms_weight, k_rms_weight, cos_sin_cache,
+                        output, q_rms_eps: float = 1e-6, sm_scale=None, layer_id: int = 0,
+                        num_kv_splits: int = NUM_KV_SPLITS_DEFAULT):
+        """B200 addition: ``make_qk_norm_rope_update_kvcache`` + ``make_attn`` as ONE task type. Every split task
+        normalises / rotates its own query heads from ``qkv`` [B, 1, Hq + 2*Hkv, D], the split that owns the newest
+        position writes K/V into the paged cache, and the last split to finish does the LSE combine into ``output``
+        [B, 1, Hq, D]: two scoreboard hops and two small ops fewer per layer."""
+        B = qkv.shape[0]
+        Hq, D = output.shape[2], output.shape[3]
+        Hkv, page = key_cache.shape[2], key_cache.shape[1]
+        assert D == 128 and self.supports_fused_attn(Hq, Hkv)
+        scale = D ** -0.5 if sm_scale is None else sm_scale
+        # partial results [B, Hq, S, D + 1] fp32 followed by one arrival counter per (batch, kv head)
+        blob = torch.zeros(B * Hq * num_kv_splits * (D + 1) + B * Hkv, dtype=torch.float32, device=qkv.device)
+        norm_w = None
+        if q_rms_weight is not None:
+            norm_w = torch.stack([q_rms_weight, k_rms_weight]).to(qkv.dtype).contiguous()
+        self._count(qkv, output)
+        q_tmp = torch.empty((B, Hq, D), dtype=qkv.dtype, device=qkv.device)
+
+        def ref():
+            ew.qk_norm_rope_update_kvcache(qkv.reshape(B, -1), q_rms_weight, k_rms_weight, cos_sin_cache, kv_lens, key_cache,
+                                           value_cache, Hq, Hkv, D, q_rms_eps,
+                                           batch_idx=torch.arange(B, dtype=torch.int32, device=qkv.device),
+                                           block_table=block_tables, q_out=q_tmp)
+            o, _ = torch_paged_decode(q_tmp, key_cache, value_cache, kv_lens + 1, block_tables, scale)
+            output.view(B, Hq, D).copy_(o.to(output.dtype))
+
+        self._torch_ops.append(ref)
+        ints = [Hq, Hkv, page, block_tables.shape[1], num_kv_splits]
+        strides = [key_cache.stride(0), key_cache.stride(1), key_cache.stride(2)]
+        return self._add(OP_ATTN_FUSED, [qkv, key_cache, value_cache, block_tables, kv_lens, cos_sin_cache], [blob, output, norm_w],
+                         M=B, ints=ints, longs=strides, floats=[scale, q_rms_eps])
 
     def make_qk_norm_rope_update_kvcache(self, qkv, key_cache, value_cache, block_tables, kv_lens, q_rms_weight, k_rms_weight,
                                          cos_sin_cache, q_norm_rope, q_rms_eps: float = 1e-6, k_rms_eps: float = 1e-6,
@@ -270,7 +308,7 @@ class ModelBuilder:
 
     # ------------------------------------------------------------------ per-task timeline
     OP_NAMES = ["linear", "rms_norm", "silu_mul", "add", "qk_norm_rope_kv", "attn_split", "attn_combine", "allreduce", "barrier",
-                "prefetch", "embedding", "argmax"]
+                "prefetch", "embedding", "argmax", "attn_fused"]
 
     def enable_profiling(self, on: bool = True):
         """Stamp %globaltimer at the start and end of every task of the following launches (thread 0 of each CTA).

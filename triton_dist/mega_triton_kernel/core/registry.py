@@ -25,6 +25,7 @@ _OPS = [
     OpInfo(9, "prefetch", "prefetch_body", "kernels/prefetch.py (tasks/prefetch.py)"),
     OpInfo(10, "embedding", "embedding_body", "(torch op in the reference model)"),
     OpInfo(11, "argmax", "argmax_body", "(torch op in the reference model)"),
+    OpInfo(12, "attn_fused", "attn_split_body<G, true>", "kernels/norm.py + kernels/flash_attn.py:33,166 in one task"),
 ]
 
 REGISTRY: Dict[str, OpInfo] = {o.name: o for o in _OPS}

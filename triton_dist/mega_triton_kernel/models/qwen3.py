@@ -58,6 +58,10 @@ class Qwen3Model:
         self.down_partial = symm((2, B, H), dt)
         self.logits = torch.zeros((B, d.lm_head.shape[0]), dtype=dt, device=dev)
         self.next_ids = torch.zeros((B,), dtype=torch.int64, device=dev)
+        import os
+
+        # qk-norm + RoPE + attention + combine as one task type (TDIST_MEGA_FUSED_ATTN=1; off by default)
+        self.fused_attn = os.environ.get("TDIST_MEGA_FUSED_ATTN", "0") == "1"
         self.build_fwd()
 
     @staticmethod
@@ -82,10 +86,14 @@ class Qwen3Model:
             else:
                 b.make_rms_norm(self.hidden, layer.input_norm_w, self.normed, layer.input_norm_eps, li)
                 b.make_qkv_proj(self.normed, attn.wqkv, self.qkv.view(B, -1), li)
-            b.make_qk_norm_rope_update_kvcache(self.qkv, kc, vc, kv.block_table, kv.positions, attn.q_norm_w, attn.k_norm_w,
-                                               d.cos_sin_cache, self.q_rope, attn.q_norm_eps, attn.k_norm_eps, layer_id=li)
-            b.make_attn(self.q_rope, kc, vc, kv.block_table, kv.positions, self.attn_out, layer_id=li,
-                        num_kv_splits=self.num_kv_splits)
+            if self.fused and self.fused_attn and b.supports_fused_attn(self.q_rope.shape[2], kc.shape[2]):
+                b.make_attn_fused(self.qkv, kc, vc, kv.block_table, kv.positions, attn.q_norm_w, attn.k_norm_w, d.cos_sin_cache,
+                                  self.attn_out, attn.q_norm_eps, layer_id=li, num_kv_splits=self.num_kv_splits)
+            else:
+                b.make_qk_norm_rope_update_kvcache(self.qkv, kc, vc, kv.block_table, kv.positions, attn.q_norm_w, attn.k_norm_w,
+                                                   d.cos_sin_cache, self.q_rope, attn.q_norm_eps, attn.k_norm_eps, layer_id=li)
+                b.make_attn(self.q_rope, kc, vc, kv.block_table, kv.positions, self.attn_out, layer_id=li,
+                            num_kv_splits=self.num_kv_splits)
             if self.fused:
                 b.make_o_proj(self.attn_out.view(B, -1), attn.wo, self.o_partial[0], li, parity_stride_bytes=stride)
                 b.make_allreduce(self.o_partial[0], None, layer_id=li, residual=self.hidden, parity_stride_bytes=stride)

@@ -369,7 +369,12 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     set_error("gemm_fused: unknown mode");
     return -1;
   }
-  if ((f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS) && want_cta_pair(a) && p.rows_per_rank >= 2 * kBlockM) {
+  // AG at 8 ranks (1024 rows per rank at the flagship shape) measured 0.159 ms on single-CTA tiles against 0.213 ms on
+  // pair tiles (the 256-row tile waits for twice as many arriving row blocks); at 2 ranks the pair kernel wins
+  // (0.328 vs 0.383 ms). Unless forced, AG therefore takes pair tiles only from 2048 rows per rank.
+  const bool pair_ok = f->mode == TDIST_GEMM_RS || a->cta_group == 2 || getenv("TDIST_GEMM_CTA_GROUP") != nullptr ||
+                       p.rows_per_rank >= 16 * kBlockM;
+  if ((f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS) && want_cta_pair(a) && pair_ok && p.rows_per_rank >= 2 * kBlockM) {
     // CTA-pair kernel: 256-row tiles on cluster pairs. Push CTAs (AG) are launched in pairs as well.
     const int ptiles_m = ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * W;
     if (f->mode == TDIST_GEMM_AG && W > 1) {

@@ -289,26 +289,46 @@ __device__ __forceinline__ void ar_consume_body(const GemmParams& p, uint32_t ep
     __syncthreads();
     const int rows = min(kBlockM, p.M - tc.row0);
     const int cols_v = min(vec_per_row, (p.N - tc.n_blk * BLOCK_N) / 8);
-    for (int idx = threadIdx.x; idx < rows * vec_per_row; idx += blockDim.x) {
-      const int r = idx / vec_per_row, cv = idx % vec_per_row;
-      if (cv >= cols_v) continue;
-      const size_t off = (size_t(tc.row0 + r) * p.ldc + size_t(tc.n_blk) * BLOCK_N) * 2 + size_t(cv) * 16;
-      int4 v;
-      if (p.use_mc) {
-        v = Pack<Tag>::mc_ld_reduce(mc_ptr(p.ctx, sym_c) + off);
-      } else {
-        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 1
-        for (int s = 0; s < W; ++s) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, sym_c, (p.ctx.rank + s) % W) + off));
-        v = Pack<Tag>::cvt(acc);
+    // kArBatch independent multimem loads per thread are issued before the first one is used: the NVLS round trip is
+    // ~2-3 us, one load in flight per thread left a 64 KB tile at ~20 us (measured at M = 2048: the whole op was 10x
+    // slower than cuBLAS + NCCL)
+    constexpr int kArBatch = 8;
+    for (int i0 = threadIdx.x; i0 < rows * vec_per_row; i0 += blockDim.x * kArBatch) {
+      size_t off[kArBatch];
+      bool on[kArBatch];
+      int4 v[kArBatch];
+#pragma unroll
+      for (int b = 0; b < kArBatch; ++b) {
+        const int idx = i0 + b * blockDim.x;
+        const int r = idx / vec_per_row, cv = idx % vec_per_row;
+        on[b] = idx < rows * vec_per_row && cv < cols_v;
+        off[b] = (size_t(tc.row0 + r) * p.ldc + size_t(tc.n_blk) * BLOCK_N) * 2 + size_t(cv) * 16;
       }
-      if (p.ar_one_shot) {
-        *reinterpret_cast<int4*>(out + off) = v;
-      } else if (p.use_mc) {
-        ptx::multimem_st_v4(mc_ptr(p.ctx, out) + off, v);
+      if (p.use_mc) {
+#pragma unroll
+        for (int b = 0; b < kArBatch; ++b)
+          if (on[b]) v[b] = Pack<Tag>::mc_ld_reduce(mc_ptr(p.ctx, sym_c) + off[b]);
       } else {
+#pragma unroll
+        for (int b = 0; b < kArBatch; ++b) {
+          if (!on[b]) continue;
+          float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll 1
-        for (int s = 0; s < W; ++s) ptx::st_v4(symm_at(p.ctx, out, (p.ctx.rank + s) % W) + off, v);
+          for (int s2 = 0; s2 < W; ++s2) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, sym_c, (p.ctx.rank + s2) % W) + off[b]));
+          v[b] = Pack<Tag>::cvt(acc);
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kArBatch; ++b) {
+        if (!on[b]) continue;
+        if (p.ar_one_shot) {
+          *reinterpret_cast<int4*>(out + off[b]) = v[b];
+        } else if (p.use_mc) {
+          ptx::multimem_st_v4(mc_ptr(p.ctx, out) + off[b], v[b]);
+        } else {
+#pragma unroll 1
+          for (int s2 = 0; s2 < W; ++s2) ptx::st_v4(symm_at(p.ctx, out, (p.ctx.rank + s2) % W) + off[b], v[b]);
+        }
       }
     }
     __syncthreads();

@@ -37,13 +37,16 @@ def test_gemm_matches_fp32_reference(M, N, K, dtype):
 
 
 @pytest.mark.parametrize("bn", [32, 64, 96, 112, 128, 160, 192, 224, 256])
-def test_gemm_every_tile_width(bn):
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_gemm_every_tile_width(bn, cta_group):
+    """Every tile-width instantiation of the single-CTA kernel and of the CTA-pair kernel (which has no 32-wide tile: the
+    request then falls back to its cost model)."""
     from triton_dist.kernels.nvidia import gemm_persistent
 
     torch.manual_seed(1)
     a = (torch.rand(512, 1024, device="cuda") * 2 - 1).bfloat16()
     b = ((torch.rand(1344, 1024, device="cuda") * 2 - 1) * 0.1).bfloat16()
-    c = gemm_persistent(a, b, block_n=bn)
+    c = gemm_persistent(a, b, block_n=bn, cta_group=cta_group)
     torch.testing.assert_close(c.float(), a.float() @ b.float().t(), atol=2e-2, rtol=2e-2)
 
 

@@ -80,3 +80,15 @@ def test_tile_order_modules():
     assert len(o) == len(set(o)) == (1024 // 128) * (1024 // 256) and o[0][0] == 1
     o = gemm_rs_tile_order(1024, 1024, 4, 1)
     assert o[0][0] == 2 and o[-1][0] == 1
+
+
+def test_compile_aot_table():
+    """The built library carries the kernel instantiation table and the C ABI (reference test_compile_aot.py)."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, "-m", "triton_dist.test.nvidia.test_compile_aot"], cwd=root, capture_output=True, text=True,
+                       env={**__import__("os").environ, "PYTHONPATH": str(root)})
+    assert r.returncode == 0, r.stdout + r.stderr

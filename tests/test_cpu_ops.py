@@ -92,3 +92,15 @@ def test_compile_aot_table():
     r = subprocess.run([sys.executable, "-m", "triton_dist.test.nvidia.test_compile_aot"], cwd=root, capture_output=True, text=True,
                        env={**__import__("os").environ, "PYTHONPATH": str(root)})
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_language_primitive_map():
+    """Every primitive name of the reference's language layer maps to an existing native device function."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, "-m", "triton_dist.test.nvidia.test_language_extra"], cwd=root, capture_output=True, text=True,
+                       env={**__import__("os").environ, "PYTHONPATH": str(root)})
+    assert r.returncode == 0, r.stdout + r.stderr

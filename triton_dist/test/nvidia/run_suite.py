@@ -31,6 +31,7 @@ def cases(suite: str, world: int):
         (T + "test_sp_decode_attn", ["--check", "--verify-iters", 2, "--stress"]),
         (T + "test_sp_ag_attention_intra_node", ["--check", "--verify-iters", 2, "--seqlen", 512 * max(world, 1)]),
         (T + "test_sp_ag_attention_intra_node", ["--check", "--verify-iters", 1, "--seqlen", 256 * max(world, 1), "--no-zigzag"]),
+        (T + "test_sp_ag_attention_inter_node", ["--check"]),
     ]
     models = [
         (T + "test_tp_e2e", ["--model", "qwen3", "--check"]),

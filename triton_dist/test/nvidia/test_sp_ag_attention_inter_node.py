@@ -13,7 +13,7 @@ if __name__ == "__main__":
     group, rank, world = setup()
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     dtype = DTYPES[args.dtype] if dev == "cuda" else torch.float32
-    B, Hq, Hkv, D, L = 1, 4, 2, 128, args.seqlen * world
+    B, Hq, Hkv, D, L = 2, 8, 2, 128, args.seqlen * world  # same shape class as the intra-node test
     Ll = L // world
     ctx = create_sp_ag_attention_context_inter_node(B, Hq, Hkv, L, Ll, D, dtype, dtype, rank, rank, world, world)
     try:

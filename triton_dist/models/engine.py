@@ -131,14 +131,25 @@ class Engine:
             torch.cuda.synchronize()
         if dist.is_initialized():
             dist.barrier()
+        prof = None
+        if self.enable_profile:  # profile (at most) the first 64 decode steps, merged over ranks (reference engine.py:153-179)
+            from ..utils import group_profile
+
+            prof = group_profile(f"engine_{self.backend}", do_prof=True, group=self.group)
+            prof.__enter__()
         t0 = time.perf_counter()
-        for _ in range(gen_len):
+        for step_i in range(gen_len):
+            if prof is not None and step_i == 64:
+                prof.__exit__(None, None, None)
+                prof = None
             position_ids = self.get_ctx(torch.zeros((bsz, 1), dtype=torch.long, device=dev))
             logits = self.model_launch(next_token, position_ids)
             full_logits = logits[:, -1, :]
             next_token = sample_token(full_logits, temperature=self.temperature, top_p=self.top_p)
             self.kv_cache.inc_offset()
             output_ids.append(next_token)
+        if prof is not None:
+            prof.__exit__(None, None, None)
         if torch.cuda.is_available():
             torch.cuda.synchronize()
         if dist.is_initialized():

@@ -134,6 +134,15 @@ def run_suite(cases) -> bool:
 
 
 def bench(fn, args, group=None, flush_l2=True):
+    """Device time of ``fn`` in ms (max over ranks). With ``--profile`` the timed loop also runs under torch.profiler and
+    the per-rank chrome traces are merged on rank 0 (``prof/<script>/merged.json.gz``), as every reference test does."""
     graph = getattr(args, "graph", False)
+    if getattr(args, "profile", False):
+        from triton_dist.utils import group_profile
+
+        name = os.path.splitext(os.path.basename(sys.argv[0] or "bench"))[0].split(".")[-1]
+        with group_profile(name, do_prof=True, group=group):
+            return perf_func_max_over_ranks(fn, args.iters, args.warmup, group=group, flush_l2=flush_l2 and not graph,
+                                            use_graph=graph)[1]
     return perf_func_max_over_ranks(fn, args.iters, args.warmup, group=group, flush_l2=flush_l2 and not graph,
                                     use_graph=graph)[1]

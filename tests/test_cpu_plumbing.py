@@ -65,3 +65,9 @@ def test_layers_suite_cpu():
 def test_mega_suite_cpu():
     """ModelBuilder graphs (per-op cases and the Qwen3 decode graph) through the eager fallback of the builder."""
     run_dist(N + "run_suite", ["--suite", "mega"], 2, timeout=1200)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_team_split_cpu(world):
+    """EP x PP team split, rank translation, strided split (reference test_team_split.py)."""
+    run_dist(N + "test_team_split", [], world)

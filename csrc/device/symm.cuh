@@ -193,6 +193,67 @@ __device__ __forceinline__ void putmem_signal_block(const SymmCtx& c, T* dst_loc
   }
 }
 
+// The rest of the NVSHMEM device vocabulary the reference exposes (language/extra/libshmem_device.py:28-342), as thin
+// forms over the mapped peer pointers. There is no proxy thread and no non-blocking queue: a "_nbi" put is the same
+// store sequence, completion = the fence / quiet that precedes the signal.
+__device__ __forceinline__ int my_pe(const SymmCtx& c) { return c.rank; }
+__device__ __forceinline__ int n_pes(const SymmCtx& c) { return c.world; }
+__device__ __forceinline__ void int_p(const SymmCtx& c, int* dst_local, int value, int peer) {
+  *symm_at(c, dst_local, peer) = value;
+}
+__device__ __forceinline__ void signal_op(const SymmCtx& c, uint32_t* flag, uint32_t value, SignalOp op, int peer) {
+  notify(c, flag, peer, value, op);
+}
+template <typename T>
+__device__ __forceinline__ void getmem_warp(const SymmCtx& c, T* dst, T* src_local, size_t bytes, int peer) {
+  copy_warp(dst, symm_at(c, src_local, peer), bytes);
+}
+template <typename T>
+__device__ __forceinline__ void putmem_nbi_block(const SymmCtx& c, T* dst_local, const T* src, size_t bytes, int peer) {
+  putmem_block(c, dst_local, src, bytes, peer);
+}
+template <typename T>
+__device__ __forceinline__ void putmem_nbi_warp(const SymmCtx& c, T* dst_local, const T* src, size_t bytes, int peer) {
+  putmem_warp(c, dst_local, src, bytes, peer);
+}
+// put + signal by one warp (the flag is published by lane 0 after the warp's stores)
+template <typename T>
+__device__ __forceinline__ void putmem_signal_warp(const SymmCtx& c, T* dst_local, const T* src, size_t bytes,
+                                                   uint32_t* flag, uint32_t value, SignalOp op, int peer) {
+  copy_warp(symm_at(c, dst_local, peer), src, bytes);
+  __syncwarp();
+  if (ptx::laneid() == 0) {
+    ptx::fence_acq_rel_sys();
+    notify(c, flag, peer, value, op);
+  }
+}
+// broadcast: the root CTA writes `bytes` of its buffer into every peer's copy (one NVLS store stream when a multicast
+// mapping exists, W - 1 unicast puts otherwise). Callers synchronise with a barrier or a signal as with NVSHMEM.
+template <typename T>
+__device__ __forceinline__ void broadcast_block(const SymmCtx& c, T* buf_local, size_t bytes, int root) {
+  if (c.rank != root) return;
+  if (c.mc_base != nullptr) {
+    const int4* s = reinterpret_cast<const int4*>(buf_local);
+    char* d = reinterpret_cast<char*>(mc_ptr(c, buf_local));
+    for (size_t i = threadIdx.x; i < bytes / 16; i += blockDim.x) ptx::multimem_st_v4(d + i * 16, ptx::ld_v4(s + i));
+  } else {
+    for (int p = 1; p < c.world; ++p) putmem_block(c, buf_local, buf_local, bytes, (c.rank + p) % c.world);
+  }
+}
+// fcollect (all-gather of equal blocks): every rank's CTA puts its `bytes` block at offset rank * bytes of every peer's
+// destination buffer.
+template <typename T>
+__device__ __forceinline__ void fcollect_block(const SymmCtx& c, T* dst_local, const T* src, size_t bytes) {
+  char* slot = reinterpret_cast<char*>(dst_local) + size_t(c.rank) * bytes;
+  for (int p = 0; p < c.world; ++p) copy_block(symm_at(c, slot, (c.rank + p) % c.world), src, bytes);
+}
+// teams are strided subsets of the world (triton_dist/runtime/team.py): rank translation is arithmetic
+__device__ __forceinline__ int team_translate_pe(int src_start, int src_stride, int pe_in_src, int dst_start, int dst_stride,
+                                                 int dst_size) {
+  const int w = src_start + pe_in_src * src_stride, d = w - dst_start;
+  return (d < 0 || d % dst_stride != 0 || d / dst_stride >= dst_size) ? -1 : d / dst_stride;
+}
+
 // ---------------------------------------------------------------- cross-GPU barrier (1 CTA, >= world threads)
 // Monotone-phase flag barrier: flags[src] on every rank holds the last phase
 // in which `src` arrived. Caller passes a phase value that increases by one

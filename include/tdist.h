@@ -132,6 +132,12 @@ typedef struct tdist_fused_args {
  * GEMM+AR (gemm_allreduce.py:509-575): one launch each. */
 int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream);
 
+/* Self-test of the NVSHMEM-style device primitives (csrc/kernels/primitives_selftest.cu; no counterpart in the reference,
+ * which tests them through Triton). `buf`: symmetric, >= (3 * world + 2) * 16 bytes, zeroed once; `flags`: symmetric,
+ * >= 2 * world + 1 words, zeroed once; `epoch` must grow with every call. Result: the int at buf + 3 * world * 16 equals
+ * `epoch` on success, -1 otherwise. Call on every rank. */
+int tdist_primitives_selftest(const tdist_symm_ctx* ctx, void* buf, uint32_t* flags, uint32_t epoch, void* stream);
+
 /* ---- MoE helpers (csrc/kernels/moe.cu; reference csrc/lib/moe_utils.cu, kernels/nvidia/moe_utils.py) ---- */
 /* sort (token,k) pairs by expert, pad every expert to block_m rows. meta[0] = padded rows, meta[1] = blocks. */
 int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,

@@ -149,6 +149,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_embedding", [i32, vp, vp, vp, i32, i32, vp])
     sig("tdist_argmax", [i32, vp, vp, i32, i32, ll, vp])
     sig("tdist_moe_align_sort", [vp, i32, i32, i32, vp, vp, vp, vp, i32, vp])
+    sig("tdist_primitives_selftest", [P(SymmCtx), vp, vp, u32, vp])
     sig("tdist_moe_tile_swizzle", [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
     sig("tdist_moe_gather_rows", [vp, vp, vp, vp, i32, i32, i32, i32, vp])
     sig("tdist_moe_topk_reduce", [i32, vp, vp, vp, vp, i32, i32, i32, vp])

@@ -6,6 +6,7 @@
 // tasks are dealt round-robin into one queue per CTA, and the queues + op table are uploaded once. run() is a single
 // cooperative launch of the interpreter kernel.
 #include <cuda_runtime.h>
+#include <stdint.h>
 #include <string.h>
 
 #include <algorithm>
@@ -375,6 +376,35 @@ int tdist_mega_get_trace(void* h, unsigned long long* out, size_t cap_words) {
     return -1;
   }
   TDIST_RT_TRY(cudaMemcpy(out, b->d_trace, words * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// Host-only planning query (no CUDA call, usable without a GPU): how a linear [N, K] (optionally gate|up paired) with
+// batch M is cut for `num_ctas` CTAs. out12 = cols_per_tile, tiles, nblk, R, nsub, kstage, kboxes, stages per tile,
+// scratch bytes, stage buffers that fit next to that scratch, stage buffer bytes, shared-memory limit.
+int tdist_mega_linear_plan(int M, int N, int K, int pair, int has_norm, int num_ctas, int* out12) {
+  if (M < 1 || M > 8 || N < 1 || K < 64 || K % 64 != 0 || num_ctas < 1) {
+    set_error("mega_linear_plan: need 1 <= M <= 8, K a positive multiple of 64");
+    return -1;
+  }
+  OpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.M = M;
+  a.N = N;
+  a.K = K;
+  a.i0 = pair ? 1 : 0;
+  a.in2 = has_norm ? reinterpret_cast<const void*>(uintptr_t(16)) : nullptr;  // only tested for null-ness
+  int cpt = 0;
+  const int tiles = tiles_of(a, OP_LINEAR, num_ctas, &cpt);
+  a.cols_per_tile = cpt;
+  const LinearGeom ge = linear_geom(cpt, K);
+  const int scratch = smem_of(a, OP_LINEAR);
+  const int ring_offset = (scratch + 1023) / 1024 * 1024;
+  int bufs = (kSmemLimit - 2048 - ring_offset - (256 + 2 * 192 + 4096)) / kSlotBytes;
+  bufs = std::max(0, std::min(bufs, kMaxRingStages));
+  const int v[12] = {cpt, tiles, ge.nblk, ge.R, ge.nsub, ge.kstage, ge.kboxes, (pair ? 2 : 1) * ge.nblk * ge.kboxes,
+                     scratch, bufs, kSlotBytes, kSmemLimit};
+  memcpy(out12, v, sizeof(v));
   return 0;
 }
 

@@ -254,6 +254,9 @@ int tdist_mega_compile(void* builder, const tdist_symm_ctx* ctx, uint32_t* ar_fl
 int tdist_mega_run(void* builder, void* stream);
 int tdist_mega_info(void* builder, int* out6); /* ops, tasks, max queue length, smem bytes, CTAs, #cross-rank ops */
 int tdist_mega_op_tiles(void* builder, int op_index);
+/* host-only planning query (no CUDA call): out12 = cols_per_tile, tiles, row blocks, rows per block, k-slabs per stage,
+ * k per stage, stages along K, stages per tile, scratch bytes, stage buffers that fit, stage buffer bytes, smem limit */
+int tdist_mega_linear_plan(int M, int N, int K, int pair, int has_norm, int num_ctas, int* out12);
 /* per-task timeline: stamp globaltimer at the start/end of every task of the following launches; get_trace copies
  * [num_ctas][max_tasks][6] uint64 nanosecond stamps of the last launch to the host (begin, end, linear tasks:
  * dependencies satisfied, activations staged, weight stream consumed, spare) */

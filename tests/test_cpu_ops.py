@@ -104,3 +104,42 @@ def test_language_primitive_map():
     r = subprocess.run([sys.executable, "-m", "triton_dist.test.nvidia.test_language_extra"], cwd=root, capture_output=True, text=True,
                        env={**__import__("os").environ, "PYTHONPATH": str(root)})
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_megakernel_linear_plan_invariants():
+    """Host-side geometry of the megakernel's weight stream (csrc/mega/mega.h linear_geom, builder.cc tiles_of) over the
+    decode shapes of the supported models at TP 1..8: every column and every k is covered exactly by the planned stages,
+    a stage fits its buffer, and at least two buffers fit next to the scratch area."""
+    import ctypes
+
+    from triton_dist import _lib
+
+    lib = _lib.load()
+    if lib is None or not hasattr(lib, "tdist_mega_linear_plan"):
+        import pytest
+
+        pytest.skip("native library not built")
+    shapes = []
+    for hidden, inter, heads, kv, vocab in [(5120, 25600, 64, 8, 151936), (4096, 12288, 32, 8, 151936), (1024, 3072, 16, 8, 151936),
+                                            (8192, 28672, 64, 8, 128256), (5120, 27648, 80, 8, 155136)]:
+        for tp in (1, 2, 4, 8):
+            shapes += [((heads + 2 * kv) * 128 // tp, hidden, 0, 1), (hidden, heads * 128 // tp, 0, 0), (inter // tp, hidden, 1, 1),
+                       (hidden, inter // tp, 0, 0), (vocab // tp, hidden, 0, 1)]
+    out = (ctypes.c_int * 12)()
+    for (N, K, pair, norm) in shapes:
+        if K % 64:
+            continue
+        for M in (1, 8):
+            rc = lib.tdist_mega_linear_plan(M, N, K, pair, norm, 148, ctypes.byref(out))
+            assert rc == 0, (M, N, K)
+            cpt, tiles, nblk, R, nsub, kstage, kboxes, stages, scratch, bufs, slot, limit = list(out)
+            assert tiles * cpt >= N and (tiles - 1) * cpt < N, (N, K, cpt, tiles)
+            assert 1 <= R <= 24 and nblk * R >= cpt and (nblk - 1) * R < cpt
+            assert R * nsub * 128 <= slot and kstage == 64 * nsub and kboxes * kstage >= K and (kboxes - 1) * kstage < K
+            assert stages == (2 if pair else 1) * nblk * kboxes
+            assert cpt <= 256 and tiles <= 148 * ((N + 148 * 256 - 1) // (148 * 256))
+            if M == 1:
+                assert bufs >= 8, (N, K, scratch, bufs)  # decode batch 1 always keeps at least 8 stage buffers
+            # the staged activations [M][K] bf16 share the SM with the stage buffers: batch 8 x K 8192 is over the limit
+            # and compile() refuses it with a clear message; everything up to ~100 KB of activations must fit
+            assert bufs >= 2 or M * K * 2 > 100000, (M, N, K, scratch, bufs)

@@ -167,6 +167,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_mega_run", [vp, vp])
     sig("tdist_mega_info", [vp, P(i32 * 6)])
     sig("tdist_mega_op_tiles", [vp, i32])
+    sig("tdist_mega_linear_plan", [i32, i32, i32, i32, i32, i32, P(i32 * 12)])
     sig("tdist_mega_get_queue", [vp, i32, vp, i32])
     sig("tdist_mega_set_trace", [vp, i32])
     sig("tdist_mega_get_trace", [vp, vp, sz])

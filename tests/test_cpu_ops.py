@@ -143,3 +143,33 @@ def test_megakernel_linear_plan_invariants():
             # the staged activations [M][K] bf16 share the SM with the stage buffers: batch 8 x K 8192 is over the limit
             # and compile() refuses it with a clear message; everything up to ~100 KB of activations must fit
             assert bufs >= 2 or M * K * 2 > 100000, (M, N, K, scratch, bufs)
+
+
+def test_contextual_autotune_picks_fastest_config():
+    """Two tunables inside one thunk: the sweep walks the product of their spaces and caches the fastest combination."""
+    import time
+
+    from triton_dist.autotuner import contextual_autotune, tunable
+
+    calls = []
+
+    @tunable("t_a", {"x": [3, 1, 2]}, key=lambda *a, **k: "k")
+    def fa(x=0):
+        calls.append(("a", x))
+        time.sleep(0.002 * x)
+
+    @tunable("t_b", {"y": [2, 0]}, key=lambda *a, **k: "k")
+    def fb(y=5):
+        calls.append(("b", y))
+        time.sleep(0.002 * y)
+
+    def thunk():
+        fa()
+        fb()
+
+    contextual_autotune(is_dist=False, n_warmup=0, n_repeat=2)(thunk)()
+    assert fa.best["k"] == {"x": 1} and fb.best["k"] == {"y": 0}
+    assert {c for c in calls if c[0] == "a"} == {("a", 1), ("a", 2), ("a", 3)}
+    calls.clear()
+    thunk()  # outside a session the cached winners are used
+    assert calls == [("a", 1), ("b", 0)]

@@ -128,8 +128,14 @@ def _time_thunk(thunk: Callable, warmup: int, iters: int, is_dist: bool, group) 
     return ms
 
 
-def contextual_autotune(is_dist: bool = False, warmup: int = 3, iters: int = 10, group=None):
-    """Decorator: tune every ``@tunable`` reached by the wrapped thunk, then run it once with the winners."""
+def contextual_autotune(is_dist: bool = False, warmup: int = 3, iters: int = 10, group=None, n_repeat: Optional[int] = None,
+                        n_warmup: Optional[int] = None):
+    """Decorator: tune every ``@tunable`` reached by the wrapped thunk, then run it once with the winners.
+    ``n_repeat`` / ``n_warmup`` are the reference's names for ``iters`` / ``warmup`` (autotuner.py:97-102)."""
+    if n_repeat is not None:
+        iters = n_repeat
+    if n_warmup is not None:
+        warmup = n_warmup
 
     def deco(thunk: Callable):
         @functools.wraps(thunk)

@@ -281,6 +281,34 @@ int tdist_gemm(const tdist_gemm_args* a, void* stream) {
   return dispatch(p, bn, grid, static_cast<cudaStream_t>(stream), false);
 }
 
+// Host-side view of the single-CTA kernel's tile walk (the SAME tile_coord the kernel calls): for tile index t writes
+// (shard, 128-row block inside the shard, n block). mode: 0 plain, 1 AG, 2 RS. Returns the number of tiles.
+int tdist_gemm_tile_order(int mode, int M, int N, int world, int rank, int block_n, int group_m, int* out3, int cap_tiles) {
+  if (M < 1 || N < 1 || world < 1 || rank < 0 || rank >= world || block_n < 8 || (mode != 0 && M % world != 0)) {
+    set_error("gemm_tile_order: bad arguments");
+    return -1;
+  }
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = mode;
+  p.M = M;
+  p.N = N;
+  p.ctx.world = world;
+  p.ctx.rank = rank;
+  p.group_m = group_m > 0 ? group_m : 8;
+  p.rows_per_rank = mode == 0 ? M : M / world;
+  const int tiles_n = (N + block_n - 1) / block_n;
+  const int tiles_m = mode == 0 ? (M + kBlockM - 1) / kBlockM : ((p.rows_per_rank + kBlockM - 1) / kBlockM) * world;
+  const int tiles = tiles_m * tiles_n;
+  for (int t = 0; t < tiles && t < cap_tiles; ++t) {
+    const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+    out3[3 * t] = tc.shard;
+    out3[3 * t + 1] = tc.blk;
+    out3[3 * t + 2] = tc.n_blk;
+  }
+  return tiles;
+}
+
 int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream) {
   if (check_common(a) != 0) return -1;
   const SymmCtx c = to_ctx(&f->ctx);

@@ -95,9 +95,9 @@ struct TileCoord {
   int row_end;  // exclusive global row limit for stores (end of shard / matrix)
   int n_blk;
 };
-__device__ __forceinline__ int blocks_per_shard(const GemmParams& p) { return (p.rows_per_rank + kBlockM - 1) / kBlockM; }
+__host__ __device__ __forceinline__ int blocks_per_shard(const GemmParams& p) { return (p.rows_per_rank + kBlockM - 1) / kBlockM; }
 
-__device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int t, int tiles_m, int tiles_n) {
+__host__ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int t, int tiles_m, int tiles_n) {
   TileCoord tc;
   if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
     // shard-major: AG consumes own shard first then rank+1, ...; RS produces the

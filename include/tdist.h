@@ -131,6 +131,9 @@ typedef struct tdist_fused_args {
 /* AG+GEMM (allgather_gemm.py:534-653), GEMM+RS (gemm_reduce_scatter.py:508-583),
  * GEMM+AR (gemm_allreduce.py:509-575): one launch each. */
 int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* stream);
+/* host-side view of the single-CTA kernel's tile walk (the same tile_coord the kernel calls, no CUDA call):
+ * out3[3t..] = (shard, 128-row block inside the shard, n block); mode 0 plain, 1 AG, 2 RS; returns the number of tiles */
+int tdist_gemm_tile_order(int mode, int M, int N, int world, int rank, int block_n, int group_m, int* out3, int cap_tiles);
 
 /* Self-test of the NVSHMEM-style device primitives (csrc/kernels/primitives_selftest.cu; no counterpart in the reference,
  * which tests them through Triton). `buf`: symmetric, >= (3 * world + 2) * 16 bytes, zeroed once; `flags`: symmetric,

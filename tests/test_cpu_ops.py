@@ -173,3 +173,35 @@ def test_contextual_autotune_picks_fastest_config():
     calls.clear()
     thunk()  # outside a session the cached winners are used
     assert calls == [("a", 1), ("b", 0)]
+
+
+def test_kernel_tile_walk_matches_python_restatement():
+    """The tile_coord the GEMM kernel calls (exposed on the host) covers every tile exactly once, visits the shards in the
+    documented order, and agrees with the Python restatements in kernels/nvidia/*_threadblock_swizzle.py."""
+    import ctypes
+
+    from triton_dist import _lib
+    from triton_dist.kernels.nvidia.ag_gemm_threadblock_swizzle import ag_gemm_tile_order
+    from triton_dist.kernels.nvidia.gemm_rs_threadblock_swizzle import gemm_rs_tile_order
+
+    lib = _lib.load()
+    if lib is None or not hasattr(lib, "tdist_gemm_tile_order"):
+        import pytest
+
+        pytest.skip("native library not built")
+    for (M, N, W, bn, gm) in [(8192, 14336, 8, 256, 8), (8192, 4096, 2, 256, 8), (1600, 1000, 4, 192, 3), (4096, 1792, 1, 224, 8)]:
+        for rank in range(W):
+            for mode, ref in ((1, ag_gemm_tile_order), (2, gemm_rs_tile_order)):
+                cap = 1 << 16
+                out = (ctypes.c_int * (3 * cap))()
+                n = lib.tdist_gemm_tile_order(mode, M, N, W, rank, bn, gm, out, cap)
+                got = [(out[3 * t], out[3 * t + 1], out[3 * t + 2]) for t in range(n)]
+                assert len(set(got)) == n == len(got)
+                assert got == ref(M, N, W, rank, block_m=128, block_n=bn, group_m=gm), (M, N, W, rank, mode)
+                first = (rank + (1 if mode == 2 else 0)) % W
+                assert got[0][0] == first and got[-1][0] == (rank if mode == 2 else (rank + W - 1) % W)
+    # plain mode: a permutation of the tile grid
+    out = (ctypes.c_int * (3 * 4096))()
+    n = lib.tdist_gemm_tile_order(0, 1000, 1032, 1, 0, 128, 8, out, 4096)
+    got = {(out[3 * t + 1], out[3 * t + 2]) for t in range(n)}
+    assert n == 8 * 9 and got == {(m, c) for m in range(8) for c in range(9)}

@@ -173,6 +173,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_mega_get_trace", [vp, vp, sz])
     sig("tdist_mega_destroy", [vp])
     sig("tdist_gemm", [P(GemmArgs), vp])
+    sig("tdist_gemm_tile_order", [i32, i32, i32, i32, i32, i32, i32, vp, i32])
     sig("tdist_gemm_fused", [P(GemmArgs), P(FusedArgs), vp])
 
 

@@ -1,0 +1,44 @@
+"""The public API checklist of SURVEY.md section 8: every name a user of the reference imports must exist here."""
+
+
+def test_public_api_checklist():
+    import importlib
+    spec = {
+     "triton_dist.utils": "initialize_distributed finalize_distributed init_seed init_nvshmem_by_torch_process_group nvshmem_create_tensor nvshmem_create_tensors nvshmem_free_tensor_sync nvshmem_barrier_all_on_stream nvshmem_signal_wait TorchStreamWrapper NVSHMEM_SIGNAL_DTYPE perf_func dist_print group_profile get_torch_prof_ctx assert_allclose generate_data sleep_async CUDA_CHECK is_cuda is_hip has_tma has_fullmesh_nvlink is_nvshmem_multimem_supported supports_p2p_native_atomic requires launch_cooperative_grid_options get_intranode_max_speed get_nvlink_max_speed get_numa_world_size get_device_property get_device_max_shared_memory_size",
+     "triton_dist.kernels.allreduce": "AllReduceMethod to_allreduce_method get_allreduce_methods",
+     "triton_dist.kernels.common_ops": "wait_eq set_signal BarrierAllContext barrier_all_on_stream",
+     "triton_dist.kernels.nvidia": "ag_gemm create_ag_gemm_context gemm_persistent gemm_non_persistent get_auto_all_gather_method AllGatherMethod cp_engine_producer_all_gather_intra_node cp_engine_producer_all_gather_inter_node gemm_rs create_gemm_rs_context create_gemm_ar_context gemm_allreduce_op create_ll_gemm_ar_context low_latency_gemm_allreduce_op fast_allgather create_fast_allgather_context _forward_pull_kernel _forward_push_2d_kernel _forward_push_3d_kernel _forward_push_2d_ll_kernel _forward_push_2d_ll_multimem_kernel _forward_push_numa_2d_kernel _forward_push_numa_2d_ll_kernel _forward_push_numa_2d_ll_multinode_kernel create_all_to_all_context fast_all_to_all all_to_all_post_process create_ag_group_gemm_context ag_group_gemm create_moe_rs_context gqa_fwd_batch_decode gqa_fwd_batch_decode_aot gqa_fwd_batch_decode_persistent gqa_fwd_batch_decode_persistent_aot gqa_fwd_batch_decode_intra_rank gqa_fwd_batch_decode_intra_rank_aot kernel_gqa_fwd_batch_decode_split_kv_persistent kernel_inter_rank_gqa_fwd_batch_decode_combine_kv get_triton_combine_kv_algo_info fused_sp_ag_attn_intra_node fused_sp_ag_attn_inter_node create_sp_ag_attention_context_intra_node create_sp_ag_attention_context_inter_node",
+     "triton_dist.kernels.nvidia.allreduce": "create_allreduce_ctx all_reduce get_auto_allreduce_method",
+     "triton_dist.kernels.nvidia.reduce_scatter": "create_reduce_scater_2d_ctx reduce_scatter_2d_op ring_reduce",
+     "triton_dist.kernels.nvidia.moe_reduce_rs": "run_moe_reduce_rs",
+     "triton_dist.kernels.nvidia.common_ops": "BarrierAllContext barrier_all_on_stream",
+     "triton_dist.kernels.nvidia.gemm_perf_model": "",
+     "triton_dist.kernels.nvidia.comm_perf_model": "",
+     "triton_dist.kernels.nvidia.ep_a2a": "",
+     "triton_dist.kernels.nvidia.moe_utils": "",
+     "triton_dist.layers.nvidia": "TP_MLP TP_Attn TP_MoE GemmARLayer EPAll2AllLayer AllGatherLayer SpGQAFlashDecodeAttention CommOp",
+     "triton_dist.models": "ModelConfig AutoLLM AutoTokenizer DenseLLM Qwen3MoE KV_Cache Engine",
+     "triton_dist.mega_triton_kernel": "ModelBuilder Qwen3Model PagedKVCache",
+     "triton_dist.autotuner": "contextual_autotune",
+     "triton_dist.language": "",
+    }
+    missing = []
+    for mod, names in spec.items():
+        m = importlib.import_module(mod)
+        for n in names.split():
+            if not hasattr(m, n):
+                missing.append(f"{mod}.{n}")
+    from triton_dist.layers.nvidia import TP_MLP, TP_Attn
+    for cls in (TP_MLP, TP_Attn):
+        for meth in "_init_parameters _init_ctx _init_AR_ctx _init_gemm_ar_ctx torch_fwd dist_triton_fwd dist_triton_AR_fwd dist_triton_gemm_ar_fwd finalize".split():
+            if not hasattr(cls, meth): missing.append(f"{cls.__name__}.{meth}")
+    for meth in "torch_ag_gemm dist_triton_ag_gemm torch_gemm_rs dist_triton_gemm_rs".split():
+        if not hasattr(TP_MLP, meth): missing.append(f"TP_MLP.{meth}")
+    from triton_dist.mega_triton_kernel import ModelBuilder
+    for meth in "make_fc1 make_fc2 make_qkv_proj make_o_proj make_linear make_attn make_silu_mul_up make_qk_norm_rope_update_kvcache make_rms_norm make_add make_barrier_all_intra_node make_allreduce make_prefetch create_symm_tensor compile run finalize".split():
+        if not hasattr(ModelBuilder, meth): missing.append(f"ModelBuilder.{meth}")
+    from triton_dist.models import DenseLLM
+    for meth in "set_fwd init_triton_dist_ctx init_triton_dist_AR_ctx init_triton_dist_gemm_ar_ctx inference".split():
+        if not hasattr(DenseLLM, meth): missing.append(f"DenseLLM.{meth}")
+    assert not missing, missing
+

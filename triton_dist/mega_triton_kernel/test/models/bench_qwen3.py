@@ -52,6 +52,8 @@ if __name__ == "__main__":
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--modes", default="torch,torch_graph,triton_dist_AR,triton_dist_gemm_ar,mega")
     ap.add_argument("--json", default="")
+    ap.add_argument("--profile", action="store_true", help="megakernel: per-task timeline of one step (summary in the JSON, chrome "
+                    "trace in prof/mega_rank<r>.json)")
     args = ap.parse_args()
     group, rank, world = setup()
     cfg = ModelConfig(model_name=args.model, max_length=args.max_length, dtype=torch.bfloat16, rank=rank, world_size=world)
@@ -80,6 +82,16 @@ if __name__ == "__main__":
             _, ms = perf_func_max_over_ranks(step, args.iters, 3)
             res["mega_ms"] = ms
             res["mega_graph"] = builder.info()
+            if args.profile:
+                import os
+
+                builder.enable_profiling(True)
+                step()
+                torch.cuda.synchronize()
+                res["mega_task_profile"] = builder.profile_summary()
+                os.makedirs("prof", exist_ok=True)
+                builder.dump_trace(f"prof/mega_rank{rank}.json")
+                builder.enable_profiling(False)
             mega.finalize()
     wb = weight_bytes_per_step(dense)
     pk = measured_peaks()

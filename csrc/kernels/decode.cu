@@ -688,9 +688,8 @@ int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vo
 // ------------------------------------------------------------------ flash decode without any allocation
 //
 // tdist_flash_decode() needs a caller-provided fp32 scratch buffer for the per-split partial results. Some callers
-// cannot provide one: code running inside a CUDA-graph capture or inside a serving loop that has handed all device
-// memory to its own pool, plugins that are loaded into a process whose allocator they must not touch, and C callers
-// that have no allocator wired up at all. For them the scratch below lives inside the library image: the driver
+// cannot provide one: a serving loop that has handed all device memory to its own pool, plugins that are loaded into a
+// process whose allocator they must not touch, and C callers that have no allocator wired up at all. For them the scratch below lives inside the library image: the driver
 // reserves it once per GPU when the module is loaded and keeps it until the process exits, so this entry point never
 // calls cudaMalloc / cudaFree (nor any torch or library routine that could).
 //
@@ -699,8 +698,8 @@ int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vo
 //
 // Two things to know when calling it:
 //  * The first call on each GPU looks up where that GPU's copy of the scratch lives (cudaGetSymbolAddress, with the
-//    calling thread's current device). That lookup is a host-side query which may load the module, so make the first
-//    call on a device ordinary (eager) work; later calls on that device only launch kernels.
+//    calling thread's current device). That lookup is a host-side query which may load the module, so the first call
+//    on a device has to come before any stream capture is started; later calls on that device only launch kernels.
 //  * There is ONE scratch per GPU, shared by every call and left holding the previous call's partials. Calls issued to
 //    the same stream are ordered and safe. Two calls that can run at the same time on one GPU (different streams,
 //    different host threads) would overwrite each other's partials: serialise them or use tdist_flash_decode().

@@ -39,6 +39,21 @@ def _case(seed, B, Hq, Hkv, kv_len, page=16):
     return q, kc, vc, bt, lens
 
 
+def _torch_decode_fp32(q, kc, vc, bt, lens, scale):
+    """Plain PyTorch fp32 paged GQA decode attention: the independent oracle for both entry points."""
+    B, Hq, D = q.shape
+    page, Hkv = kc.shape[1], kc.shape[2]
+    out = torch.empty(B, Hq, D, device=q.device, dtype=torch.float32)
+    for b in range(B):
+        n = int(lens[b])
+        pages = bt[b, : (n + page - 1) // page].long()
+        k = kc[pages].reshape(-1, Hkv, D)[:n].float().repeat_interleave(Hq // Hkv, dim=1)  # [n, Hq, D]
+        v = vc[pages].reshape(-1, Hkv, D)[:n].float().repeat_interleave(Hq // Hkv, dim=1)
+        s = torch.einsum("hd,nhd->hn", q[b].float(), k) * scale
+        out[b] = torch.einsum("hn,nhd->hd", torch.softmax(s, dim=-1), v)
+    return out
+
+
 def test_noalloc_decode_matches_buffered_decode_twice():
     from triton_dist import _lib
 
@@ -61,6 +76,8 @@ def test_noalloc_decode_matches_buffered_decode_twice():
         assert rc == 0, lib.tdist_last_error()
         torch.cuda.synchronize()
         torch.testing.assert_close(out_new.float(), out_ref.float(), atol=2e-2, rtol=2e-2)
+        # and both against plain fp32 PyTorch, so that a fault shared by the two entry points cannot hide
+        torch.testing.assert_close(out_new.float(), _torch_decode_fp32(q, kc, vc, bt, lens, scale), atol=2e-2, rtol=2e-2)
 
 
 def test_noalloc_decode_rejects_oversized_problem():

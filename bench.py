@@ -26,21 +26,79 @@ import time
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
-sys.path.insert(0, str(ROOT))
 
 M, K_HID, N_FFN = 8192, 4096, 14336
 METRIC = "ag_gemm+gemm_rs aggregate TFLOP/s (Llama-3-8B MLP shape, TP=N)"
+NVLINK_GBS = 770.0  # measured peer-copy rate per direction per GPU (B200_PROFILING.md)
+REFERENCE_CLASS = ("reference TP_MLP.torch_ag_gemm + TP_MLP.torch_gemm_rs (layers/nvidia/tp_mlp.py:231-264, NCCL + cuBLAS): "
+                   "the unmodified reference source; its Triton kernels cannot be built offline (DESIGN.md section 6)")
 
 
-def reference_arm(args) -> None:
-    """The reference needs its Triton fork (LLVM + NVIDIA toolchain downloads) and nvshmem4py; the offline install
-    fails, so there is nothing to run."""
-    ref = ROOT / "baseline" / "_ref"
-    why = "reference not installable offline: python/setup.py downloads LLVM/toolchain (URLError), nvshmem4py absent"
-    if ref.exists() and any(ref.iterdir()):
-        why = "baseline/_ref present but triton_dist needs its patched Triton + NVSHMEM, which are not in this image"
-    if int(os.environ.get("RANK", "0")) == 0:
-        print(json.dumps({"impl": "reference", "unavailable": why}))
+def measured_peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback"}
+
+
+def reference_tree():
+    """Where the unmodified reference package lives: baseline/_ref (populated by scripts/install_reference.sh, travels
+    to the GPU box) or the read-only checkout of the authoring container."""
+    for cand in (ROOT / "baseline" / "_ref" / "triton_dist", Path("/root/reference/python/triton_dist")):
+        if (cand / "layers" / "nvidia" / "tp_mlp.py").exists():
+            return cand
+    return None
+
+
+def load_reference_tp_mlp(tree: Path):
+    """Import the reference's layers/nvidia/tp_mlp.py UNMODIFIED. Its module-level imports of the Triton-compiled kernel
+    modules (which need the reference's own Triton fork + NVSHMEM, not buildable offline) resolve to empty placeholder
+    modules, so only its torch / NCCL methods can run: touching anything else raises. Nothing of this repository is
+    importable in this process (the repo root is not on sys.path and `triton_dist` is claimed by the placeholders)."""
+    import importlib.abc
+    import importlib.machinery
+    import importlib.util
+    import types
+
+    class _Placeholder:
+        def __init__(self, name):
+            self._name = name
+
+        def __call__(self, *a, **k):
+            raise RuntimeError(f"reference symbol {self._name} needs the reference's Triton/NVSHMEM build (unavailable offline)")
+
+        def __getattr__(self, item):
+            if item.startswith("__"):
+                raise AttributeError(item)
+            return _Placeholder(f"{self._name}.{item}")
+
+    class _StubModule(types.ModuleType):
+        __path__ = []  # a package, so that submodule imports go through the finder as well
+
+        def __getattr__(self, item):
+            if item.startswith("__"):
+                raise AttributeError(item)
+            return _Placeholder(f"{self.__name__}.{item}")
+
+    class _Finder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
+        def find_spec(self, fullname, path=None, target=None):
+            if fullname == "triton_dist" or fullname.startswith("triton_dist."):
+                return importlib.machinery.ModuleSpec(fullname, self, is_package=True)
+            return None
+
+        def create_module(self, spec):
+            return _StubModule(spec.name)
+
+        def exec_module(self, module):
+            pass
+
+    assert "triton_dist" not in sys.modules, "the reference arm must not have this repository's package loaded"
+    sys.meta_path.insert(0, _Finder())
+    spec = importlib.util.spec_from_file_location("reference_tp_mlp", str(tree / "layers" / "nvidia" / "tp_mlp.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.TP_MLP
 
 
 class ClockSampler:
@@ -103,7 +161,7 @@ def decode_section(rank: int, world: int, steps: int):
 
     from triton_dist.mega_triton_kernel import ModelBuilder, Qwen3Model
     from triton_dist.models import DenseLLM, ModelConfig
-    from triton_dist.utils import measured_peaks, perf_func_max_over_ranks
+    from triton_dist.utils import perf_func_max_over_ranks
 
     cfg = ModelConfig(model_name="Qwen/Qwen3-32B", max_length=1024, dtype=torch.bfloat16, rank=rank, world_size=world)
     dense = DenseLLM(cfg, None)
@@ -147,24 +205,44 @@ def main() -> None:
     ap.add_argument("--impl", default="tdist", choices=["tdist", "torch", "reference"])
     ap.add_argument("--no-decode", action="store_true", help="skip the Qwen3-32B decode section")
     args = ap.parse_args()
-    if args.impl == "reference":
-        reference_arm(args)
-        return
     args.warmup = max(args.warmup, 3)
-
-    import torch
-    import torch.distributed as dist
-
     os.environ.setdefault("RANK", "0")
     os.environ.setdefault("WORLD_SIZE", str(1))
     os.environ.setdefault("LOCAL_RANK", "0")
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29555")
-    from triton_dist.kernels.nvidia.allgather_gemm import ag_gemm, create_ag_gemm_context, torch_ag_gemm
-    from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs, gemm_rs_op, torch_gemm_rs
-    from triton_dist.utils import NVLINK_GBS_MEASURED, finalize_distributed, initialize_distributed, measured_peaks
 
-    initialize_distributed(seed=1234)
+    ref_mlp_cls = None
+    if args.impl == "reference":
+        tree = reference_tree()
+        why = None
+        if tree is None:
+            why = "no reference source tree (baseline/_ref/triton_dist missing: run scripts/install_reference.sh)"
+        else:
+            try:
+                ref_mlp_cls = load_reference_tp_mlp(tree)
+            except Exception as e:  # noqa: BLE001
+                why = f"reference layers/nvidia/tp_mlp.py failed to load: {type(e).__name__}: {e}"[:200]
+        if why is not None:
+            if int(os.environ["RANK"]) == 0:
+                print(json.dumps({"impl": "reference", "unavailable": why}))
+            return
+    else:
+        sys.path.insert(0, str(ROOT))
+
+    import torch
+    import torch.distributed as dist
+
+    if args.impl == "reference":
+        # plain torch.distributed: nothing of this repository runs in the reference arm
+        torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+        finalize = dist.destroy_process_group
+    else:
+        from triton_dist.utils import finalize_distributed, initialize_distributed
+
+        initialize_distributed(seed=1234)
+        finalize = finalize_distributed
     rank, world = dist.get_rank(), dist.get_world_size()
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -175,22 +253,51 @@ def main() -> None:
     w_down = ((torch.rand(K_HID, k_loc, device=dev, generator=g) * 2 - 1) * 0.02).to(dtype)  # row-parallel [N, K/W]
     x_host = ((torch.rand(m_loc, K_HID, generator=torch.Generator().manual_seed(rank)) * 2 - 1)).to(dtype).pin_memory()
     x_dev = x_host.to(dev, non_blocking=True)
-    ag_ctx = create_ag_gemm_context(x_dev, w_up, rank, world, max_M=M, num_local_ranks=world)
-    rs_ctx = create_gemm_rs_context(M, K_HID, rank, world, world, dtype)
-    h = torch.empty((M, n_loc), dtype=dtype, device=dev)
-    y = torch.empty((m_loc, K_HID), dtype=dtype, device=dev)
     flush = torch.empty(256 * 2**20, dtype=torch.uint8, device=dev)
-    res_host = torch.empty(8, dtype=torch.float32).pin_memory()
+    y_host = [torch.empty((m_loc, K_HID), dtype=dtype).pin_memory() for _ in range(2)]
+    cleanup = []
 
     if args.impl == "tdist":
-        def step(x):
-            ag_gemm(x, w_up, ag_ctx, out=h)
-            return gemm_rs_op(h, w_down, rs_ctx, output=y)
+        from triton_dist.kernels.nvidia.allgather_gemm import ag_gemm, create_ag_gemm_context
+        from triton_dist.kernels.nvidia.gemm_reduce_scatter import create_gemm_rs_context, gemm_rs_op
+
+        ag_ctx = create_ag_gemm_context(x_dev, w_up, rank, world, max_M=M, num_local_ranks=world)
+        rs_ctx = create_gemm_rs_context(M, K_HID, rank, world, world, dtype)
+        cleanup += [ag_ctx.finalize, rs_ctx.finalize]
+        h = torch.empty((M, n_loc), dtype=dtype, device=dev)
+        y = torch.empty((m_loc, K_HID), dtype=dtype, device=dev)
+
+        def op_ag(x):
+            return ag_gemm(x, w_up, ag_ctx, out=h)
+
+        def op_rs(hh):
+            return gemm_rs_op(hh, w_down, rs_ctx, output=y)
         launches_per_step = 2
-    else:
-        def step(x):
-            return torch_gemm_rs(torch_ag_gemm(x, w_up), w_down)
+    elif args.impl == "torch":
+        from triton_dist.kernels.nvidia.allgather_gemm import torch_ag_gemm
+        from triton_dist.kernels.nvidia.gemm_reduce_scatter import torch_gemm_rs
+
+        def op_ag(x):
+            return torch_ag_gemm(x, w_up)
+
+        def op_rs(hh):
+            return torch_gemm_rs(hh, w_down)
         launches_per_step = 0
+    else:
+        mlp = ref_mlp_cls(rank=rank, world_size=world, group=dist.group.WORLD)
+        mlp.gate_up_proj, mlp.down_proj = w_up, w_down  # what TP_MLP._init_parameters leaves behind: the local shards
+        op_ag, op_rs = mlp.torch_ag_gemm, mlp.torch_gemm_rs
+        launches_per_step = 0
+
+    def step(x):
+        return op_rs(op_ag(x))
+
+    # in-process comparator of the tdist arm: the reference's oracle path (NCCL + cuBLAS through torch)
+    def baseline_step(x):
+        from triton_dist.kernels.nvidia.allgather_gemm import torch_ag_gemm
+        from triton_dist.kernels.nvidia.gemm_reduce_scatter import torch_gemm_rs
+
+        return torch_gemm_rs(torch_ag_gemm(x, w_up), w_down)
 
     def timed_device(n_steps: int) -> float:
         """Sum of per-step device times (ms); L2 flushed before every step, outside the timed span."""
@@ -205,31 +312,45 @@ def main() -> None:
         torch.cuda.synchronize()
         return sum(s.elapsed_time(e) for s, e in evs)
 
-    # end-to-end: every step copies its input from pinned host memory and reads a result back. The copies run on a
-    # copy stream into two alternating device buffers so that the H2D of step i+1 overlaps the compute of step i
+    # end-to-end: every step copies its input from pinned host memory and reads the WHOLE result tensor back into pinned
+    # host memory. Input copies run on one copy stream into two alternating device buffers, result copies on another
+    # out of two alternating device buffers, so that H2D of step i+1 and D2H of step i-1 overlap the compute of step i
     # (what a serving loop does); the timed span covers all copies, all compute and all read-backs of the K steps.
-    copy_stream = torch.cuda.Stream()
+    h2d_stream, d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
     x_bufs = [torch.empty_like(x_dev), torch.empty_like(x_dev)]
+    y_bufs = [torch.empty((m_loc, K_HID), dtype=dtype, device=dev) for _ in range(2)]
 
     def timed_e2e(n_steps: int) -> float:
         cur = torch.cuda.current_stream()
         start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ready = [torch.cuda.Event(), torch.cuda.Event()]
         consumed = [torch.cuda.Event(), torch.cuda.Event()]
-        copy_stream.wait_stream(cur)
+        produced = [torch.cuda.Event(), torch.cuda.Event()]
+        drained = [torch.cuda.Event(), torch.cuda.Event()]
+        h2d_stream.wait_stream(cur)
+        d2h_stream.wait_stream(cur)
         start.record(cur)
-        copy_stream.wait_event(start)
+        h2d_stream.wait_event(start)
+        d2h_stream.wait_event(start)
         for i in range(n_steps):
             b = i & 1
-            with torch.cuda.stream(copy_stream):
+            with torch.cuda.stream(h2d_stream):
                 if i >= 2:
-                    copy_stream.wait_event(consumed[b])  # buffer b is free once step i-2 has read it
+                    h2d_stream.wait_event(consumed[b])  # buffer b is free once step i-2 has read it
                 x_bufs[b].copy_(x_host, non_blocking=True)  # H2D of this step's input
-                ready[b].record(copy_stream)
+                ready[b].record(h2d_stream)
             cur.wait_event(ready[b])
+            if i >= 2:
+                cur.wait_event(drained[b])  # result buffer b has been read back
             out = step(x_bufs[b])
+            y_bufs[b].copy_(out)  # device-side hand-over (the op's output buffer is reused by the next step)
             consumed[b].record(cur)
-            res_host.copy_(out[0, :8].float(), non_blocking=True)  # D2H read of the step's result
+            produced[b].record(cur)
+            with torch.cuda.stream(d2h_stream):
+                d2h_stream.wait_event(produced[b])
+                y_host[b].copy_(y_bufs[b], non_blocking=True)  # D2H of the step's result [M/W, 4096]
+                drained[b].record(d2h_stream)
+        cur.wait_stream(d2h_stream)
         stop.record(cur)
         torch.cuda.synchronize()
         return start.elapsed_time(stop)
@@ -270,11 +391,10 @@ def main() -> None:
         return float(t.item())
 
     dist.barrier()
-    ag_ms = op_ms((lambda: ag_gemm(x_dev, w_up, ag_ctx, out=h)) if args.impl == "tdist" else (lambda: torch_ag_gemm(x_dev, w_up)))
-    rs_ms = op_ms((lambda: gemm_rs(h, w_down, rs_ctx)) if args.impl == "tdist" else (lambda: torch_gemm_rs(h, w_down)))
-    base_ms = None
-    if args.impl == "tdist":
-        base_ms = op_ms(lambda: torch_gemm_rs(torch_ag_gemm(x_dev, w_up), w_down))
+    ag_ms = op_ms(lambda: op_ag(x_dev))
+    h_in = op_ag(x_dev)
+    rs_ms = op_ms(lambda: op_rs(h_in))
+    base_ms = op_ms(lambda: baseline_step(x_dev)) if args.impl == "tdist" else None
 
     flops_step = 2.0 * M * N_FFN * K_HID * 2  # whole job, both GEMMs
     ms_per_step = total_ms / args.steps
@@ -282,7 +402,7 @@ def main() -> None:
     pk = measured_peaks()
     per_gpu_flops = flops_step / 2 / world
     link_bytes = (world - 1) * m_loc * K_HID * 2
-    roof_ms = max(per_gpu_flops / (pk["bf16_tflops"] * 1e9), link_bytes / (NVLINK_GBS_MEASURED * 1e6))
+    roof_ms = max(per_gpu_flops / (pk["bf16_tflops"] * 1e9), link_bytes / (NVLINK_GBS * 1e6))
     out = {
         "metric": METRIC, "value": round(value, 2), "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "strong",
@@ -293,8 +413,10 @@ def main() -> None:
                    "timing": "CUDA events per step, max over ranks"},
         "clocks": clocks,
         "e2e": {"value": round(flops_step / (e2e_ms / args.steps * 1e-3) / 1e12, 2), "unit": "TFLOP/s",
-                "ms_per_step": round(e2e_ms / args.steps, 5), "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 32,
-                "note": "H2D of step i+1 overlaps compute of step i (copy stream, two device buffers)"},
+                "ms_per_step": round(e2e_ms / args.steps, 5), "h2d_bytes_per_step": x_host.numel() * 2,
+                "d2h_bytes_per_step": y_host[0].numel() * 2,
+                "note": "per rank; H2D of step i+1 and D2H of step i-1 overlap the compute of step i (two copy streams, "
+                        "double-buffered device and pinned host buffers); the whole result [M/W, 4096] is read back"},
         "gpu_launches": launches_per_step * args.steps,
         "breakdown": {
             "ag_gemm_ms": round(ag_ms, 5), "ag_gemm_tflops_per_gpu": round(per_gpu_flops / ag_ms / 1e9, 1),
@@ -306,8 +428,11 @@ def main() -> None:
             "speedup_vs_torch_nccl_cublas": None if base_ms is None else round(base_ms / ms_per_step, 3),
         },
     }
-    ag_ctx.finalize()
-    rs_ctx.finalize()
+    if args.impl == "reference":
+        out["reference_class"] = REFERENCE_CLASS
+        out["reference_source"] = str(reference_tree())
+    for fn in cleanup:
+        fn()
     if args.impl == "tdist" and not args.no_decode and os.environ.get("TDIST_BENCH_DECODE", "1") != "0":
         try:
             out["decode"] = decode_section(rank, world, max(args.steps, 10))
@@ -315,7 +440,7 @@ def main() -> None:
             out["decode"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0:
         print(json.dumps(out))
-    finalize_distributed()
+    finalize()
 
 
 if __name__ == "__main__":

@@ -179,6 +179,23 @@ static int want_cta_pair(const tdist_gemm_args* a) {
   return a->M >= 2 * kBlockM;
 }
 
+// protocol variant of a fused op: explicit argument > environment (TDIST_AG_VARIANT / TDIST_RS_VARIANT: 1 = point to
+// point, 2 = NVLS) > NVLS whenever the heap has a multicast mapping
+static int pick_variant(const tdist_fused_args* f, const SymmCtx& c, const char* env_name) {
+  int v = f->variant;
+  if (v == 0) {
+    const char* e = getenv(env_name);
+    if (e) v = atoi(e);
+  }
+  if (v == 0) v = (c.mc_base != nullptr && c.world > 1) ? 2 : 1;
+  if (v == 2 && c.mc_base == nullptr) v = -1;
+  return v;
+}
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
 static double g_last_cost = 0;
 static int pick_block_n(int M_tiles, int N, int ctas, int forced) {
   static const int cands[] = {256, 224, 192, 160, 128, 112, 96, 64, 32};
@@ -328,6 +345,7 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
   p.group_m = a->group_m > 0 ? a->group_m : 8;
   const int sms = a->num_sms > 0 ? a->num_sms : sm_count();
   int comm = f->num_comm_ctas;
+  bool comm_given = comm >= 0;
   int tiles_m;
   if (W == 1 && (f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS)) {
     // a single rank has nothing to gather or scatter: run the plain GEMM straight from / into the caller's tensors
@@ -346,10 +364,44 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     }
     p.rows_per_rank = a->M / W;
     p.a_local = a->a;
+    p.a_lda = a->lda;
     p.a_ws = f->ws;
     p.c = a->c;
     p.ldc = a->ldc;
     if (W == 1) comm = 0;
+    if (comm < 0) comm = env_int("TDIST_AG_PUSH_CTAS", -1);
+    comm_given = comm >= 0;
+    const int v = pick_variant(f, c, "TDIST_AG_VARIANT");
+    if (v < 0) {
+      set_error("ag_gemm: the NVLS variant needs a heap with a multicast mapping");
+      return -1;
+    }
+    p.variant = v == 2 ? VARIANT_NVLS : VARIANT_LEGACY;
+    const size_t par_need = size_t(a->M) * a->K * 2;
+    p.ws_parity_bytes = f->ws_bytes > 0 ? f->ws_bytes / 2 : par_need;
+    if (p.ws_parity_bytes < par_need) {
+      set_error("ag_gemm: workspace too small (need 2 * M * K elements)");
+      return -1;
+    }
+    const int bps_ag = (p.rows_per_rank + kBlockM - 1) / kBlockM;
+    if (p.variant == VARIANT_NVLS) {
+      // `slices` CTAs share a 128-row block; the other push CTAs work ahead on the following blocks
+      int slices = env_int("TDIST_AG_SLICES", 8);
+      if (slices < 1) slices = 1;
+      if (slices > kAgSlots) slices = kAgSlots;
+      while (slices & (slices - 1)) slices &= slices - 1;  // power of two (divides 128)
+      p.ag_slices = slices;
+      if (f->flags_words > 0 && f->flags_words < size_t(W) * bps_ag * kAgSlots) {
+        set_error("ag_gemm: flag area too small for the NVLS protocol (need W * ceil(M/W/128) * 32 words)");
+        return -1;
+      }
+    } else if (a->lda != a->K) {
+      set_error("ag_gemm: the point-to-point push needs a contiguous shard (lda == K)");
+      return -1;
+    } else if (f->flags_words > 0 && f->flags_words < size_t(W) * bps_ag * kAgParts) {
+      set_error("ag_gemm: flag area too small (need W * ceil(M/W/128) * 4 words)");
+      return -1;
+    }
     if (comm < 0) {
       // as many push CTAs as the wave count of the GEMM part tolerates (they are free until they add a wave)
       const int tm = ((a->M / W + kBlockM - 1) / kBlockM) * W;
@@ -363,10 +415,9 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
         }
       }
     }
-    const size_t par = size_t(a->M) * a->K * 2;
     if (make_tmap(&p.tma_a_local, a->a, p.rows_per_rank, a->K, a->lda, kBlockM) != 0) return -1;
     if (make_tmap(&p.tma_a[0], f->ws, a->M, a->K, a->K, kBlockM) != 0) return -1;
-    if (make_tmap(&p.tma_a[1], static_cast<char*>(f->ws) + par, a->M, a->K, a->K, kBlockM) != 0) return -1;
+    if (make_tmap(&p.tma_a[1], static_cast<char*>(f->ws) + p.ws_parity_bytes, a->M, a->K, a->K, kBlockM) != 0) return -1;
     tiles_m = ((p.rows_per_rank + kBlockM - 1) / kBlockM) * W;
   } else if (f->mode == TDIST_GEMM_RS) {
     // a->a = [M, K/W] local; f->ws = symmetric scatter buffer [2][W][M/W][N]; f->out = [M/W, N]
@@ -379,6 +430,17 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.out = f->out;
     p.ldc = a->N;
     comm = 0;
+    const int v = pick_variant(f, c, "TDIST_RS_VARIANT");
+    p.variant = v == 2 ? VARIANT_NVLS : VARIANT_LEGACY;  // without multicast the pull variant sums plain peer loads
+    if (v < 0) p.variant = VARIANT_LEGACY;
+    p.use_mc = c.mc_base != nullptr;
+    // both layouts ([W][M/W][N] scatter slots, [M][N] partial buffer) need M * N elements per parity
+    const size_t par_need = size_t(a->M) * a->N * 2;
+    p.ws_parity_bytes = f->ws_bytes > 0 ? f->ws_bytes / 2 : par_need;
+    if (p.ws_parity_bytes < par_need) {
+      set_error("gemm_rs: workspace too small (need 2 * M * N elements)");
+      return -1;
+    }
     if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
     tiles_m = ((p.rows_per_rank + kBlockM - 1) / kBlockM) * W;
   } else if (f->mode == TDIST_GEMM_AR) {
@@ -389,6 +451,11 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.ldc = a->ldc;
     p.ar_one_shot = f->ar_one_shot;
     p.use_mc = c.mc_base != nullptr && f->use_mc;
+    p.ws_parity_bytes = f->ws_bytes > 0 ? f->ws_bytes / 2 : size_t(a->M) * a->ldc * 2;
+    if (p.ws_parity_bytes < size_t(a->M) * a->ldc * 2) {
+      set_error("gemm_ar: workspace too small (need 2 * M * ldc elements)");
+      return -1;
+    }
     if (comm < 0) comm = 8;
     if (comm < 1) comm = 1;
     if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
@@ -397,20 +464,34 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     set_error("gemm_fused: unknown mode");
     return -1;
   }
-  // AG at 8 ranks (1024 rows per rank at the flagship shape) measured 0.159 ms on single-CTA tiles against 0.213 ms on
-  // pair tiles (the 256-row tile waits for twice as many arriving row blocks); at 2 ranks the pair kernel wins
-  // (0.328 vs 0.383 ms). Unless forced, AG therefore takes pair tiles only from 2048 rows per rank.
+  // Tile kind. Point-to-point AG at 8 ranks measured 0.159 ms on single-CTA tiles against 0.213 ms on pair tiles (a
+  // 256-row tile waits for twice as many arriving row blocks), so that variant takes pair tiles only from 2048 rows per
+  // rank; with the NVLS broadcast all shards arrive block by block and pair tiles are the default.
   const bool pair_ok = f->mode == TDIST_GEMM_RS || a->cta_group == 2 || getenv("TDIST_GEMM_CTA_GROUP") != nullptr ||
-                       p.rows_per_rank >= 16 * kBlockM;
+                       p.variant == VARIANT_NVLS || p.rows_per_rank >= 16 * kBlockM;
+  const bool nvls_ag = f->mode == TDIST_GEMM_AG && p.variant == VARIANT_NVLS;
+  auto round_push = [&](int cm) {
+    // NVLS push: whole groups of `ag_slices` CTAs, so that each block is pushed by one group
+    if (!nvls_ag) return cm;
+    cm = cm / p.ag_slices * p.ag_slices;
+    return cm < p.ag_slices ? p.ag_slices : cm;
+  };
+  auto check_rs_flags = [&](int bn) {
+    if (f->mode != TDIST_GEMM_RS || p.variant != VARIANT_NVLS || f->flags_words == 0) return 0;
+    const size_t need = size_t(W) * ((p.rows_per_rank + kBlockM - 1) / kBlockM) * ((a->N + bn - 1) / bn);
+    if (f->flags_words >= need) return 0;
+    set_error("gemm_rs: flag area too small for the NVLS protocol (need W * ceil(M/W/128) * ceil(N/BLOCK_N) words)");
+    return -1;
+  };
   if ((f->mode == TDIST_GEMM_AG || f->mode == TDIST_GEMM_RS) && want_cta_pair(a) && pair_ok && p.rows_per_rank >= 2 * kBlockM) {
     // CTA-pair kernel: 256-row tiles on cluster pairs. Push CTAs (AG) are launched in pairs as well.
     const int ptiles_m = ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * W;
     if (f->mode == TDIST_GEMM_AG && W > 1) {
-      if (f->num_comm_ctas < 0) {
+      if (!comm_given) {
         // largest even push-CTA count that does not add a GEMM wave
         long best_waves = -1;
         comm = 12;
-        for (int c2 = 12; c2 <= 32; c2 += 4) {
+        for (int c2 = 8; c2 <= 32; c2 += 4) {
           const int prs = (sms - c2) / 2;
           const int bnc = pick_block_n2(ptiles_m, a->N, prs, a->block_n);
           const long tl = long(ptiles_m) * ((a->N + bnc - 1) / bnc);
@@ -421,7 +502,7 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
           }
         }
       }
-      comm = (comm + 1) / 2 * 2;
+      comm = round_push((comm + 1) / 2 * 2);
     }
     p.num_comm_ctas = comm;
     const int pairs = (sms - comm) / 2;
@@ -430,11 +511,13 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
       return -1;
     }
     const int bn2 = pick_block_n2(ptiles_m, a->N, pairs, a->block_n);
+    if (check_rs_flags(bn2) != 0) return -1;
     if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn2 / 2) != 0) return -1;
     const long ptiles = long(ptiles_m) * ((a->N + bn2 - 1) / bn2);
     const int use_pairs = (f->mode == TDIST_GEMM_RS) ? pairs : int(ptiles < pairs ? ptiles : pairs);
     return dispatch2(p, bn2, comm + 2 * use_pairs, static_cast<cudaStream_t>(stream));
   }
+  if (f->mode == TDIST_GEMM_AG) comm = round_push(comm);
   p.num_comm_ctas = comm;
   const int gemm_ctas_max = sms - comm;
   if (gemm_ctas_max < 1) {
@@ -442,9 +525,10 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     return -1;
   }
   const int bn = pick_block_n(tiles_m, a->N, gemm_ctas_max, a->block_n);
+  if (check_rs_flags(bn) != 0) return -1;
   if (make_tmap(&p.tma_b, a->b, a->N, a->K, a->ldb, bn) != 0) return -1;
   const int tiles = tiles_m * ((a->N + bn - 1) / bn);
-  // RS: the whole grid takes part in the reduction tail, so always launch every SM
+  // RS: the whole grid takes part in the reduction (tail or NVLS reducer warps), so always launch every SM
   const int gemm_ctas = (f->mode == TDIST_GEMM_RS) ? gemm_ctas_max : (tiles < gemm_ctas_max ? tiles : gemm_ctas_max);
   return dispatch(p, bn, comm + gemm_ctas, static_cast<cudaStream_t>(stream), true);
 }

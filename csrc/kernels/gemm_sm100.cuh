@@ -39,7 +39,20 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 x 16-bit = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 256;
-constexpr int kAgParts = 4;  // AG: each 128-row block is pushed as 4 independently flagged 32-row parts
+constexpr int kAgParts = 4;  // AG (unicast ring): each 128-row block is pushed as 4 independently flagged 32-row parts
+constexpr int kAgSlots = 32;  // AG: flag words reserved per (source rank, 128-row block)
+constexpr int kRsUnitRows = 16;  // RS (NVLS pull): rows of a tile one reducer warp sums per unit
+
+// Variants of the fused protocols (GemmParams::variant).
+//   AG 0: unicast ring — push CTAs copy the shard to each peer with bulk copies (works without multicast)
+//   AG 1: NVLS broadcast — push CTAs multimem.st the shard once, the switch replicates it; every rank pushes its
+//         128-row blocks in the same order, so block j of ALL shards arrives together and the GEMM walks remote
+//         tiles block-major
+//   RS 0: scatter — the epilogue stores each partial tile into the owner's slot, fp32 slot reduction as a tail
+//   RS 1: NVLS pull — the epilogue stores the partial tile LOCALLY and flags the owner; idle warps of the owner's
+//         GEMM CTAs multimem.ld_reduce finished tiles while later tiles are computed (no scatter traffic, no tail);
+//         every rank walks the owners round-robin so that all owners reduce all the time
+enum GemmVariant : int { VARIANT_LEGACY = 0, VARIANT_NVLS = 1 };
 
 struct GemmParams {
   CUtensorMap tma_a[2];     // AG: gathered workspace for parity 0/1; otherwise [0] only
@@ -65,6 +78,11 @@ struct GemmParams {
   int ar_one_shot;    // AR: every rank reduces every tile (small outputs)
   int use_mc;         // AR: NVLS available
   int transpose_out;  // PLAIN: C is written transposed (swap-AB skinny GEMMs)
+  int variant;             // GemmVariant
+  int ag_slices;           // AG 1: push CTAs cooperating on one 128-row block (= flags per block), power of two <= kAgSlots
+  long long a_lda;         // AG: row stride of a_local in elements
+  size_t ws_parity_bytes;  // distance between the two parity halves of the workspace: a constant of the CONTEXT, so that
+                           // calls of different sizes on one context never overlap the other parity's live data
   // grouped (MoE) GEMM: block_expert[m_blk] selects the expert whose [N, K] weight slab (rows
   // expert*N .. of B) multiplies the 128-row block; negative = padding block, skipped by all roles
   const int* block_expert;
@@ -99,7 +117,30 @@ __host__ __device__ __forceinline__ int blocks_per_shard(const GemmParams& p) { 
 
 __host__ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int t, int tiles_m, int tiles_n) {
   TileCoord tc;
-  if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
+  if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+    // owner-interleaved, the same walk on every rank: tile t belongs to owner t % W, so all owners receive finished
+    // tiles at the same steady rate and their reducers never idle
+    const int W = p.ctx.world;
+    const int bps = blocks_per_shard(p);
+    tc.shard = t % W;
+    const int i = t / W;
+    tc.blk = i % bps;
+    tc.n_blk = i / bps;
+    tc.row0 = tc.shard * p.rows_per_rank + tc.blk * kBlockM;
+    tc.row_end = (tc.shard + 1) * p.rows_per_rank;
+  } else if (p.mode == GEMM_AG && p.variant == VARIANT_NVLS && t >= blocks_per_shard(p) * tiles_n) {
+    // remote shards, block-major: (block 0 of rank+1, rank+2, ...), (block 1 of ...): the order in which the
+    // broadcast pushes of all ranks land
+    const int W = p.ctx.world;
+    const int bps = blocks_per_shard(p);
+    const int r = t - bps * tiles_n;
+    const int unit = r / tiles_n;
+    tc.n_blk = r - unit * tiles_n;
+    tc.blk = unit / (W - 1);
+    tc.shard = (p.ctx.rank + 1 + unit % (W - 1)) % W;
+    tc.row0 = tc.shard * p.rows_per_rank + tc.blk * kBlockM;
+    tc.row_end = (tc.shard + 1) * p.rows_per_rank;
+  } else if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
     // shard-major: AG consumes own shard first then rank+1, ...; RS produces the
     // segment of rank+1 first and its own last (same rotation as the reference,
     // allgather_gemm.py:224-229 / gemm_reduce_scatter.py:188,198).
@@ -158,7 +199,7 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
   const int bps = blocks_per_shard(p);
   const size_t row_bytes = size_t(p.K) * 2;
   const int parity = (epoch >> 1) & 1;
-  const size_t ws_parity_off = size_t(parity) * size_t(p.M) * row_bytes;
+  const size_t ws_parity_off = size_t(parity) * p.ws_parity_bytes;
   const char* src_base = static_cast<const char*>(p.a_local);
   uint32_t bar_phase = 0;  // bit s = parity of slot s
   // work items: (step t = 1..W-1, block j, part q), flattened in consumption order and dealt round-robin to
@@ -174,7 +215,7 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
     const int rows = min(kBlockM / kAgParts, blk_rows - r0);
     if (rows > 0) {
       const size_t part_bytes = size_t(rows) * row_bytes;
-      const char* src = src_base + (size_t(j) * kBlockM + r0) * row_bytes;
+      const char* src = src_base + (size_t(j) * kBlockM + r0) * row_bytes;  // (the ring needs a contiguous shard: lda == K)
       char* dst = symm_at(p.ctx, static_cast<char*>(p.a_ws), peer) + ws_parity_off +
                   (size_t(rank) * p.rows_per_rank + size_t(j) * kBlockM + r0) * row_bytes;
       const int n_chunks = int((part_bytes + kChunk - 1) / kChunk);
@@ -210,6 +251,121 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
   }
 }
 
+// AG producer, NVLS variant: the push CTAs broadcast this rank's shard with multimem.st — every 16 bytes leave the GPU
+// once and the switch delivers them to all ranks' workspaces. `ag_slices` CTAs share one 128-row block (each pushes
+// 128 / ag_slices rows and releases its own flag), consecutive groups of CTAs take consecutive blocks, so blocks
+// complete in row order at full rate. All threads of the CTA move data: 8 independent 16-byte loads per thread are in
+// flight before the first store is issued.
+__device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint32_t epoch, int comm_idx, int num_comm) {
+  const int rank = p.ctx.rank;
+  const int bps = blocks_per_shard(p);
+  const int slices = p.ag_slices;
+  const int rows_per_slice = kBlockM / slices;
+  const int row_vecs = p.K / 8;  // 16-byte vectors per row
+  const int parity = (epoch >> 1) & 1;
+  const char* src_base = static_cast<const char*>(p.a_local);
+  char* dst_base = mc_ptr(p.ctx, static_cast<char*>(p.a_ws)) + size_t(parity) * p.ws_parity_bytes +
+                   size_t(rank) * p.rows_per_rank * size_t(p.K) * 2;
+  const int items = bps * slices;
+  constexpr int kBatch = 8;
+  for (int item = comm_idx; item < items; item += num_comm) {
+    const int j = item / slices, sl = item - j * slices;
+    const int r0 = j * kBlockM + sl * rows_per_slice;
+    const int rows = max(0, min(rows_per_slice, p.rows_per_rank - r0));
+    const int n_vec = rows * row_vecs;
+    for (int i0 = threadIdx.x; i0 < n_vec; i0 += blockDim.x * kBatch) {
+      int4 v[kBatch];
+      size_t doff[kBatch];
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        const int i = i0 + b * blockDim.x;
+        if (i < n_vec) {
+          const int r = i / row_vecs, cv = i - r * row_vecs;
+          v[b] = ptx::ld_nc_v4(src_base + (size_t(r0 + r) * p.a_lda) * 2 + size_t(cv) * 16);
+          doff[b] = (size_t(r0 + r) * p.K) * 2 + size_t(cv) * 16;
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b)
+        if (i0 + b * blockDim.x < n_vec) ptx::multimem_st_v4(dst_base + doff[b], v[b]);
+    }
+    __syncthreads();
+    // flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots]; the first `slices` of a block are used
+    if (threadIdx.x == 0) {
+      ptx::fence_acq_rel_sys();
+      ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sl), epoch);
+    }
+  }
+}
+
+// RS consumer, NVLS variant: run by the two otherwise idle warps of every GEMM CTA. A unit is kRsUnitRows rows of one
+// (128-row block, n block) tile of MY segment; units are dealt round-robin to the reducer warps of the grid in the
+// order the tiles are produced (the same on every rank). The warp waits until all W ranks have flagged the tile, sums
+// the W partial copies in the switch with multimem.ld_reduce (fp32 accumulation) and writes the result to `out`.
+// Without a multicast mapping the same loop sums plain peer loads.
+template <typename Tag, int BLOCK_N>
+__device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch, int cw, int ncw, int tiles_n, bool pair_order) {
+  const int W = p.ctx.world;
+  const int lane = threadIdx.x & 31;
+  const int bps = blocks_per_shard(p);
+  const int bps2 = (p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM);
+  const int parity = (epoch >> 1) & 1;
+  constexpr int kSub = kBlockM / kRsUnitRows;
+  const int seg_tiles = (pair_order ? bps2 * 2 : bps) * tiles_n;  // 128-row tiles of my segment in production order
+  const int units = seg_tiles * kSub;
+  const char* part = static_cast<const char*>(p.c) + size_t(parity) * p.ws_parity_bytes;
+  const char* part_mc = mc_ptr(p.ctx, part);
+  char* out = static_cast<char*>(p.out);
+  const bool use_mc = p.ctx.mc_base != nullptr && p.use_mc;
+  constexpr int kBatch = 8;
+  for (int u = cw; u < units; u += ncw) {
+    const int ti = u / kSub, sc = u - ti * kSub;
+    int blk, n_blk;
+    if (pair_order) {
+      // pair tiles are produced as (pair block i % bps2, n block i / bps2); both 128-row halves at once
+      const int i = ti >> 1;
+      blk = (i % bps2) * 2 + (ti & 1);
+      n_blk = i / bps2;
+    } else {
+      blk = ti % bps;
+      n_blk = ti / bps;
+    }
+    const int r0 = blk * kBlockM + sc * kRsUnitRows;
+    if (blk >= bps || r0 >= p.rows_per_rank) continue;
+    // flags layout (RS, NVLS): [W src][bps][tiles_n], written by src when its partial tile is stored
+    if (lane < W) wait_ge_sys(p.flags + (size_t(lane) * bps + blk) * tiles_n + n_blk, epoch);
+    __syncwarp();
+    const int rows = min(kRsUnitRows, p.rows_per_rank - r0);
+    const int col0 = n_blk * BLOCK_N;
+    const int vpr = min(BLOCK_N, p.N - col0) / 8;  // 16-byte vectors per row of this tile
+    const int n_vec = rows * vpr;
+    for (int i0 = lane; i0 < n_vec; i0 += 32 * kBatch) {
+      int4 v[kBatch];
+      size_t ooff[kBatch];
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        const int i = i0 + b * 32;
+        if (i < n_vec) {
+          const int r = i / vpr, cv = i - r * vpr;
+          ooff[b] = (size_t(r0 + r) * p.N + col0) * 2 + size_t(cv) * 16;
+          const size_t poff = (size_t(p.ctx.rank) * p.rows_per_rank * size_t(p.N)) * 2 + ooff[b];
+          if (use_mc) {
+            v[b] = Pack<Tag>::mc_ld_reduce(part_mc + poff);
+          } else {
+            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+            for (int s2 = 0; s2 < W; ++s2) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, part, (p.ctx.rank + s2) % W) + poff));
+            v[b] = Pack<Tag>::cvt(acc);
+          }
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b)
+        if (i0 + b * 32 < n_vec) *reinterpret_cast<int4*>(out + ooff[b]) = v[b];
+    }
+  }
+}
+
 // RS tail: out[r, :] = sum_src scatter[parity][src][r, :] for my segment,
 // gated per 128-row block by the W arrival flags. Executed by every CTA of the
 // grid after its GEMM work, so the tail runs at full HBM bandwidth.
@@ -222,7 +378,7 @@ __device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epo
   const int bps = blocks_per_shard(p);
   const int parity = (epoch >> 1) & 1;
   const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
-  const int4* scat = reinterpret_cast<const int4*>(static_cast<const char*>(p.c) + size_t(parity) * W * seg_elems * 2);
+  const int4* scat = reinterpret_cast<const int4*>(static_cast<const char*>(p.c) + size_t(parity) * p.ws_parity_bytes);
   int4* out = static_cast<int4*>(p.out);
   const size_t seg_vecs = seg_elems / 8;
   const int row_vecs = p.N / 8;                 // 16-byte vectors per row
@@ -280,7 +436,7 @@ __device__ __forceinline__ void ar_consume_body(const GemmParams& p, uint32_t ep
   const int tiles = tiles_m * tiles_n;
   constexpr int vec_per_row = BLOCK_N / 8;
   const int parity = (epoch >> 1) & 1;
-  char* sym_c = static_cast<char*>(p.c) + size_t(parity) * size_t(p.M) * p.ldc * 2;
+  char* sym_c = static_cast<char*>(p.c) + size_t(parity) * p.ws_parity_bytes;
   char* out = static_cast<char*>(p.out);
   for (int t = comm_idx; t < tiles; t += num_comm) {
     if (!p.ar_one_shot && (t % W) != p.ctx.rank) continue;
@@ -368,7 +524,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
   if (gemm_cta < 0) {
     // ------------------------------------------------------------ comm CTA
     if (p.mode == GEMM_AG) {
-      ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+      if (p.variant == VARIANT_NVLS)
+        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+      else
+        ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
     } else if (p.mode == GEMM_AR) {
       if (p.is_bf16)
         ar_consume_body<BF16, BLOCK_N>(p, epoch, blockIdx.x, p.num_comm_ctas, tiles_m, tiles_n);
@@ -411,7 +570,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
 
     if (warp == 0) {
       // ======================================================== TMA producer
-      if (lane == 0) {
+      // The whole warp walks the tiles (so that its lanes can poll the arrival flags of a block in parallel); lane 0
+      // issues the copies.
+      {
         int stage = 0;
         uint32_t ph = 0;
         const int bps = blocks_per_shard(p);
@@ -431,22 +592,29 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               a_row = tc.blk * kBlockM;
             } else {
               ta = &p.tma_a[parity];
-              // wait until all parts of block (src, blk) have landed in my workspace
-#pragma unroll
-              for (int q = 0; q < kAgParts; ++q) wait_ge_sys(p.flags + (tc.shard * bps + tc.blk) * kAgParts + q, epoch);
+              // wait until every part of block (src, blk) has landed in my workspace
+              if (p.variant == VARIANT_NVLS) {
+                if (lane < p.ag_slices) wait_ge_sys(p.flags + (size_t(tc.shard) * bps + tc.blk) * kAgSlots + lane, epoch);
+              } else {
+                if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps + tc.blk) * kAgParts + lane, epoch);
+              }
+              __syncwarp();
               ptx::fence_proxy_async();
             }
           }
-          for (int kb = 0; kb < num_k; ++kb) {
-            ptx::mbar_wait(empty_bar + stage, ph ^ 1);
-            ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);
-            ptx::tma_load_2d(smem_a + stage * L::kABytes, ta, full_bar + stage, kb * kBlockK, a_row);
-            ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK, b_row);
-            if (++stage == STAGES) {
-              stage = 0;
-              ph ^= 1;
+          if (lane == 0) {
+            for (int kb = 0; kb < num_k; ++kb) {
+              ptx::mbar_wait(empty_bar + stage, ph ^ 1);
+              ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);
+              ptx::tma_load_2d(smem_a + stage * L::kABytes, ta, full_bar + stage, kb * kBlockK, a_row);
+              ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK, b_row);
+              if (++stage == STAGES) {
+                stage = 0;
+                ph ^= 1;
+              }
             }
           }
+          __syncwarp();
         }
       }
     } else if (warp == 1) {
@@ -495,10 +663,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       // RS/AR: a finished tile is published (system fence + counter/flag) one tile LATER, right before the next
       // tile's stores are issued: by then its NVLink stores have drained, so the fence costs nothing instead of
       // stalling the epilogue for a link round trip per tile.
-      int pend_t = -1, pend_shard = 0, pend_blk = 0;
-      auto publish = [&](int t_done, int shard, int blk) {
+      int pend_t = -1, pend_shard = 0, pend_blk = 0, pend_nblk = 0;
+      auto publish = [&](int t_done, int shard, int blk, int n_blk) {
         ptx::fence_acq_rel_sys();
-        if (p.mode == GEMM_RS) {
+        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+          // my partial tile is in my own memory: tell the owner it may be summed
+          const int bps = blocks_per_shard(p);
+          notify(p.ctx, p.flags + (size_t(p.ctx.rank) * bps + blk) * tiles_n + n_blk, shard, epoch);
+        } else if (p.mode == GEMM_RS) {
           const int bps = blocks_per_shard(p);
           const int cidx = shard * bps + blk;
           const uint32_t done = ptx::atom_add_acq_rel_gpu(p.counters + cidx, 1) + 1;
@@ -516,22 +688,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
         if (p.block_expert != nullptr && p.block_expert[tc.blk] < 0) continue;
         ptx::mbar_wait(tmem_full + acc, acc_ph);
         ptx::tcgen05_fence_after();
-        if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk);
+        if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk, pend_nblk);
         pend_t = -1;
         // destination of this tile
         char* dst_base = static_cast<char*>(p.c);
         long long ld = p.ldc;
         int row0 = tc.row0 + q * 32;  // first global row handled by this warp
         int row_limit = tc.row_end;
-        if (p.mode == GEMM_RS) {
+        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+          // partial tile stays local, in the [M, N] layout that is identical (and multicast-mapped) on every rank
+          dst_base += size_t(parity) * p.ws_parity_bytes;
+          ld = p.N;
+        } else if (p.mode == GEMM_RS) {
           const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
-          dst_base = symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) +
-                     (size_t(parity) * W + p.ctx.rank) * seg_elems * 2;
+          dst_base = symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) + size_t(parity) * p.ws_parity_bytes +
+                     size_t(p.ctx.rank) * seg_elems * 2;
           row0 -= tc.shard * p.rows_per_rank;
           row_limit = p.rows_per_rank;
           ld = p.N;
         } else if (p.mode == GEMM_AR) {
-          dst_base += size_t(parity) * size_t(p.M) * p.ldc * 2;
+          dst_base += size_t(parity) * p.ws_parity_bytes;
         }
         const int col0 = tc.n_blk * BLOCK_N;
 #pragma unroll 1
@@ -598,13 +774,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           pend_t = t;
           pend_shard = tc.shard;
           pend_blk = tc.blk;
+          pend_nblk = tc.n_blk;
         }
         if (++acc == 2) {
           acc = 0;
           acc_ph ^= 1;
         }
       }
-      if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk);
+      if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk, pend_nblk);
+    } else if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+      // ======================================================== warps 2-3: NVLS reducers of my own segment
+      const int cw = gemm_cta * 2 + (warp - 2);
+      if (p.is_bf16)
+        rs_pull_body<BF16, BLOCK_N>(p, epoch, cw, num_gemm * 2, tiles_n, false);
+      else
+        rs_pull_body<F16, BLOCK_N>(p, epoch, cw, num_gemm * 2, tiles_n, false);
     }
     // teardown of the GEMM roles
     ptx::tcgen05_fence_before();
@@ -613,7 +797,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
   }
 
   // ------------------------------------------------------------ fused tails (all CTAs)
-  if (p.mode == GEMM_RS) {
+  if (p.mode == GEMM_RS && p.variant == VARIANT_LEGACY) {
     __syncthreads();
     if (p.is_bf16)
       rs_reduce_body<BF16>(p, epoch);

@@ -39,7 +39,29 @@ struct PairCoord {
 __device__ __forceinline__ PairCoord pair_coord(const GemmParams& p, int t, int ptiles_m, int tiles_n) {
   PairCoord tc;
   const int gm = max(1, p.group_m / 2);
-  if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
+  if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+    // owner-interleaved walk, identical on every rank (see tile_coord)
+    const int W = p.ctx.world;
+    const int bps2 = (p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM);
+    tc.shard = t % W;
+    const int i = t / W;
+    tc.pblk = i % bps2;
+    tc.n_blk = i / bps2;
+    tc.row0 = tc.shard * p.rows_per_rank + tc.pblk * 2 * kBlockM;
+    tc.row_end = (tc.shard + 1) * p.rows_per_rank;
+  } else if (p.mode == GEMM_AG && p.variant == VARIANT_NVLS &&
+             t >= ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * tiles_n) {
+    // remote shards block-major (see tile_coord)
+    const int W = p.ctx.world;
+    const int bps2 = (p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM);
+    const int r = t - bps2 * tiles_n;
+    const int unit = r / tiles_n;
+    tc.n_blk = r - unit * tiles_n;
+    tc.pblk = unit / (W - 1);
+    tc.shard = (p.ctx.rank + 1 + unit % (W - 1)) % W;
+    tc.row0 = tc.shard * p.rows_per_rank + tc.pblk * 2 * kBlockM;
+    tc.row_end = (tc.shard + 1) * p.rows_per_rank;
+  } else if (p.mode == GEMM_AG || p.mode == GEMM_RS) {
     const int W = p.ctx.world;
     const int bps2 = (p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM);
     const int per_shard = bps2 * tiles_n;
@@ -97,7 +119,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
   const int parity = (epoch >> 1) & 1;
 
   if (gemm_cta < 0) {
-    if (p.mode == GEMM_AG) ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+    if (p.mode == GEMM_AG) {
+      if (p.variant == VARIANT_NVLS)
+        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+      else
+        ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+    }
   } else {
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + STAGES * L::kABytes;
@@ -133,7 +160,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
 
     if (warp == 0) {
       // ======================================================== TMA producer (both CTAs)
-      if (lane == 0) {
+      // whole warp walks the tiles (lanes poll the arrival flags of a block in parallel), lane 0 issues the copies
+      {
         int stage = 0;
         uint32_t ph = 0;
         for (int t = pair; t < tiles; t += num_pairs) {
@@ -148,27 +176,34 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
             } else {
               ta = &p.tma_a[parity];
               if (blk128 < bps128) {
-#pragma unroll
-                for (int q = 0; q < kAgParts; ++q) wait_ge_sys(p.flags + (tc.shard * bps128 + blk128) * kAgParts + q, epoch);
+                if (p.variant == VARIANT_NVLS) {
+                  if (lane < p.ag_slices) wait_ge_sys(p.flags + (size_t(tc.shard) * bps128 + blk128) * kAgSlots + lane, epoch);
+                } else {
+                  if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps128 + blk128) * kAgParts + lane, epoch);
+                }
+                __syncwarp();
                 ptx::fence_proxy_async();
               }
             }
           }
           const int b_row = tc.n_blk * BLOCK_N + int(cta_rank) * (BLOCK_N / 2);
-          for (int kb = 0; kb < num_k; ++kb) {
-            ptx::mbar_wait(empty_bar + stage, ph ^ 1);
-            const uint32_t leader_full = ptx::smem_u32(full_bar + stage) & kPeerBitMask;
-            if (leader)
-              ptx::mbar_arrive_expect_tx(full_bar + stage, 2 * L::kStageBytes);
-            else
-              ptx::mbar_arrive_cluster(full_bar + stage, 0);
-            ptx::tma_load_2d_cg2(smem_a + stage * L::kABytes, ta, leader_full, kb * kBlockK, a_row);
-            ptx::tma_load_2d_cg2(smem_b + stage * L::kBBytes, &p.tma_b, leader_full, kb * kBlockK, b_row);
-            if (++stage == STAGES) {
-              stage = 0;
-              ph ^= 1;
+          if (lane == 0) {
+            for (int kb = 0; kb < num_k; ++kb) {
+              ptx::mbar_wait(empty_bar + stage, ph ^ 1);
+              const uint32_t leader_full = ptx::smem_u32(full_bar + stage) & kPeerBitMask;
+              if (leader)
+                ptx::mbar_arrive_expect_tx(full_bar + stage, 2 * L::kStageBytes);
+              else
+                ptx::mbar_arrive_cluster(full_bar + stage, 0);
+              ptx::tma_load_2d_cg2(smem_a + stage * L::kABytes, ta, leader_full, kb * kBlockK, a_row);
+              ptx::tma_load_2d_cg2(smem_b + stage * L::kBBytes, &p.tma_b, leader_full, kb * kBlockK, b_row);
+              if (++stage == STAGES) {
+                stage = 0;
+                ph ^= 1;
+              }
             }
           }
+          __syncwarp();
         }
       }
     } else if (warp == 1) {
@@ -211,9 +246,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
       int acc = 0;
       uint32_t acc_ph = 0;
       const int W = p.ctx.world;
-      int pend_shard = 0, pend_blk = -1;
-      auto publish = [&](int shard, int blk) {
+      int pend_shard = 0, pend_blk = -1, pend_nblk = 0;
+      auto publish = [&](int shard, int blk, int n_blk) {
         ptx::fence_acq_rel_sys();
+        if (p.variant == VARIANT_NVLS) {
+          // my 128 rows of the partial tile are in my own memory: tell the owner they may be summed
+          notify(p.ctx, p.flags + (size_t(p.ctx.rank) * bps128 + blk) * tiles_n + n_blk, shard, epoch);
+          return;
+        }
         const int cidx = shard * bps128 + blk;
         const uint32_t done = ptx::atom_add_acq_rel_gpu(p.counters + cidx, 1) + 1;
         if (done == static_cast<uint32_t>(tiles_n)) {
@@ -226,15 +266,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
         const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
         ptx::mbar_wait(tmem_full + acc, acc_ph);
         ptx::tcgen05_fence_after();
-        if (pend_blk >= 0 && warp == 4 && lane == 0) publish(pend_shard, pend_blk);
+        if (pend_blk >= 0 && warp == 4 && lane == 0) publish(pend_shard, pend_blk, pend_nblk);
         pend_blk = -1;
         char* dst_base = static_cast<char*>(p.c);
         long long ld = p.ldc;
         int row0 = tc.row0 + int(cta_rank) * kBlockM + q * 32;
         int row_limit = tc.row_end;
-        if (p.mode == GEMM_RS) {
+        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+          dst_base += size_t(parity) * p.ws_parity_bytes;
+          ld = p.N;
+        } else if (p.mode == GEMM_RS) {
           const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
-          dst_base = symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) + (size_t(parity) * W + p.ctx.rank) * seg_elems * 2;
+          dst_base = symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) + size_t(parity) * p.ws_parity_bytes +
+                     size_t(p.ctx.rank) * seg_elems * 2;
           row0 -= tc.shard * p.rows_per_rank;
           row_limit = p.rows_per_rank;
           ld = p.N;
@@ -288,6 +332,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
           if (blk128 < bps128) {
             pend_shard = tc.shard;
             pend_blk = blk128;
+            pend_nblk = tc.n_blk;
           }
         }
         if (++acc == 2) {
@@ -295,7 +340,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
           acc_ph ^= 1;
         }
       }
-      if (pend_blk >= 0 && warp == 4 && lane == 0) publish(pend_shard, pend_blk);
+      if (pend_blk >= 0 && warp == 4 && lane == 0) publish(pend_shard, pend_blk, pend_nblk);
+    } else if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+      // ======================================================== warps 2-3: NVLS reducers of my own segment
+      const int cw = gemm_cta * 2 + (warp - 2);
+      const int ncw = (static_cast<int>(gridDim.x) - p.num_comm_ctas) * 2;
+      if (p.is_bf16)
+        rs_pull_body<BF16, BLOCK_N>(p, epoch, cw, ncw, tiles_n, true);
+      else
+        rs_pull_body<F16, BLOCK_N>(p, epoch, cw, ncw, tiles_n, true);
     }
     // teardown: the pair stays together until both CTAs are done with each other's shared memory / barriers
     ptx::tcgen05_fence_before();
@@ -303,7 +356,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
     if (warp == 2) ptx::tmem_dealloc_cg2<kTmemCols>(tmem_base);
   }
 
-  if (p.mode == GEMM_RS) {
+  if (p.mode == GEMM_RS && p.variant == VARIANT_LEGACY) {
     __syncthreads();
     if (p.is_bf16)
       rs_reduce_body<BF16>(p, epoch);

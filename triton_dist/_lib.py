@@ -75,6 +75,9 @@ class FusedArgs(ctypes.Structure):
         ("num_comm_ctas", ctypes.c_int),
         ("ar_one_shot", ctypes.c_int),
         ("use_mc", ctypes.c_int),
+        ("variant", ctypes.c_int),
+        ("ws_bytes", ctypes.c_size_t),
+        ("flags_words", ctypes.c_size_t),
     ]
 
 

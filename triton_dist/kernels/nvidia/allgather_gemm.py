@@ -4,13 +4,16 @@ API of the reference's ``kernels/nvidia/allgather_gemm.py`` (context :417-531,
 ``ag_gemm`` :534-653, ``gemm_persistent`` / ``gemm_non_persistent`` :656-720).
 
 B200 implementation: ONE launch of the tcgen05 GEMM engine
-(csrc/kernels/gemm_sm100.cuh, mode AG). A few CTAs push this rank's A shard to
-every peer's gather workspace with bulk async copies over NVLink, 128 rows at a
-time with a release flag per block; the remaining CTAs run the persistent
-TMA -> tcgen05 -> TMEM GEMM over the shards in arrival order (own shard first,
+(csrc/kernels/gemm_sm100.cuh, mode AG). A few CTAs push this rank's A shard
+into every rank's gather workspace — with NVLS ``multimem.st`` (each byte leaves
+the GPU once, the switch replicates it; all ranks push their 128-row blocks in
+the same order) or, without a multicast mapping, with bulk async copies to each
+peer — and release flags per block; the remaining CTAs run the persistent
+TMA -> tcgen05 -> TMEM GEMM over the blocks in arrival order (own shard first,
 read straight from the caller's tensor). No copy engine, no second stream, no
-host-side barrier: the workspace is double buffered by call parity and flags
-are monotone, so back-to-back calls and CUDA graphs are safe.
+host-side barrier: the workspace is double buffered by call parity (the two
+halves are a fixed distance apart, whatever the size of a call) and flags are
+monotone, so back-to-back calls of any sizes and CUDA graphs are safe.
 """
 from __future__ import annotations
 
@@ -82,6 +85,7 @@ class AllGatherGEMMTensorParallelContext:
     stages: int = 4
     num_comm_sms: int = -1  # CTAs that push the local shard to the peers (-1 = chosen so that no GEMM wave is added)
     cta_group: int = 0  # 0 auto, 1 single-CTA tiles, 2 CTA pairs
+    variant: int = 0  # 0 auto (NVLS broadcast push when the heap has a multicast mapping), 1 point-to-point, 2 NVLS
     all_gather_method: AllGatherMethod = AllGatherMethod.Auto
     for_correctness: bool = False
     ag_intranode_stream: Optional["torch.cuda.Stream"] = None
@@ -102,7 +106,9 @@ class AllGatherGEMMTensorParallelContext:
             # [2 parity][max_M][K] gather workspace + per-(src, 128-row block) arrival flags
             self.symm_workspace = heap.alloc((2, self.max_M, self.K), self.tensor_dtype, zero=False)
             self.symm_workspaces = heap.peer_views(self.symm_workspace)
-            self.state = CollectiveState(4 * (self.num_ranks * ((self.max_M // self.num_ranks + 127) // 128) + 16))
+            # 32 flag words per (source rank, 128-row block): one per push CTA sharing the block
+            self.flags_words = 32 * (self.num_ranks * ((self.max_M // self.num_ranks + 127) // 128) + 16)
+            self.state = CollectiveState(self.flags_words)
             self.max_gemm_sm = torch.cuda.get_device_properties("cuda").multi_processor_count
             heap.barrier_all()
             torch.cuda.synchronize()
@@ -165,7 +171,7 @@ def ag_gemm(a: torch.Tensor, b: torch.Tensor, ctx: AllGatherGEMMTensorParallelCo
     st = ctx.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=1, ws=ctx.symm_workspace.data_ptr(), out=None, flags=st.flags_ptr, flags2=None,
                        counters=None, phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=ctx.num_comm_sms, ar_one_shot=0,
-                       use_mc=0)
-    # the workspace parity stride is M*K, so it must hold 2*M*K elements: guaranteed by M <= max_M
+                       use_mc=0, variant=ctx.variant, ws_bytes=ctx.symm_workspace.numel() * ctx.symm_workspace.element_size(),
+                       flags_words=ctx.flags_words)
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "ag_gemm")
     return out

@@ -140,13 +140,14 @@ def _launch(ctx: GemmARContext, a: torch.Tensor, b: torch.Tensor, one_shot: bool
         out = torch.empty((M, N), dtype=a.dtype, device=a.device)
     else:
         out = ctx.symm_ar_out_buf[:M]
-    # tiles are laid out with row stride N in the symmetric buffer
-    sym_c = ctx.symm_gemm_out_buf.view(-1)[:2 * M * N].view(2, M, N)
+    # tiles are laid out with row stride N in the symmetric buffer; its two parity halves are max_M * N apart
+    sym_c = ctx.symm_gemm_out_buf
     args = _gemm_args(a, b, sym_c[0], M, N, K, block_n=block_n, group_m=8)
     st = ctx.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=3, ws=sym_c.data_ptr(), out=out.data_ptr(), flags=st.flags_ptr,
                        flags2=ctx.flags2.data_ptr(), counters=None, phase=st.phase_ptr, done=st.done_ptr,
-                       num_comm_ctas=ctx.NUM_COMM_SMS, ar_one_shot=int(one_shot), use_mc=int(ctx.use_mc))
+                       num_comm_ctas=ctx.NUM_COMM_SMS, ar_one_shot=int(one_shot), use_mc=int(ctx.use_mc), variant=0,
+                       ws_bytes=sym_c.numel() * sym_c.element_size(), flags_words=0)
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "gemm_ar")
     if not one_shot and copy_to_local:
         return out.clone()

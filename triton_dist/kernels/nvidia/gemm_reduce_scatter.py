@@ -3,14 +3,23 @@
 API of the reference's ``kernels/nvidia/gemm_reduce_scatter.py`` (context
 :40-82, ``gemm_rs`` :508-583).
 
-B200 implementation: ONE launch of the tcgen05 GEMM engine in mode RS. Tiles
-are produced owner-by-owner starting at ``rank+1``; the epilogue stores each
-partial tile (TMEM -> bf16 -> 128-byte rows) straight into slot ``rank`` of the
-owner's scatter buffer over NVLink, the last tile of a 128-row block releases a
-flag on the owner, and after its tiles every CTA joins the flag-gated fp32
-reduction of this rank's own segment. ``fuse_scatter`` is therefore always on;
-the flag is accepted for API compatibility. Scatter buffers are double buffered
-by call parity, so no inter-call barrier is needed.
+B200 implementation: ONE launch of the tcgen05 GEMM engine in mode RS.
+
+* NVLS (default when the heap has a multicast mapping): every rank walks the
+  output tiles in the same owner-interleaved order; the epilogue stores each
+  partial tile (TMEM -> bf16 -> 128-byte rows) into a LOCAL symmetric buffer
+  and flags the owner; the two idle warps of every GEMM CTA on the owner sum
+  finished tiles across ranks in the switch (``multimem.ld_reduce``, fp32
+  accumulation) while later tiles are still being computed. Nothing is
+  scattered, no SM is reserved, there is no reduction tail.
+* point-to-point: tiles are produced owner-by-owner starting at ``rank+1``; the
+  epilogue stores each partial tile into slot ``rank`` of the owner's scatter
+  buffer over NVLink, and after its tiles every CTA joins the flag-gated fp32
+  reduction of this rank's own segment.
+
+``fuse_scatter`` is always on; the flag is accepted for API compatibility.
+Buffers are double buffered by call parity (fixed distance between the halves),
+so no inter-call barrier is needed.
 """
 from __future__ import annotations
 
@@ -39,6 +48,8 @@ class GEMMReduceScatterTensorParallelContext:
     GROUP_M: int = 8
     stages: int = 4
     counters: Optional[torch.Tensor] = None
+    variant: int = 0  # 0 auto, 1 point-to-point scatter, 2 NVLS pull-reduce
+    cta_group: int = 0
 
     def __post_init__(self):
         if self.rs_ctx.native:
@@ -81,11 +92,12 @@ def gemm_rs_op(input: torch.Tensor, weight: torch.Tensor, ctx: GEMMReduceScatter
     if output is None:
         output = torch.empty((M // W, N), dtype=ctx.output_dtype, device=input.device)
     heap = _symm.get_heap()
-    args = _gemm_args(input, weight, output, M, N, local_K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_M)
+    args = _gemm_args(input, weight, output, M, N, local_K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_M, cta_group=ctx.cta_group)
     st = rs.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=2, ws=rs.scatter_buf.data_ptr(), out=output.data_ptr(), flags=st.flags_ptr,
                        flags2=None, counters=ctx.counters.data_ptr(), phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=0,
-                       ar_one_shot=0, use_mc=0)
+                       ar_one_shot=0, use_mc=0, variant=ctx.variant,
+                       ws_bytes=rs.scatter_buf.numel() * rs.scatter_buf.element_size(), flags_words=st.flags.numel())
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "gemm_rs")
     return output
 

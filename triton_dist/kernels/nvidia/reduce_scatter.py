@@ -53,7 +53,10 @@ class ReduceScatter2DContext:
             # [2 parity][W slots][max_M / W][N]
             self.scatter_buf = heap.alloc((2, self.world_size, self.max_M // self.world_size, self.N), self.dtype, zero=False)
             self.scatter_bufs = heap.peer_views(self.scatter_buf)
-            self.state = CollectiveState()
+            # fused GEMM+RS, NVLS protocol: one flag per (source rank, 128-row block, n tile >= 32 wide); the stand-alone
+            # reduce-scatter needs a W-wide row per CTA
+            blocks = self.world_size * ((self.max_M // self.world_size + 127) // 128)
+            self.state = CollectiveState(max(_lib.MAX_CTAS * _lib.MAX_RANKS, blocks * ((self.N + 31) // 32) + 64))
             self.barrier = BarrierAllContext(True)
             self.reduction_stream = torch.cuda.Stream(priority=-1)
 

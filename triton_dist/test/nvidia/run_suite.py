@@ -14,9 +14,10 @@ M = "triton_dist.mega_triton_kernel.test.models."
 
 def cases(suite: str, world: int):
     core = [
-        (T + "test_ag_gemm", [2048 * world, 512 * world, 1024, "--check", "--stress"]),
+        (T + "test_ag_gemm", [2048 * world, 512 * world, 1024, "--check", "--stress", "--alternate"]),
         (T + "test_ag_gemm", [200 * world, 136 * world, 520, "--check", "--verify-iters", 2]),
-        (T + "test_gemm_rs", [2048 * world, 1024, 512 * world, "--check", "--stress"]),
+        (T + "test_gemm_rs", [2048 * world, 1024, 512 * world, "--check", "--stress", "--alternate"]),
+        (T + "test_gemm_rs", [200 * world, 136, 72 * world, "--check", "--verify-iters", 2]),
         (T + "test_gemm_ar", [64, 1024, 512 * world, "--check", "--low-latency", "--stress"]),
         (T + "test_gemm_ar", [2048, 1024, 256 * world, "--check", "--verify-iters", 2]),
         (T + "test_allreduce", ["--check", "--max-bytes", 4 * 2**20, "--verify-iters", 2, "--stress"]),

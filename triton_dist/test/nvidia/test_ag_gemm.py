@@ -15,6 +15,7 @@ if __name__ == "__main__":
     p.add_argument("K", type=int)
     p.add_argument("--block-n", type=int, default=0)
     p.add_argument("--comm-sms", type=int, default=-1)
+    p.add_argument("--alternate", action="store_true", help="two sizes back to back on one context, rank skew, no host sync")
     args = p.parse_args()
     group, rank, world = setup()
     dtype = DTYPES[args.dtype]
@@ -33,6 +34,21 @@ if __name__ == "__main__":
         ok = all_ok(check_close(C, ref, dtype, f"ag_gemm iter {it}"))
         if not ok:
             break
+    if ok and args.alternate and m_loc % 2 == 0:
+        # sizes alternate between calls: the other parity half of the workspace must still be intact when a fast rank
+        # is already one call ahead (the halves are a fixed distance apart, not a size-dependent one)
+        ins, outs = [], []
+        for it in range(8):
+            rows = m_loc if it % 2 == 0 else m_loc // 2
+            ins.append(rand((rows, args.K), dtype))
+        torch.cuda.synchronize()
+        dist.barrier()
+        for it, a_in in enumerate(ins):
+            if it % 3 == rank % 3:
+                skew(True)
+            outs.append(ag_gemm(a_in, B, ctx))
+        for it, (a_in, c_out) in enumerate(zip(ins, outs)):
+            ok = all_ok(check_close(c_out, torch_ag_gemm(a_in.float(), B.float()), dtype, f"ag_gemm alternate {it}")) and ok
     if ok and not args.check:
         A = rand((m_loc, args.K), dtype)
         t_fused = bench(lambda: ag_gemm(A, B, ctx), args)

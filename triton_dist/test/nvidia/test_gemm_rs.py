@@ -14,6 +14,7 @@ if __name__ == "__main__":
     p.add_argument("N", type=int)
     p.add_argument("K", type=int)
     p.add_argument("--block-n", type=int, default=0)
+    p.add_argument("--alternate", action="store_true", help="two sizes back to back on one context, rank skew, no host sync")
     args = p.parse_args()
     group, rank, world = setup()
     dtype = DTYPES[args.dtype]
@@ -30,6 +31,18 @@ if __name__ == "__main__":
         ok = all_ok(check_close(C, ref, dtype, f"gemm_rs iter {it}"))
         if not ok:
             break
+    if ok and args.alternate and (args.M // 2) % world == 0:
+        ins, outs = [], []
+        for it in range(8):
+            ins.append(rand((args.M if it % 2 == 0 else args.M // 2, k_loc), dtype))
+        torch.cuda.synchronize()
+        dist.barrier()
+        for it, a_in in enumerate(ins):
+            if it % 3 == rank % 3:
+                skew(True)
+            outs.append(gemm_rs(a_in, B, ctx))
+        for it, (a_in, c_out) in enumerate(zip(ins, outs)):
+            ok = all_ok(check_close(c_out, torch_gemm_rs(a_in.float(), B.float()), dtype, f"gemm_rs alternate {it}")) and ok
     if ok and not args.check:
         A = rand((args.M, k_loc), dtype)
         t_fused = bench(lambda: gemm_rs(A, B, ctx), args)

@@ -385,15 +385,28 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     }
     const int bps_ag = (p.rows_per_rank + kBlockM - 1) / kBlockM;
     if (p.variant == VARIANT_NVLS) {
-      // `slices` CTAs share a 128-row block; the other push CTAs work ahead on the following blocks
+      // `slices` push CTAs split the rows of a 128-row block, which is pushed (and flagged, and consumed) in `slabs`
+      // K slabs. Measured at 8 ranks (profiles/README.md): ONE group of push CTAs, so that blocks complete strictly in
+      // order; 4 CTAs already saturate the NVLS ingress, 8 leave headroom.
       int slices = env_int("TDIST_AG_SLICES", 8);
       if (slices < 1) slices = 1;
-      if (slices > kAgSlots) slices = kAgSlots;
+      if (slices > 32) slices = 32;  // one polling lane per slice
       while (slices & (slices - 1)) slices &= slices - 1;  // power of two (divides 128)
+      int slabs = env_int("TDIST_AG_KSLABS", 1);
+      const int num_kb = (a->K + kBlockK - 1) / kBlockK;
+      if (slabs > kAgSlots / slices) slabs = kAgSlots / slices;
+      if (slabs > num_kb) slabs = num_kb;
+      if (slabs < 1) slabs = 1;
       p.ag_slices = slices;
+      p.ag_slab_kblocks = (num_kb + slabs - 1) / slabs;
+      p.ag_kslabs = (num_kb + p.ag_slab_kblocks - 1) / p.ag_slab_kblocks;
       if (f->flags_words > 0 && f->flags_words < size_t(W) * bps_ag * kAgSlots) {
-        set_error("ag_gemm: flag area too small for the NVLS protocol (need W * ceil(M/W/128) * 32 words)");
+        set_error("ag_gemm: flag area too small for the NVLS protocol (need W * ceil(M/W/128) * 128 words)");
         return -1;
+      }
+      if (comm < 0) {
+        comm = slices;
+        comm_given = true;
       }
     } else if (a->lda != a->K) {
       set_error("ag_gemm: the point-to-point push needs a contiguous shard (lda == K)");
@@ -434,6 +447,8 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.variant = v == 2 ? VARIANT_NVLS : VARIANT_LEGACY;  // without multicast the pull variant sums plain peer loads
     if (v < 0) p.variant = VARIANT_LEGACY;
     p.use_mc = c.mc_base != nullptr;
+    p.rs_unit_rows = env_int("TDIST_RS_UNIT_ROWS", 8);
+    if (p.rs_unit_rows != 8 && p.rs_unit_rows != 16 && p.rs_unit_rows != 32) p.rs_unit_rows = 8;
     // both layouts ([W][M/W][N] scatter slots, [M][N] partial buffer) need M * N elements per parity
     const size_t par_need = size_t(a->M) * a->N * 2;
     p.ws_parity_bytes = f->ws_bytes > 0 ? f->ws_bytes / 2 : par_need;

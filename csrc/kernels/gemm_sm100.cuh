@@ -40,8 +40,7 @@ constexpr int kBlockK = 64;  // 64 x 16-bit = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 256;
 constexpr int kAgParts = 4;  // AG (unicast ring): each 128-row block is pushed as 4 independently flagged 32-row parts
-constexpr int kAgSlots = 32;  // AG: flag words reserved per (source rank, 128-row block)
-constexpr int kRsUnitRows = 16;  // RS (NVLS pull): rows of a tile one reducer warp sums per unit
+constexpr int kAgSlots = 128;  // AG: flag words reserved per (source rank, 128-row block): K slabs x row slices
 
 // Variants of the fused protocols (GemmParams::variant).
 //   AG 0: unicast ring — push CTAs copy the shard to each peer with bulk copies (works without multicast)
@@ -79,7 +78,10 @@ struct GemmParams {
   int use_mc;         // AR: NVLS available
   int transpose_out;  // PLAIN: C is written transposed (swap-AB skinny GEMMs)
   int variant;             // GemmVariant
-  int ag_slices;           // AG 1: push CTAs cooperating on one 128-row block (= flags per block), power of two <= kAgSlots
+  int ag_slices;           // AG 1: push CTAs cooperating on one 128-row block (row slices), power of two <= 32
+  int ag_kslabs;           // AG 1: a block is pushed, flagged and consumed in this many K slabs; ag_slices * ag_kslabs <= kAgSlots
+  int ag_slab_kblocks;     // AG 1: 64-wide k blocks per slab
+  int rs_unit_rows;        // RS 1: rows of a tile one reducer warp sums per unit (8, 16 or 32)
   long long a_lda;         // AG: row stride of a_local in elements
   size_t ws_parity_bytes;  // distance between the two parity halves of the workspace: a constant of the CONTEXT, so that
                            // calls of different sizes on one context never overlap the other parity's live data
@@ -252,53 +254,119 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
 }
 
 // AG producer, NVLS variant: the push CTAs broadcast this rank's shard with multimem.st — every 16 bytes leave the GPU
-// once and the switch delivers them to all ranks' workspaces. `ag_slices` CTAs share one 128-row block (each pushes
-// 128 / ag_slices rows and releases its own flag), consecutive groups of CTAs take consecutive blocks, so blocks
-// complete in row order at full rate. All threads of the CTA move data: 8 independent 16-byte loads per thread are in
-// flight before the first store is issued.
-__device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint32_t epoch, int comm_idx, int num_comm) {
+// once and the switch delivers them to all ranks' workspaces. An item is (128-row block j, K slab s, row slice sl):
+// `ag_slices` CTAs split the rows of a block, and a block is sent slab by slab, so that the consumers' K loops can
+// follow the arrival. Items are dealt round-robin to the push CTAs in (block, slab, slice) order.
+// Warps 0..6 move data and never wait for the link: they run ONE software-pipelined stream over all items of the CTA
+// (the loads of the next chunk, possibly of the next item, are issued before the stores of the current one) and after
+// the last store of an item arrive on a shared-memory barrier. Warp 7 publishes: it waits for an item's arrivals,
+// makes the stores visible system-wide (a full round trip through the switch) and releases the item's flag on every
+// rank. kDepth items are in flight between the two roles, which hides the fence latency behind the data stream.
+__device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint8_t* smem, uint32_t epoch, int comm_idx, int num_comm) {
+  constexpr int kDepth = 4;
+  constexpr int kDataThreads = kGemmThreads - 32;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kDepth;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kDepth; ++i) {
+      ptx::mbar_init(full + i, kDataThreads);
+      ptx::mbar_init(empty + i, 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
   const int rank = p.ctx.rank;
   const int bps = blocks_per_shard(p);
-  const int slices = p.ag_slices;
+  const int slices = p.ag_slices, slabs = p.ag_kslabs;
   const int rows_per_slice = kBlockM / slices;
-  const int row_vecs = p.K / 8;  // 16-byte vectors per row
+  const int slab_cols = p.ag_slab_kblocks * kBlockK;
   const int parity = (epoch >> 1) & 1;
+  const int items = bps * slabs * slices;
+  if (threadIdx.x >= kDataThreads) {
+    // ---- publisher. flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots], slot = slab * slices + slice
+    if (threadIdx.x == kDataThreads) {
+      int n = 0;
+      for (int item = comm_idx; item < items; item += num_comm, ++n) {
+        const int sl = item % slices;
+        const int js = item / slices;
+        const int j = js / slabs, sb = js - j * slabs;
+        ptx::mbar_wait(full + n % kDepth, (n / kDepth) & 1);
+        ptx::fence_acq_rel_sys();
+        ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sb * slices + sl), epoch);
+        ptx::mbar_arrive(empty + n % kDepth);
+      }
+    }
+    return;
+  }
   const char* src_base = static_cast<const char*>(p.a_local);
   char* dst_base = mc_ptr(p.ctx, static_cast<char*>(p.a_ws)) + size_t(parity) * p.ws_parity_bytes +
                    size_t(rank) * p.rows_per_rank * size_t(p.K) * 2;
-  const int items = bps * slices;
-  constexpr int kBatch = 8;
-  for (int item = comm_idx; item < items; item += num_comm) {
-    const int j = item / slices, sl = item - j * slices;
-    const int r0 = j * kBlockM + sl * rows_per_slice;
-    const int rows = max(0, min(rows_per_slice, p.rows_per_rank - r0));
-    const int n_vec = rows * row_vecs;
-    for (int i0 = threadIdx.x; i0 < n_vec; i0 += blockDim.x * kBatch) {
-      int4 v[kBatch];
-      size_t doff[kBatch];
+  constexpr int kBatch = 8;  // 16-byte vectors per thread and chunk
+  struct Chunk {
+    int n, item, k, iters;  // item ordinal of this CTA, global item, iteration inside the item, iterations of the item
+    int r0, col0, seg_vecs, n_vec;
+  };
+  auto geom = [&](Chunk& c) {
+    const int sl = c.item % slices;
+    const int js = c.item / slices;
+    const int j = js / slabs, sb = js - j * slabs;
+    c.r0 = j * kBlockM + sl * rows_per_slice;
+    const int rows = max(0, min(rows_per_slice, p.rows_per_rank - c.r0));
+    c.col0 = sb * slab_cols;
+    c.seg_vecs = max(0, min(slab_cols, p.K - c.col0)) / 8;  // 16-byte vectors per row of this slab
+    c.n_vec = rows * c.seg_vecs;
+    c.iters = max(1, (c.n_vec + kDataThreads * kBatch - 1) / (kDataThreads * kBatch));
+  };
+  auto advance = [&](Chunk& c) -> bool {
+    if (++c.k < c.iters) return true;
+    c.k = 0;
+    ++c.n;
+    c.item += num_comm;
+    if (c.item >= items) return false;
+    geom(c);
+    return true;
+  };
+  auto load = [&](const Chunk& c, int4 (&v)[kBatch], size_t (&doff)[kBatch]) {
+    if (c.k == 0 && c.n >= kDepth) ptx::mbar_wait(empty + c.n % kDepth, ((c.n / kDepth) - 1) & 1);  // barrier reusable
+    const int i0 = c.k * kDataThreads * kBatch + threadIdx.x;
 #pragma unroll
-      for (int b = 0; b < kBatch; ++b) {
-        const int i = i0 + b * blockDim.x;
-        if (i < n_vec) {
-          const int r = i / row_vecs, cv = i - r * row_vecs;
-          v[b] = ptx::ld_nc_v4(src_base + (size_t(r0 + r) * p.a_lda) * 2 + size_t(cv) * 16);
-          doff[b] = (size_t(r0 + r) * p.K) * 2 + size_t(cv) * 16;
-        }
+    for (int b = 0; b < kBatch; ++b) {
+      const int i = i0 + b * kDataThreads;
+      if (i < c.n_vec) {
+        const int r = i / c.seg_vecs, cv = i - r * c.seg_vecs;
+        v[b] = ptx::ld_nc_v4(src_base + (size_t(c.r0 + r) * p.a_lda + c.col0) * 2 + size_t(cv) * 16);
+        doff[b] = (size_t(c.r0 + r) * p.K + c.col0) * 2 + size_t(cv) * 16;
       }
+    }
+  };
+  Chunk c{0, comm_idx, 0, 1, 0, 0, 0, 0};
+  if (c.item >= items) return;
+  geom(c);
+  int4 va[kBatch];
+  size_t da[kBatch];
+  load(c, va, da);
+  for (bool have = true; have;) {
+    Chunk nx = c;
+    const bool have_nx = advance(nx);
+    int4 vb[kBatch];
+    size_t db[kBatch];
+    if (have_nx) load(nx, vb, db);
+    const int i0 = c.k * kDataThreads * kBatch + threadIdx.x;
 #pragma unroll
-      for (int b = 0; b < kBatch; ++b)
-        if (i0 + b * blockDim.x < n_vec) ptx::multimem_st_v4(dst_base + doff[b], v[b]);
+    for (int b = 0; b < kBatch; ++b)
+      if (i0 + b * kDataThreads < c.n_vec) ptx::multimem_st_v4(dst_base + da[b], va[b]);
+    if (c.k == c.iters - 1) ptx::mbar_arrive(full + c.n % kDepth);
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b) {
+      va[b] = vb[b];
+      da[b] = db[b];
     }
-    __syncthreads();
-    // flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots]; the first `slices` of a block are used
-    if (threadIdx.x == 0) {
-      ptx::fence_acq_rel_sys();
-      ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sl), epoch);
-    }
+    c = nx;
+    have = have_nx;
   }
 }
 
-// RS consumer, NVLS variant: run by the two otherwise idle warps of every GEMM CTA. A unit is kRsUnitRows rows of one
+// RS consumer, NVLS variant: run by the two otherwise idle warps of every GEMM CTA. A unit is rs_unit_rows rows of one
 // (128-row block, n block) tile of MY segment; units are dealt round-robin to the reducer warps of the grid in the
 // order the tiles are produced (the same on every rank). The warp waits until all W ranks have flagged the tile, sums
 // the W partial copies in the switch with multimem.ld_reduce (fp32 accumulation) and writes the result to `out`.
@@ -310,7 +378,8 @@ __device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch
   const int bps = blocks_per_shard(p);
   const int bps2 = (p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM);
   const int parity = (epoch >> 1) & 1;
-  constexpr int kSub = kBlockM / kRsUnitRows;
+  const int unit_rows = p.rs_unit_rows;
+  const int kSub = kBlockM / unit_rows;
   const int seg_tiles = (pair_order ? bps2 * 2 : bps) * tiles_n;  // 128-row tiles of my segment in production order
   const int units = seg_tiles * kSub;
   const char* part = static_cast<const char*>(p.c) + size_t(parity) * p.ws_parity_bytes;
@@ -330,12 +399,12 @@ __device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch
       blk = ti % bps;
       n_blk = ti / bps;
     }
-    const int r0 = blk * kBlockM + sc * kRsUnitRows;
+    const int r0 = blk * kBlockM + sc * unit_rows;
     if (blk >= bps || r0 >= p.rows_per_rank) continue;
     // flags layout (RS, NVLS): [W src][bps][tiles_n], written by src when its partial tile is stored
     if (lane < W) wait_ge_sys(p.flags + (size_t(lane) * bps + blk) * tiles_n + n_blk, epoch);
     __syncwarp();
-    const int rows = min(kRsUnitRows, p.rows_per_rank - r0);
+    const int rows = min(unit_rows, p.rows_per_rank - r0);
     const int col0 = n_blk * BLOCK_N;
     const int vpr = min(BLOCK_N, p.N - col0) / 8;  // 16-byte vectors per row of this tile
     const int n_vec = rows * vpr;
@@ -525,7 +594,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
     // ------------------------------------------------------------ comm CTA
     if (p.mode == GEMM_AG) {
       if (p.variant == VARIANT_NVLS)
-        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+        ag_push_mc_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
       else
         ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
     } else if (p.mode == GEMM_AR) {
@@ -586,32 +655,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           }
           const CUtensorMap* ta = &p.tma_a[0];
           int a_row = tc.row0;
+          const uint32_t* slab_flags = nullptr;
           if (p.mode == GEMM_AG) {
             if (tc.shard == p.ctx.rank) {
               ta = &p.tma_a_local;
               a_row = tc.blk * kBlockM;
             } else {
               ta = &p.tma_a[parity];
-              // wait until every part of block (src, blk) has landed in my workspace
-              if (p.variant == VARIANT_NVLS) {
-                if (lane < p.ag_slices) wait_ge_sys(p.flags + (size_t(tc.shard) * bps + tc.blk) * kAgSlots + lane, epoch);
-              } else {
+              if (p.variant != VARIANT_NVLS) {
+                // wait until every part of block (src, blk) has landed in my workspace
                 if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps + tc.blk) * kAgParts + lane, epoch);
+                __syncwarp();
+                ptx::fence_proxy_async();
+              } else {
+                slab_flags = p.flags + (size_t(tc.shard) * bps + tc.blk) * kAgSlots;
               }
+            }
+          }
+          for (int kb = 0; kb < num_k; ++kb) {
+            if (slab_flags != nullptr && kb % p.ag_slab_kblocks == 0) {
+              // NVLS push: the K loop follows the arrival of the block's K slabs (lanes poll the row slices of a slab)
+              if (lane < p.ag_slices) wait_ge_sys(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
               __syncwarp();
               ptx::fence_proxy_async();
             }
-          }
-          if (lane == 0) {
-            for (int kb = 0; kb < num_k; ++kb) {
+            if (lane == 0) {
               ptx::mbar_wait(empty_bar + stage, ph ^ 1);
               ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);
               ptx::tma_load_2d(smem_a + stage * L::kABytes, ta, full_bar + stage, kb * kBlockK, a_row);
               ptx::tma_load_2d(smem_b + stage * L::kBBytes, &p.tma_b, full_bar + stage, kb * kBlockK, b_row);
-              if (++stage == STAGES) {
-                stage = 0;
-                ph ^= 1;
-              }
+            }
+            if (++stage == STAGES) {
+              stage = 0;
+              ph ^= 1;
             }
           }
           __syncwarp();
@@ -768,7 +844,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             }
           }
         }
-        if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
+        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+          // the partial tile went to local memory: nothing to drain, flag the owner right away
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (warp == 4 && lane == 0) publish(t, tc.shard, tc.blk, tc.n_blk);
+        } else if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
           // all 4 epilogue warps have issued their stores; remember the tile, publish it one tile later
           asm volatile("bar.sync 1, 128;" ::: "memory");
           pend_t = t;

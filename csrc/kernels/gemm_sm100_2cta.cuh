@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
   if (gemm_cta < 0) {
     if (p.mode == GEMM_AG) {
       if (p.variant == VARIANT_NVLS)
-        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+        ag_push_mc_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
       else
         ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
     }
@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
           const CUtensorMap* ta = &p.tma_a[0];
           int a_row = tc.row0 + int(cta_rank) * kBlockM;  // my 128 rows of the 256-row tile
           const int blk128 = tc.pblk * 2 + int(cta_rank);
+          const uint32_t* slab_flags = nullptr;
           if (p.mode == GEMM_AG) {
             if (tc.shard == p.ctx.rank) {
               ta = &p.tma_a_local;
@@ -176,19 +177,25 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
             } else {
               ta = &p.tma_a[parity];
               if (blk128 < bps128) {
-                if (p.variant == VARIANT_NVLS) {
-                  if (lane < p.ag_slices) wait_ge_sys(p.flags + (size_t(tc.shard) * bps128 + blk128) * kAgSlots + lane, epoch);
-                } else {
+                if (p.variant != VARIANT_NVLS) {
                   if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps128 + blk128) * kAgParts + lane, epoch);
+                  __syncwarp();
+                  ptx::fence_proxy_async();
+                } else {
+                  slab_flags = p.flags + (size_t(tc.shard) * bps128 + blk128) * kAgSlots;
                 }
-                __syncwarp();
-                ptx::fence_proxy_async();
               }
             }
           }
           const int b_row = tc.n_blk * BLOCK_N + int(cta_rank) * (BLOCK_N / 2);
-          if (lane == 0) {
-            for (int kb = 0; kb < num_k; ++kb) {
+          for (int kb = 0; kb < num_k; ++kb) {
+            if (slab_flags != nullptr && kb % p.ag_slab_kblocks == 0) {
+              // NVLS push: the K loop follows the arrival of my 128 rows' K slabs
+              if (lane < p.ag_slices) wait_ge_sys(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
+              __syncwarp();
+              ptx::fence_proxy_async();
+            }
+            if (lane == 0) {
               ptx::mbar_wait(empty_bar + stage, ph ^ 1);
               const uint32_t leader_full = ptx::smem_u32(full_bar + stage) & kPeerBitMask;
               if (leader)
@@ -197,10 +204,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
                 ptx::mbar_arrive_cluster(full_bar + stage, 0);
               ptx::tma_load_2d_cg2(smem_a + stage * L::kABytes, ta, leader_full, kb * kBlockK, a_row);
               ptx::tma_load_2d_cg2(smem_b + stage * L::kBBytes, &p.tma_b, leader_full, kb * kBlockK, b_row);
-              if (++stage == STAGES) {
-                stage = 0;
-                ph ^= 1;
-              }
+            }
+            if (++stage == STAGES) {
+              stage = 0;
+              ph ^= 1;
             }
           }
           __syncwarp();
@@ -326,7 +333,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
             if (grow < row_limit && gcol < p.N && c + cj * 8 < BLOCK_N) ptx::st_v4(dst_base + (size_t(grow) * ld + gcol) * 2, w);
           }
         }
-        if (p.mode == GEMM_RS) {
+        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+          // the partial tile went to local memory: nothing to drain, flag the owner right away
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          const int blk128 = tc.pblk * 2 + int(cta_rank);
+          if (blk128 < bps128 && warp == 4 && lane == 0) publish(tc.shard, blk128, tc.n_blk);
+        } else if (p.mode == GEMM_RS) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
           const int blk128 = tc.pblk * 2 + int(cta_rank);
           if (blk128 < bps128) {

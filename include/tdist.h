@@ -129,7 +129,7 @@ typedef struct tdist_fused_args {
   int variant;        /* protocol: 0 = auto (NVLS when the heap has a multicast mapping), 1 = point-to-point (AG: unicast
                          push ring, RS: scatter + slot reduction), 2 = NVLS (AG: multimem.st broadcast push, RS: partial
                          tiles stay local and the owner sums them with multimem.ld_reduce). NVLS layouts: AG flags
-                         >= W*ceil(M/W/128)*32 words; RS ws = [2][max_M][N] partial buffer, flags >= W*ceil(M/W/128)*ceil(N/64) */
+                         >= W*ceil(M/W/128)*128 words; RS ws = [2][max_M][N] partial buffer, flags >= W*ceil(M/W/128)*ceil(N/64) */
   size_t ws_bytes;    /* size of ws; its two parity halves are ws_bytes/2 apart whatever the size of this call */
   size_t flags_words; /* capacity of flags (checked against the layout of the chosen protocol); 0 = unchecked */
 } tdist_fused_args;

@@ -39,19 +39,20 @@ if __name__ == "__main__":
     ref = torch_ag_gemm(A.float(), B.float())
     rows.append(dict(op="ag_gemm", cfg="torch NCCL+cuBLAS", ms=t_ref, ok=True))
     dist_print(f"ag_gemm  torch NCCL+cuBLAS: {t_ref:.4f} ms")
-    ag_cfgs = [(0, 0, -1, 8)] if args.quick or world == 1 else [
-        (2, 2, -1, 8), (2, 2, 8, 8), (2, 2, 16, 8), (2, 2, 32, 8), (2, 2, 16, 4), (2, 2, 32, 16), (2, 1, -1, 8), (2, 1, 16, 8),
-        (2, 1, 32, 8), (1, 1, -1, 8), (1, 2, -1, 8)]
-    for variant, cta_group, comm, slices in ag_cfgs:
+    ag_cfgs = [(0, 0, -1, 8, 1)] if args.quick or world == 1 else [
+        (2, 2, 8, 8, 1), (2, 2, 8, 8, 2), (2, 2, 8, 8, 4), (2, 2, 8, 8, 8), (2, 2, 4, 4, 4), (2, 2, 16, 16, 1), (2, 2, 16, 16, 4),
+        (2, 2, 32, 32, 1), (2, 2, 32, 32, 4), (2, 1, 8, 8, 4), (2, 1, 16, 16, 4), (1, 2, -1, 8, 1)]
+    for variant, cta_group, comm, slices, slabs in ag_cfgs:
         os.environ["TDIST_AG_SLICES"] = str(slices)
+        os.environ["TDIST_AG_KSLABS"] = str(slabs)
         ctx = create_ag_gemm_context(A, B, rank, world, max_M=M, num_local_ranks=world, num_comm_sms=comm)
         ctx.variant, ctx.cta_group = variant, cta_group
         C = ag_gemm(A, B, ctx)
         good = all_ok(check_close(C, ref, dt, "ag_gemm"))
         _, t = perf_func_max_over_ranks(lambda: ag_gemm(A, B, ctx), args.iters, 3, flush_l2=True)
-        name = f"{VAR.get(variant, 'auto')} cta_group={cta_group} push_ctas={comm} slices={slices}"
+        name = f"{VAR.get(variant, 'auto')} cta_group={cta_group} push_ctas={comm} slices={slices} kslabs={slabs}"
         rows.append(dict(op="ag_gemm", cfg=name, ms=t, ok=good))
-        dist_print(f"ag_gemm  {name:48s}: {t:.4f} ms  {t_ref / t:.2f}x  {'ok' if good else 'WRONG'}")
+        dist_print(f"ag_gemm  {name:60s}: {t:.4f} ms  {t_ref / t:.2f}x  {'ok' if good else 'WRONG'}")
         all_good = all_good and good
         ctx.finalize()
 
@@ -63,18 +64,21 @@ if __name__ == "__main__":
     ref2 = torch_gemm_rs(A2.float(), B2.float())
     rows.append(dict(op="gemm_rs", cfg="torch cuBLAS+NCCL", ms=t_ref, ok=True))
     dist_print(f"gemm_rs  torch cuBLAS+NCCL: {t_ref:.4f} ms")
-    rs_cfgs = [(0, 0, 0)] if args.quick or world == 1 else [(2, 2, 0), (2, 1, 0), (2, 2, 128), (1, 2, 0), (1, 1, 0)]
-    for variant, cta_group, bn in rs_cfgs:
+    rs_cfgs = [(0, 0, 0, 8)] if args.quick or world == 1 else [(2, 2, 0, 8), (2, 2, 0, 16), (2, 2, 0, 32), (2, 1, 0, 8), (1, 2, 0, 8)]
+    for variant, cta_group, bn, unit_rows in rs_cfgs:
+        os.environ["TDIST_RS_UNIT_ROWS"] = str(unit_rows)
         ctx = create_gemm_rs_context(M, K, rank, world, world, dt, BLOCK_N=bn)
         ctx.variant, ctx.cta_group = variant, cta_group
         C2 = gemm_rs(A2, B2, ctx)
         good = all_ok(check_close(C2, ref2, dt, "gemm_rs"))
         _, t = perf_func_max_over_ranks(lambda: gemm_rs(A2, B2, ctx), args.iters, 3, flush_l2=True)
-        name = f"{VAR.get(variant, 'auto')} cta_group={cta_group} block_n={bn}"
+        name = f"{VAR.get(variant, 'auto')} cta_group={cta_group} block_n={bn} unit_rows={unit_rows}"
         rows.append(dict(op="gemm_rs", cfg=name, ms=t, ok=good))
-        dist_print(f"gemm_rs  {name:48s}: {t:.4f} ms  {t_ref / t:.2f}x  {'ok' if good else 'WRONG'}")
+        dist_print(f"gemm_rs  {name:60s}: {t:.4f} ms  {t_ref / t:.2f}x  {'ok' if good else 'WRONG'}")
         all_good = all_good and good
         ctx.finalize()
+    for k in ("TDIST_AG_SLICES", "TDIST_AG_KSLABS", "TDIST_RS_UNIT_ROWS"):
+        os.environ.pop(k, None)
     if args.json and rank == 0:
         with open(args.json, "w") as f:
             json.dump(dict(world=world, M=M, N=N, K=K, rows=rows), f, indent=1)

@@ -106,8 +106,8 @@ class AllGatherGEMMTensorParallelContext:
             # [2 parity][max_M][K] gather workspace + per-(src, 128-row block) arrival flags
             self.symm_workspace = heap.alloc((2, self.max_M, self.K), self.tensor_dtype, zero=False)
             self.symm_workspaces = heap.peer_views(self.symm_workspace)
-            # 32 flag words per (source rank, 128-row block): one per push CTA sharing the block
-            self.flags_words = 32 * (self.num_ranks * ((self.max_M // self.num_ranks + 127) // 128) + 16)
+            # 128 flag words per (source rank, 128-row block): K slabs x push CTAs sharing the block
+            self.flags_words = 128 * (self.num_ranks * ((self.max_M // self.num_ranks + 127) // 128) + 16)
             self.state = CollectiveState(self.flags_words)
             self.max_gemm_sm = torch.cuda.get_device_properties("cuda").multi_processor_count
             heap.barrier_all()

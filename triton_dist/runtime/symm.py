@@ -92,10 +92,20 @@ class SymmetricHeap:
         # barrier state lives at the start of the heap
         self._bar_flags = self.alloc((_lib.MAX_RANKS,), torch.int32)
         self._bar_state = self.alloc((2,), torch.int32)
+        # The barrier kernel cannot order its own bootstrap: a fast rank's first arrival would land in a slow rank's
+        # flag words BEFORE that rank's zero fill above has executed, be wiped by it, and the slow rank would then wait
+        # for ever. So every rank finishes zeroing, and all ranks meet on the host, before the first device barrier.
+        torch.cuda.synchronize()
+        self._host_barrier()
         self.barrier_all()
         torch.cuda.synchronize()
 
     # ------------------------------------------------------------------ helpers
+    def _host_barrier(self) -> None:
+        if self.world > 1:
+            t = torch.zeros(1, dtype=torch.int32)
+            dist.all_reduce(t, group=self.group)
+
     def _all_ok(self, ok: bool) -> bool:
         if self.world == 1:
             return ok

@@ -109,6 +109,22 @@ __device__ __forceinline__ void wait_ge_sys(const uint32_t* flag, uint32_t value
   }
 #endif
 }
+// Same wait, polling with RELAXED loads and ending with one acquire load of the flag. Inside a kernel that keeps many
+// loads in flight (TMA pipelines, NVLS loads) an acquire in every poll iteration is expensive: a system-scope acquire
+// also waits for the SM's other outstanding memory traffic (measured on the fused GEMM+RS at 8 ranks, profiles/README.md).
+__device__ __forceinline__ void wait_ge_sys_poll_relaxed(const uint32_t* flag, uint32_t value) {
+#ifdef TDIST_SPIN_LIMIT
+  TDIST_SPIN_GUARD_DECL;
+  uint32_t v;
+  while (static_cast<int32_t>((v = ptx::ld_relaxed_sys(flag)) - value) < 0) {
+    TDIST_SPIN_GUARD(flag, v, value)
+  }
+#else
+  while (static_cast<int32_t>(ptx::ld_relaxed_sys(flag) - value) < 0) {
+  }
+#endif
+  (void)ptx::ld_acquire_sys(flag);
+}
 // Warp-collective wait on n consecutive flags (n <= 32): the first n lanes of
 // the warp each poll one flag, then the warp re-converges — this is exactly
 // how the reference lowers dl.wait (DistributedOpToLLVM.cpp:179-206).

@@ -447,6 +447,7 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.variant = v == 2 ? VARIANT_NVLS : VARIANT_LEGACY;  // without multicast the pull variant sums plain peer loads
     if (v < 0) p.variant = VARIANT_LEGACY;
     p.use_mc = c.mc_base != nullptr;
+    p.debug = env_int("TDIST_FUSED_DEBUG", 0);
     p.rs_unit_rows = env_int("TDIST_RS_UNIT_ROWS", 8);
     if (p.rs_unit_rows != 8 && p.rs_unit_rows != 16 && p.rs_unit_rows != 32) p.rs_unit_rows = 8;
     // both layouts ([W][M/W][N] scatter slots, [M][N] partial buffer) need M * N elements per parity

@@ -82,6 +82,7 @@ struct GemmParams {
   int ag_kslabs;           // AG 1: a block is pushed, flagged and consumed in this many K slabs; ag_slices * ag_kslabs <= kAgSlots
   int ag_slab_kblocks;     // AG 1: 64-wide k blocks per slab
   int rs_unit_rows;        // RS 1: rows of a tile one reducer warp sums per unit (8, 16 or 32)
+  int debug;               // ablations: 1 = RS reducers do nothing, 2 = no publish fence, 4 = reducers do not wait for flags (1, 2, 4: wrong results, timing only); 8 = RS publishes with a system-scope fence + release store
   long long a_lda;         // AG: row stride of a_local in elements
   size_t ws_parity_bytes;  // distance between the two parity halves of the workspace: a constant of the CONTEXT, so that
                            // calls of different sizes on one context never overlap the other parity's live data
@@ -255,114 +256,55 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
 
 // AG producer, NVLS variant: the push CTAs broadcast this rank's shard with multimem.st — every 16 bytes leave the GPU
 // once and the switch delivers them to all ranks' workspaces. An item is (128-row block j, K slab s, row slice sl):
-// `ag_slices` CTAs split the rows of a block, and a block is sent slab by slab, so that the consumers' K loops can
-// follow the arrival. Items are dealt round-robin to the push CTAs in (block, slab, slice) order.
-// Warps 0..6 move data and never wait for the link: they run ONE software-pipelined stream over all items of the CTA
-// (the loads of the next chunk, possibly of the next item, are issued before the stores of the current one) and after
-// the last store of an item arrive on a shared-memory barrier. Warp 7 publishes: it waits for an item's arrivals,
-// makes the stores visible system-wide (a full round trip through the switch) and releases the item's flag on every
-// rank. kDepth items are in flight between the two roles, which hides the fence latency behind the data stream.
-__device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint8_t* smem, uint32_t epoch, int comm_idx, int num_comm) {
-  constexpr int kDepth = 4;
-  constexpr int kDataThreads = kGemmThreads - 32;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* empty = full + kDepth;
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < kDepth; ++i) {
-      ptx::mbar_init(full + i, kDataThreads);
-      ptx::mbar_init(empty + i, 1);
-    }
-    ptx::fence_barrier_init();
-  }
-  __syncthreads();
+// `ag_slices` CTAs split the rows of a block, and a block may be sent in K slabs so that the consumers' K loops can
+// follow the arrival. Items are dealt round-robin to the push CTAs in (block, slab, slice) order. All threads of the
+// CTA move data (8 independent 16-byte loads per thread in flight before the first store), then the CTA meets, one
+// thread makes the stores visible system-wide and releases the item's flag on every rank.
+// Measured alternative (profiles/README.md): a publisher warp that fences while the other warps keep streaming is
+// SLOWER (0.173 vs 0.145 ms at 8 ranks) — the system fence then also waits for the younger stores, so flags come late.
+__device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint32_t epoch, int comm_idx, int num_comm) {
   const int rank = p.ctx.rank;
   const int bps = blocks_per_shard(p);
   const int slices = p.ag_slices, slabs = p.ag_kslabs;
   const int rows_per_slice = kBlockM / slices;
   const int slab_cols = p.ag_slab_kblocks * kBlockK;
   const int parity = (epoch >> 1) & 1;
-  const int items = bps * slabs * slices;
-  if (threadIdx.x >= kDataThreads) {
-    // ---- publisher. flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots], slot = slab * slices + slice
-    if (threadIdx.x == kDataThreads) {
-      int n = 0;
-      for (int item = comm_idx; item < items; item += num_comm, ++n) {
-        const int sl = item % slices;
-        const int js = item / slices;
-        const int j = js / slabs, sb = js - j * slabs;
-        ptx::mbar_wait(full + n % kDepth, (n / kDepth) & 1);
-        ptx::fence_acq_rel_sys();
-        ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sb * slices + sl), epoch);
-        ptx::mbar_arrive(empty + n % kDepth);
-      }
-    }
-    return;
-  }
   const char* src_base = static_cast<const char*>(p.a_local);
   char* dst_base = mc_ptr(p.ctx, static_cast<char*>(p.a_ws)) + size_t(parity) * p.ws_parity_bytes +
                    size_t(rank) * p.rows_per_rank * size_t(p.K) * 2;
-  constexpr int kBatch = 8;  // 16-byte vectors per thread and chunk
-  struct Chunk {
-    int n, item, k, iters;  // item ordinal of this CTA, global item, iteration inside the item, iterations of the item
-    int r0, col0, seg_vecs, n_vec;
-  };
-  auto geom = [&](Chunk& c) {
-    const int sl = c.item % slices;
-    const int js = c.item / slices;
+  const int items = bps * slabs * slices;
+  constexpr int kBatch = 8;
+  for (int item = comm_idx; item < items; item += num_comm) {
+    const int sl = item % slices;
+    const int js = item / slices;
     const int j = js / slabs, sb = js - j * slabs;
-    c.r0 = j * kBlockM + sl * rows_per_slice;
-    const int rows = max(0, min(rows_per_slice, p.rows_per_rank - c.r0));
-    c.col0 = sb * slab_cols;
-    c.seg_vecs = max(0, min(slab_cols, p.K - c.col0)) / 8;  // 16-byte vectors per row of this slab
-    c.n_vec = rows * c.seg_vecs;
-    c.iters = max(1, (c.n_vec + kDataThreads * kBatch - 1) / (kDataThreads * kBatch));
-  };
-  auto advance = [&](Chunk& c) -> bool {
-    if (++c.k < c.iters) return true;
-    c.k = 0;
-    ++c.n;
-    c.item += num_comm;
-    if (c.item >= items) return false;
-    geom(c);
-    return true;
-  };
-  auto load = [&](const Chunk& c, int4 (&v)[kBatch], size_t (&doff)[kBatch]) {
-    if (c.k == 0 && c.n >= kDepth) ptx::mbar_wait(empty + c.n % kDepth, ((c.n / kDepth) - 1) & 1);  // barrier reusable
-    const int i0 = c.k * kDataThreads * kBatch + threadIdx.x;
+    const int r0 = j * kBlockM + sl * rows_per_slice;
+    const int rows = max(0, min(rows_per_slice, p.rows_per_rank - r0));
+    const int col0 = sb * slab_cols;
+    const int seg_vecs = max(0, min(slab_cols, p.K - col0)) / 8;  // 16-byte vectors per row of this slab
+    const int n_vec = rows * seg_vecs;
+    for (int i0 = threadIdx.x; i0 < n_vec; i0 += blockDim.x * kBatch) {
+      int4 v[kBatch];
+      size_t doff[kBatch];
 #pragma unroll
-    for (int b = 0; b < kBatch; ++b) {
-      const int i = i0 + b * kDataThreads;
-      if (i < c.n_vec) {
-        const int r = i / c.seg_vecs, cv = i - r * c.seg_vecs;
-        v[b] = ptx::ld_nc_v4(src_base + (size_t(c.r0 + r) * p.a_lda + c.col0) * 2 + size_t(cv) * 16);
-        doff[b] = (size_t(c.r0 + r) * p.K + c.col0) * 2 + size_t(cv) * 16;
+      for (int b = 0; b < kBatch; ++b) {
+        const int i = i0 + b * blockDim.x;
+        if (i < n_vec) {
+          const int r = i / seg_vecs, cv = i - r * seg_vecs;
+          v[b] = ptx::ld_nc_v4(src_base + (size_t(r0 + r) * p.a_lda + col0) * 2 + size_t(cv) * 16);
+          doff[b] = (size_t(r0 + r) * p.K + col0) * 2 + size_t(cv) * 16;
+        }
       }
-    }
-  };
-  Chunk c{0, comm_idx, 0, 1, 0, 0, 0, 0};
-  if (c.item >= items) return;
-  geom(c);
-  int4 va[kBatch];
-  size_t da[kBatch];
-  load(c, va, da);
-  for (bool have = true; have;) {
-    Chunk nx = c;
-    const bool have_nx = advance(nx);
-    int4 vb[kBatch];
-    size_t db[kBatch];
-    if (have_nx) load(nx, vb, db);
-    const int i0 = c.k * kDataThreads * kBatch + threadIdx.x;
 #pragma unroll
-    for (int b = 0; b < kBatch; ++b)
-      if (i0 + b * kDataThreads < c.n_vec) ptx::multimem_st_v4(dst_base + da[b], va[b]);
-    if (c.k == c.iters - 1) ptx::mbar_arrive(full + c.n % kDepth);
-#pragma unroll
-    for (int b = 0; b < kBatch; ++b) {
-      va[b] = vb[b];
-      da[b] = db[b];
+      for (int b = 0; b < kBatch; ++b)
+        if (i0 + b * blockDim.x < n_vec) ptx::multimem_st_v4(dst_base + doff[b], v[b]);
     }
-    c = nx;
-    have = have_nx;
+    __syncthreads();
+    // flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots], slot = slab * slices + slice
+    if (threadIdx.x == 0) {
+      ptx::fence_acq_rel_sys();
+      ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sb * slices + sl), epoch);
+    }
   }
 }
 
@@ -387,6 +329,7 @@ __device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch
   char* out = static_cast<char*>(p.out);
   const bool use_mc = p.ctx.mc_base != nullptr && p.use_mc;
   constexpr int kBatch = 8;
+  if (p.debug & 1) return;
   for (int u = cw; u < units; u += ncw) {
     const int ti = u / kSub, sc = u - ti * kSub;
     int blk, n_blk;
@@ -402,7 +345,7 @@ __device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch
     const int r0 = blk * kBlockM + sc * unit_rows;
     if (blk >= bps || r0 >= p.rows_per_rank) continue;
     // flags layout (RS, NVLS): [W src][bps][tiles_n], written by src when its partial tile is stored
-    if (lane < W) wait_ge_sys(p.flags + (size_t(lane) * bps + blk) * tiles_n + n_blk, epoch);
+    if (lane < W && !(p.debug & 4)) wait_ge_sys_poll_relaxed(p.flags + (size_t(lane) * bps + blk) * tiles_n + n_blk, epoch);
     __syncwarp();
     const int rows = min(unit_rows, p.rows_per_rank - r0);
     const int col0 = n_blk * BLOCK_N;
@@ -594,7 +537,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
     // ------------------------------------------------------------ comm CTA
     if (p.mode == GEMM_AG) {
       if (p.variant == VARIANT_NVLS)
-        ag_push_mc_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
       else
         ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
     } else if (p.mode == GEMM_AR) {
@@ -613,6 +556,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
     uint64_t* tmem_full = empty_bar + STAGES;
     uint64_t* tmem_empty = tmem_full + 2;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint32_t* stored_count = tmem_ptr_smem + 1;  // RS (NVLS): tiles of this CTA whose partial result is in memory
     constexpr int kTmemCols = tmem_cols<BLOCK_N>();
     constexpr int kAccStride = (BLOCK_N + 31) / 32 * 32;
 
@@ -629,6 +573,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
         ptx::mbar_init(tmem_full + i, 1);
         ptx::mbar_init(tmem_empty + i, 4);  // one arrival per epilogue warp
       }
+      *stored_count = 0;
       ptx::fence_barrier_init();
     }
     if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_ptr_smem);
@@ -664,7 +609,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               ta = &p.tma_a[parity];
               if (p.variant != VARIANT_NVLS) {
                 // wait until every part of block (src, blk) has landed in my workspace
-                if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps + tc.blk) * kAgParts + lane, epoch);
+                if (lane < kAgParts) wait_ge_sys_poll_relaxed(p.flags + (tc.shard * bps + tc.blk) * kAgParts + lane, epoch);
                 __syncwarp();
                 ptx::fence_proxy_async();
               } else {
@@ -675,7 +620,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           for (int kb = 0; kb < num_k; ++kb) {
             if (slab_flags != nullptr && kb % p.ag_slab_kblocks == 0) {
               // NVLS push: the K loop follows the arrival of the block's K slabs (lanes poll the row slices of a slab)
-              if (lane < p.ag_slices) wait_ge_sys(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
+              if (lane < p.ag_slices) wait_ge_sys_poll_relaxed(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
               __syncwarp();
               ptx::fence_proxy_async();
             }
@@ -741,7 +686,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       // stalling the epilogue for a link round trip per tile.
       int pend_t = -1, pend_shard = 0, pend_blk = 0, pend_nblk = 0;
       auto publish = [&](int t_done, int shard, int blk, int n_blk) {
-        ptx::fence_acq_rel_sys();
+        if (!(p.debug & 2)) ptx::fence_acq_rel_sys();
         if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
           // my partial tile is in my own memory: tell the owner it may be summed
           const int bps = blocks_per_shard(p);
@@ -845,9 +790,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           }
         }
         if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
-          // the partial tile went to local memory: nothing to drain, flag the owner right away
+          // The partial tile is in local memory. Telling the owner needs a system-scope fence, and that fence also
+          // waits for whatever else this SM has in flight (measured: 24 us of the 8-rank op when the epilogue issued
+          // it while the reducer warp's NVLS loads were outstanding). So the epilogue only counts the tile; warp 3
+          // publishes it.
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (warp == 4 && lane == 0) publish(t, tc.shard, tc.blk, tc.n_blk);
+          if (warp == 4 && lane == 0) {
+            __threadfence_block();
+            atomicAdd(stored_count, 1u);
+          }
         } else if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
           // all 4 epilogue warps have issued their stores; remember the tile, publish it one tile later
           asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -863,12 +814,36 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       }
       if (pend_t >= 0 && warp == 4 && lane == 0) publish(pend_t, pend_shard, pend_blk, pend_nblk);
     } else if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
-      // ======================================================== warps 2-3: NVLS reducers of my own segment
-      const int cw = gemm_cta * 2 + (warp - 2);
-      if (p.is_bf16)
-        rs_pull_body<BF16, BLOCK_N>(p, epoch, cw, num_gemm * 2, tiles_n, false);
-      else
-        rs_pull_body<F16, BLOCK_N>(p, epoch, cw, num_gemm * 2, tiles_n, false);
+      if (warp == 3) {
+        // ====================================================== warp 3: publishes this CTA's finished tiles
+        if (lane == 0) {
+          const int bps = blocks_per_shard(p);
+          uint32_t k = 0;
+          for (int t = gemm_cta; t < tiles; t += num_gemm, ++k) {
+            const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+            while (*reinterpret_cast<volatile uint32_t*>(stored_count) <= k) {
+            }
+            __threadfence_block();
+            uint32_t* flag = symm_at(p.ctx, p.flags + (size_t(p.ctx.rank) * bps + tc.blk) * tiles_n + tc.n_blk, tc.shard);
+            if (!(p.debug & 8)) {
+              // The partial tile is in THIS GPU's memory and the owner's switch reads are served from this GPU's L2,
+              // so a GPU-scope fence orders the tile before the flag; the flag itself is a plain system-scope store.
+              // (A system-scope fence here costs ~35 us of the 8-rank op: it waits for the NVLS loads of warp 2.)
+              ptx::fence_acq_rel_gpu();
+              ptx::st_relaxed_sys(flag, epoch);
+            } else {
+              if (!(p.debug & 2)) ptx::fence_acq_rel_sys();
+              ptx::st_release_sys(flag, epoch);
+            }
+          }
+        }
+      } else {
+        // ====================================================== warp 2: NVLS reducer of my own segment
+        if (p.is_bf16)
+          rs_pull_body<BF16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_n, false);
+        else
+          rs_pull_body<F16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_n, false);
+      }
     }
     // teardown of the GEMM roles
     ptx::tcgen05_fence_before();

@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
   if (gemm_cta < 0) {
     if (p.mode == GEMM_AG) {
       if (p.variant == VARIANT_NVLS)
-        ag_push_mc_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+        ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
       else
         ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
     }
@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
     uint64_t* tmem_full = empty_bar + STAGES;
     uint64_t* tmem_empty = tmem_full + 2;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint32_t* stored_count = tmem_ptr_smem + 1;  // RS (NVLS): tiles of this CTA whose partial result is in memory
     constexpr int kTmemCols = tmem_cols<BLOCK_N>();
     constexpr int kAccStride = (BLOCK_N + 31) / 32 * 32;
 
@@ -150,6 +151,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
         ptx::mbar_init(tmem_full + i, 1);
         ptx::mbar_init(tmem_empty + i, 8);
       }
+      *stored_count = 0;
       ptx::fence_barrier_init();
     }
     if (warp == 2) ptx::tmem_alloc_cg2<kTmemCols>(tmem_ptr_smem);
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
               ta = &p.tma_a[parity];
               if (blk128 < bps128) {
                 if (p.variant != VARIANT_NVLS) {
-                  if (lane < kAgParts) wait_ge_sys(p.flags + (tc.shard * bps128 + blk128) * kAgParts + lane, epoch);
+                  if (lane < kAgParts) wait_ge_sys_poll_relaxed(p.flags + (tc.shard * bps128 + blk128) * kAgParts + lane, epoch);
                   __syncwarp();
                   ptx::fence_proxy_async();
                 } else {
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
           for (int kb = 0; kb < num_k; ++kb) {
             if (slab_flags != nullptr && kb % p.ag_slab_kblocks == 0) {
               // NVLS push: the K loop follows the arrival of my 128 rows' K slabs
-              if (lane < p.ag_slices) wait_ge_sys(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
+              if (lane < p.ag_slices) wait_ge_sys_poll_relaxed(slab_flags + (kb / p.ag_slab_kblocks) * p.ag_slices + lane, epoch);
               __syncwarp();
               ptx::fence_proxy_async();
             }
@@ -255,7 +257,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
       const int W = p.ctx.world;
       int pend_shard = 0, pend_blk = -1, pend_nblk = 0;
       auto publish = [&](int shard, int blk, int n_blk) {
-        ptx::fence_acq_rel_sys();
+        if (!(p.debug & 2)) ptx::fence_acq_rel_sys();
         if (p.variant == VARIANT_NVLS) {
           // my 128 rows of the partial tile are in my own memory: tell the owner they may be summed
           notify(p.ctx, p.flags + (size_t(p.ctx.rank) * bps128 + blk) * tiles_n + n_blk, shard, epoch);
@@ -334,10 +336,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
           }
         }
         if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
-          // the partial tile went to local memory: nothing to drain, flag the owner right away
+          // the partial tile is in local memory: count it, warp 3 publishes it (the system fence of a publish also
+          // waits for the reducer warp's outstanding NVLS loads; see gemm_sm100.cuh)
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          const int blk128 = tc.pblk * 2 + int(cta_rank);
-          if (blk128 < bps128 && warp == 4 && lane == 0) publish(tc.shard, blk128, tc.n_blk);
+          if (warp == 4 && lane == 0) {
+            __threadfence_block();
+            atomicAdd(stored_count, 1u);
+          }
         } else if (p.mode == GEMM_RS) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
           const int blk128 = tc.pblk * 2 + int(cta_rank);
@@ -354,13 +359,38 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
       }
       if (pend_blk >= 0 && warp == 4 && lane == 0) publish(pend_shard, pend_blk, pend_nblk);
     } else if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
-      // ======================================================== warps 2-3: NVLS reducers of my own segment
-      const int cw = gemm_cta * 2 + (warp - 2);
-      const int ncw = (static_cast<int>(gridDim.x) - p.num_comm_ctas) * 2;
-      if (p.is_bf16)
-        rs_pull_body<BF16, BLOCK_N>(p, epoch, cw, ncw, tiles_n, true);
-      else
-        rs_pull_body<F16, BLOCK_N>(p, epoch, cw, ncw, tiles_n, true);
+      if (warp == 3) {
+        // ====================================================== warp 3: publishes this CTA's finished half tiles
+        if (lane == 0) {
+          uint32_t k = 0;
+          for (int t = pair; t < tiles; t += num_pairs, ++k) {
+            const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
+            while (*reinterpret_cast<volatile uint32_t*>(stored_count) <= k) {
+            }
+            __threadfence_block();
+            const int blk128 = tc.pblk * 2 + int(cta_rank);
+            if (blk128 >= bps128) continue;
+            uint32_t* flag = symm_at(p.ctx, p.flags + (size_t(p.ctx.rank) * bps128 + blk128) * tiles_n + tc.n_blk, tc.shard);
+            if (!(p.debug & 8)) {
+              // The partial tile is in THIS GPU's memory and the owner's switch reads are served from this GPU's L2,
+              // so a GPU-scope fence orders the tile before the flag; the flag itself is a plain system-scope store.
+              // (A system-scope fence here costs ~35 us of the 8-rank op: it waits for the NVLS loads of warp 2.)
+              ptx::fence_acq_rel_gpu();
+              ptx::st_relaxed_sys(flag, epoch);
+            } else {
+              if (!(p.debug & 2)) ptx::fence_acq_rel_sys();
+              ptx::st_release_sys(flag, epoch);
+            }
+          }
+        }
+      } else {
+        // ====================================================== warp 2: NVLS reducer of my own segment
+        const int ncw = static_cast<int>(gridDim.x) - p.num_comm_ctas;
+        if (p.is_bf16)
+          rs_pull_body<BF16, BLOCK_N>(p, epoch, gemm_cta, ncw, tiles_n, true);
+        else
+          rs_pull_body<F16, BLOCK_N>(p, epoch, gemm_cta, ncw, tiles_n, true);
+      }
     }
     // teardown: the pair stays together until both CTAs are done with each other's shared memory / barriers
     ptx::tcgen05_fence_before();

@@ -203,12 +203,12 @@ __global__ void __launch_bounds__(512) allgather_kernel(SymmCtx c, const int4* _
 // the packet itself, so a message costs one NVLink one-way trip and no fence.
 // llbuf: [2 parity][W][shard_u64] packets (16 B each). in/out are 8-byte units.
 __global__ void __launch_bounds__(512) allgather_ll_kernel(SymmCtx c, const uint2* __restrict__ in, int4* llbuf,
-                                                           uint2* out, size_t shard_u64, PhaseState ps,
-                                                           int use_mc) {
+                                                           uint2* out, size_t shard_u64, size_t parity_pkts,
+                                                           PhaseState ps, int use_mc) {
   const uint32_t base = phase_begin(ps);
   const uint32_t flag = base + 1;
   const int W = c.world;
-  int4* buf = llbuf + ((base >> 1) & 1) * W * shard_u64;
+  int4* buf = llbuf + ((base >> 1) & 1) * parity_pkts;  // fixed distance: half the buffer, not a size of this call
   const size_t per_cta = (shard_u64 + gridDim.x - 1) / gridDim.x;
   const size_t beg = blockIdx.x * per_cta;
   const size_t end = min(beg + per_cta, shard_u64);
@@ -243,12 +243,12 @@ __global__ void __launch_bounds__(512) allgather_ll_kernel(SymmCtx c, const uint
 // out: [seg_vecs] = sum over ranks of their segment `rank`.
 template <typename Tag>
 __global__ void __launch_bounds__(512) reduce_scatter_kernel(SymmCtx c, const int4* __restrict__ in, int4* scat,
-                                                             int4* out, size_t seg_vecs, uint32_t* flags,
-                                                             PhaseState ps) {
+                                                             int4* out, size_t seg_vecs, size_t parity_vecs,
+                                                             uint32_t* flags, PhaseState ps) {
   const uint32_t base = phase_begin(ps);
   const uint32_t phase = base + 1;
   const int W = c.world;
-  int4* buf = scat + ((base >> 1) & 1) * W * seg_vecs;
+  int4* buf = scat + ((base >> 1) & 1) * parity_vecs;  // fixed distance between the parity halves
   const size_t per_cta = (seg_vecs + gridDim.x - 1) / gridDim.x;
   const size_t beg = blockIdx.x * per_cta;
   const size_t end = min(beg + per_cta, seg_vecs);
@@ -348,8 +348,10 @@ int tdist_allreduce(const tdist_symm_ctx* ctx, int method, int dtype, const void
       }
       case TDIST_AR_TWO_SHOT: {
         const size_t shard_cap = (n_vec + W - 1) / W + 2 * size_t(grid);
-        const size_t parity_vecs = W * shard_cap + n_vec;
-        if (ws_bytes / 16 < 2 * parity_vecs) {
+        // the two parity halves are half the workspace apart whatever this call's size is: calls of different sizes
+        // must not overlap the half a slower rank is still reading
+        const size_t parity_vecs = ws_bytes / 16 / 2;
+        if (parity_vecs < W * shard_cap + n_vec) {
           set_error("allreduce two_shot: workspace too small");
           return -1;
         }
@@ -389,7 +391,7 @@ int tdist_allreduce(const tdist_symm_ctx* ctx, int method, int dtype, const void
 }
 
 int tdist_allgather(const tdist_symm_ctx* ctx, int mode, const void* in, void* symm, void* out, size_t shard_bytes,
-                    uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas, void* stream) {
+                    size_t symm_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas, void* stream) {
   const SymmCtx c = to_ctx(ctx);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const PhaseState ps{phase, done};
@@ -404,9 +406,14 @@ int tdist_allgather(const tdist_symm_ctx* ctx, int mode, const void* in, void* s
       return -1;
     }
     const size_t n = shard_bytes / 8;
+    const size_t parity_pkts = symm_bytes / 16 / 2;
+    if (parity_pkts < size_t(c.world) * n) {
+      set_error("allgather LL: packet buffer too small (need 2 * W * shard_bytes * 2 bytes)");
+      return -1;
+    }
     int grid = pick_grid(n, max_ctas, 512);
     allgather_ll_kernel<<<grid, 512, 0, s>>>(c, static_cast<const uint2*>(in), static_cast<int4*>(symm),
-                                             static_cast<uint2*>(out), n, ps, mode == TDIST_AG_LL_MC);
+                                             static_cast<uint2*>(out), n, parity_pkts, ps, mode == TDIST_AG_LL_MC);
     return check_launch("allgather_ll");
   }
   if (shard_bytes % 16 != 0) {
@@ -424,8 +431,8 @@ int tdist_allgather(const tdist_symm_ctx* ctx, int mode, const void* in, void* s
   return check_launch("allgather");
 }
 
-int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, void* scatter_ws, void* out,
-                         size_t seg_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas,
+int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, void* scatter_ws, size_t ws_bytes,
+                         void* out, size_t seg_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas,
                          void* stream) {
   if (seg_bytes % 16 != 0) {
     set_error("reduce_scatter: segment bytes must be a multiple of 16");
@@ -433,11 +440,16 @@ int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, v
   }
   const SymmCtx c = to_ctx(ctx);
   const size_t n = seg_bytes / 16;
+  const size_t parity_vecs = ws_bytes / 16 / 2;
+  if (parity_vecs < size_t(c.world) * n) {
+    set_error("reduce_scatter: workspace too small (need 2 * W * seg_bytes)");
+    return -1;
+  }
   if (max_ctas > TDIST_MAX_CTAS) max_ctas = TDIST_MAX_CTAS;
   int grid = pick_grid(n, max_ctas, 512);
   TDIST_DISPATCH_DTYPE(dtype, {
     reduce_scatter_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
-        c, static_cast<const int4*>(in), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), n, flags,
+        c, static_cast<const int4*>(in), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), n, parity_vecs, flags,
         PhaseState{phase, done});
   });
   return check_launch("reduce_scatter");

@@ -181,13 +181,13 @@ static int want_cta_pair(const tdist_gemm_args* a) {
 
 // protocol variant of a fused op: explicit argument > environment (TDIST_AG_VARIANT / TDIST_RS_VARIANT: 1 = point to
 // point, 2 = NVLS) > NVLS whenever the heap has a multicast mapping
-static int pick_variant(const tdist_fused_args* f, const SymmCtx& c, const char* env_name) {
+static int pick_variant(const tdist_fused_args* f, const SymmCtx& c, const char* env_name, int min_world_for_nvls) {
   int v = f->variant;
   if (v == 0) {
     const char* e = getenv(env_name);
     if (e) v = atoi(e);
   }
-  if (v == 0) v = (c.mc_base != nullptr && c.world > 1) ? 2 : 1;
+  if (v == 0) v = (c.mc_base != nullptr && c.world >= min_world_for_nvls) ? 2 : 1;
   if (v == 2 && c.mc_base == nullptr) v = -1;
   return v;
 }
@@ -371,7 +371,9 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     if (W == 1) comm = 0;
     if (comm < 0) comm = env_int("TDIST_AG_PUSH_CTAS", -1);
     comm_given = comm >= 0;
-    const int v = pick_variant(f, c, "TDIST_AG_VARIANT");
+    // measured (profiles/README.md, Llama-3-8B MLP shape): with one peer the broadcast has nothing to save and the
+    // unicast ring wins (0.317 vs 0.349 ms); at 4 ranks they tie, at 8 the broadcast wins (0.149 vs 0.219 ms)
+    const int v = pick_variant(f, c, "TDIST_AG_VARIANT", 3);
     if (v < 0) {
       set_error("ag_gemm: the NVLS variant needs a heap with a multicast mapping");
       return -1;
@@ -405,7 +407,13 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
         return -1;
       }
       if (comm < 0) {
-        comm = slices;
+        // one group of `slices` CTAs per ~8 MiB of shard: a group moves ~100 GB/s, the push has to finish well inside
+        // the GEMM (measured: 8 CTAs at 8 ranks / 8 MiB, 16 at 4 ranks / 16 MiB; more groups than needed delay the
+        // first blocks, because groups work on different blocks at the same time)
+        const size_t shard_bytes = size_t(p.rows_per_rank) * a->K * 2;
+        int groups = int((shard_bytes + (6u << 20)) / (8u << 20));
+        groups = groups < 1 ? 1 : groups > 4 ? 4 : groups;
+        comm = slices * groups;
         comm_given = true;
       }
     } else if (a->lda != a->K) {
@@ -443,13 +451,14 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     p.out = f->out;
     p.ldc = a->N;
     comm = 0;
-    const int v = pick_variant(f, c, "TDIST_RS_VARIANT");
+    // measured: the NVLS pull wins at 2, 4 and 8 ranks (0.341 / 0.176 / 0.130 ms against 0.367 / 0.254 / 0.230 ms)
+    const int v = pick_variant(f, c, "TDIST_RS_VARIANT", 2);
     p.variant = v == 2 ? VARIANT_NVLS : VARIANT_LEGACY;  // without multicast the pull variant sums plain peer loads
     if (v < 0) p.variant = VARIANT_LEGACY;
     p.use_mc = c.mc_base != nullptr;
     p.debug = env_int("TDIST_FUSED_DEBUG", 0);
-    p.rs_unit_rows = env_int("TDIST_RS_UNIT_ROWS", 8);
-    if (p.rs_unit_rows != 8 && p.rs_unit_rows != 16 && p.rs_unit_rows != 32) p.rs_unit_rows = 8;
+    p.rs_unit_rows = env_int("TDIST_RS_UNIT_ROWS", 16);
+    if (p.rs_unit_rows != 8 && p.rs_unit_rows != 16 && p.rs_unit_rows != 32) p.rs_unit_rows = 16;
     // both layouts ([W][M/W][N] scatter slots, [M][N] partial buffer) need M * N elements per parity
     const size_t par_need = size_t(a->M) * a->N * 2;
     p.ws_parity_bytes = f->ws_bytes > 0 ? f->ws_bytes / 2 : par_need;

@@ -125,12 +125,12 @@ template <typename Tag>
 __global__ void __launch_bounds__(512) moe_reduce_rs_kernel(SymmCtx c, const int4* __restrict__ y, int4* scat,
                                                             int4* __restrict__ out, const int* __restrict__ pair_to_row,
                                                             const float* __restrict__ weights, int tokens, int topk,
-                                                            int row_vecs, uint32_t* flags, PhaseState ps) {
+                                                            int row_vecs, size_t parity_vecs, uint32_t* flags, PhaseState ps) {
   const uint32_t base = phase_begin(ps);
   const int W = c.world;
   const int seg_tokens = tokens / W;
   const size_t seg_vecs = size_t(seg_tokens) * row_vecs;
-  int4* buf = scat + ((base >> 1) & 1) * W * seg_vecs;
+  int4* buf = scat + ((base >> 1) & 1) * parity_vecs;  // fixed distance between the parity halves of the workspace
   const size_t per_cta = (seg_vecs + gridDim.x - 1) / gridDim.x;
   const size_t beg = blockIdx.x * per_cta;
   const size_t end = min(beg + per_cta, seg_vecs);
@@ -274,7 +274,7 @@ int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_t
   return check_launch("moe_topk_reduce");
 }
 
-int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, void* out,
+int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, size_t ws_bytes, void* out,
                         const int* pair_to_row, const float* weights, int tokens, int topk, int row_bytes, uint32_t* flags,
                         uint32_t* phase, uint32_t* done, int max_ctas, void* stream) {
   const SymmCtx c = to_ctx(ctx);
@@ -284,6 +284,11 @@ int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, voi
   }
   const int row_vecs = row_bytes / 16;
   const size_t seg_vecs = size_t(tokens / c.world) * row_vecs;
+  const size_t parity_vecs = ws_bytes / 16 / 2;
+  if (parity_vecs < size_t(c.world) * seg_vecs) {
+    set_error("moe_reduce_rs: workspace too small (need 2 * tokens * row_bytes)");
+    return -1;
+  }
   if (max_ctas > TDIST_MAX_CTAS) max_ctas = TDIST_MAX_CTAS;
   int grid = int((seg_vecs + 511) / 512);
   if (grid > max_ctas) grid = max_ctas;
@@ -291,7 +296,7 @@ int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, voi
   TDIST_DISPATCH_DTYPE(dtype, {
     moe_reduce_rs_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
         c, static_cast<const int4*>(y), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), pair_to_row, weights,
-        tokens, topk, row_vecs, flags, PhaseState{phase, done});
+        tokens, topk, row_vecs, parity_vecs, flags, PhaseState{phase, done});
   });
   return check_launch("moe_reduce_rs");
 }

@@ -54,6 +54,7 @@ const DriverApi& driver() {
     resolve("cuMulticastAddDevice", a.cuMulticastAddDevice, ignore);
     resolve("cuMulticastBindMem", a.cuMulticastBindMem, ignore);
     resolve("cuMulticastGetGranularity", a.cuMulticastGetGranularity, ignore);
+    resolve("cuMulticastUnbind", a.cuMulticastUnbind, ignore);
     a.ok = ok;
   });
   return api;

@@ -36,6 +36,7 @@ struct DriverApi {
   CUresult (*cuMulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
   CUresult (*cuMulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t,
                                  size_t, unsigned long long) = nullptr;
+  CUresult (*cuMulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
   CUresult (*cuMulticastGetGranularity)(size_t*, const CUmulticastObjectProp*,
                                         CUmulticastGranularity_flags) = nullptr;
   CUresult (*cuStreamWriteValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;

@@ -40,7 +40,7 @@ struct Heap {
   // multicast
   CUmemGenericAllocationHandle mc_handle = 0;
   CUdeviceptr mc_va = 0;
-  bool mc_added = false, mc_mapped = false;
+  bool mc_added = false, mc_mapped = false, mc_bound = false;
   // generic
   void* base[TDIST_MAX_RANKS] = {nullptr};
 };
@@ -272,6 +272,8 @@ extern "C" {
 
 const char* tdist_last_error(void) { return tdist::last_error(); }
 
+static void release_vmm(Heap* h);
+
 int tdist_heap_create(int rank, int world, int device, size_t bytes, const char* job_id, tdist_heap** out) {
   if (world < 1 || world > TDIST_MAX_RANKS || rank < 0 || rank >= world) {
     tdist::set_error("tdist_heap_create: bad rank/world");
@@ -286,6 +288,7 @@ int tdist_heap_create(int rank, int world, int device, size_t bytes, const char*
   h->bytes = bytes;
   h->job = job_id ? job_id : "job";
   if (tdist::heap_create_vmm(h) != 0) {
+    release_vmm(h);
     delete h;
     return -1;
   }
@@ -409,6 +412,7 @@ int tdist_heap_mc_phase_b(tdist_heap* hh) {
     return -1;
   }
   TDIST_CU_TRY(d.cuMulticastBindMem(h->mc_handle, 0, h->handles[h->rank], 0, h->bytes, 0));
+  h->mc_bound = true;
   TDIST_CU_TRY(d.cuMemAddressReserve(&h->mc_va, h->bytes, 0, 0, 0));
   TDIST_CU_TRY(d.cuMemMap(h->mc_va, h->bytes, 0, h->mc_handle, 0));
   CUmemAccessDesc acc;
@@ -440,21 +444,37 @@ int tdist_heap_fill_ctx(tdist_heap* hh, tdist_symm_ctx* out) {
   return 0;
 }
 
+// Undo whatever part of a VMM heap exists (also called for a heap whose creation failed half way: nothing may stay
+// mapped or pinned, because the caller then falls back to a second, cudaIpc-backed heap of the same size).
+static void release_vmm(Heap* h) {
+  const tdist::DriverApi& d = tdist::driver();
+  if (!d.ok) return;
+  if (h->mc_mapped) {
+    d.cuMemUnmap(h->mc_va, h->bytes);
+    d.cuMemAddressFree(h->mc_va, h->bytes);
+    h->mc_mapped = false;
+  }
+  if (h->mc_handle) {
+    // unbind this device's memory from the multicast object before the handles go away
+    if (h->mc_bound && d.cuMulticastUnbind) d.cuMulticastUnbind(h->mc_handle, h->device, 0, h->bytes);
+    d.cuMemRelease(h->mc_handle);
+    h->mc_handle = 0;
+  }
+  for (int p = 0; p < static_cast<int>(h->handles.size()); ++p) {
+    if (h->va && h->base[p]) d.cuMemUnmap(h->va + static_cast<size_t>(p) * h->bytes, h->bytes);
+    if (h->handles[p]) d.cuMemRelease(h->handles[p]);
+    h->handles[p] = 0;
+    h->base[p] = nullptr;
+  }
+  if (h->va) d.cuMemAddressFree(h->va, h->bytes * h->world);
+  h->va = 0;
+}
+
 int tdist_heap_destroy(tdist_heap* hh) {
   Heap* h = reinterpret_cast<Heap*>(hh);
-  const tdist::DriverApi& d = tdist::driver();
   cudaDeviceSynchronize();
   if (h->mode == 1) {
-    if (h->mc_mapped) {
-      d.cuMemUnmap(h->mc_va, h->bytes);
-      d.cuMemAddressFree(h->mc_va, h->bytes);
-    }
-    if (h->mc_handle) d.cuMemRelease(h->mc_handle);
-    for (int p = 0; p < h->world; ++p) {
-      d.cuMemUnmap(h->va + static_cast<size_t>(p) * h->bytes, h->bytes);
-      if (h->handles[p]) d.cuMemRelease(h->handles[p]);
-    }
-    d.cuMemAddressFree(h->va, h->bytes * h->world);
+    release_vmm(h);
   } else {
     for (int p = 0; p < h->world; ++p) {
       if (p == h->rank) continue;

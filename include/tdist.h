@@ -75,10 +75,11 @@ enum { TDIST_AG_PULL = 0, TDIST_AG_PUSH = 1, TDIST_AG_PUSH_MC = 2, TDIST_AG_LL =
 /* kernels/nvidia/low_latency_allgather.py:47-777. symm: [W][shard] (LL modes:
  * [2][W][shard/8] 16-byte packets). out may be NULL (result stays in symm). */
 int tdist_allgather(const tdist_symm_ctx* ctx, int mode, const void* in, void* symm, void* out, size_t shard_bytes,
-                    uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas, void* stream);
+                    size_t symm_bytes /* LL modes: size of symm; its parity halves are symm_bytes/2 apart */, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas, void* stream);
 
-/* kernels/nvidia/reduce_scatter.py:285-866. in: [W][seg]; scatter_ws (symm): [2][W][seg]; out: [seg] */
-int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, void* scatter_ws, void* out,
+/* kernels/nvidia/reduce_scatter.py:285-866. in: [W][seg]; scatter_ws (symm): two parity halves ws_bytes/2 apart, each
+ * [W][seg]; out: [seg] */
+int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, void* scatter_ws, size_t ws_bytes, void* out,
                          size_t seg_bytes, uint32_t* flags, uint32_t* phase, uint32_t* done, int max_ctas,
                          void* stream);
 /* out = sum of `slots` segments (ring_reduce, reduce_scatter.py:673-810) */
@@ -161,7 +162,7 @@ int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids
 int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,
                           int topk, int row_bytes, void* stream);
 /* fused top-k reduce + reduce-scatter over token segments (moe_reduce_rs.py:292-376) */
-int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, void* out,
+int tdist_moe_reduce_rs(const tdist_symm_ctx* ctx, int dtype, const void* y, void* scatter_ws, size_t ws_bytes, void* out,
                         const int* pair_to_row, const float* weights, int tokens, int topk, int row_bytes, uint32_t* flags,
                         uint32_t* phase, uint32_t* done, int max_ctas, void* stream);
 

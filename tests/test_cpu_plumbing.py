@@ -41,6 +41,11 @@ def test_tp_e2e_vs_hf_cpu(model):
     run_dist(N + "test_tp_e2e", ["--model", model, "--check"], 2, timeout=900)
 
 
+def test_tp_e2e_comparison_can_fail_cpu():
+    """The HF comparison is not vacuous: with ten LM-head rows swapped every backend mode must be reported as a mismatch."""
+    run_dist(N + "test_tp_e2e", ["--model", "qwen3", "--check", "--corrupt", "--modes", "torch,triton_dist_AR"], 2, timeout=900)
+
+
 def test_ep_dispatch_combine_cpu():
     run_dist(N + "test_ep_a2a", ["--check", "--verify-iters", 2], 2)
 

@@ -135,8 +135,8 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_stream_wait_value64", [vp, vp, ctypes.c_ulonglong, i32])
     sig("tdist_barrier_all", [P(SymmCtx), vp, vp, vp, vp])
     sig("tdist_allreduce", [P(SymmCtx), i32, i32, vp, vp, sz, vp, sz, vp, vp, vp, i32, i32, vp])
-    sig("tdist_allgather", [P(SymmCtx), i32, vp, vp, vp, sz, vp, vp, vp, i32, vp])
-    sig("tdist_reduce_scatter", [P(SymmCtx), i32, vp, vp, vp, sz, vp, vp, vp, i32, vp])
+    sig("tdist_allgather", [P(SymmCtx), i32, vp, vp, vp, sz, sz, vp, vp, vp, i32, vp])
+    sig("tdist_reduce_scatter", [P(SymmCtx), i32, vp, vp, sz, vp, sz, vp, vp, vp, i32, vp])
     sig("tdist_slot_reduce", [i32, vp, vp, sz, i32, i32, i32, vp])
     sig("tdist_p2p_copy", [vp, vp, sz, i32, vp])
     sig("tdist_signal_set", [vp, u32, i32, vp])
@@ -156,7 +156,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_moe_tile_swizzle", [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
     sig("tdist_moe_gather_rows", [vp, vp, vp, vp, i32, i32, i32, i32, vp])
     sig("tdist_moe_topk_reduce", [i32, vp, vp, vp, vp, i32, i32, i32, vp])
-    sig("tdist_moe_reduce_rs", [P(SymmCtx), i32, vp, vp, vp, vp, vp, i32, i32, i32, vp, vp, vp, i32, vp])
+    sig("tdist_moe_reduce_rs", [P(SymmCtx), i32, vp, vp, sz, vp, vp, vp, i32, i32, i32, vp, vp, vp, i32, vp])
     sig("tdist_a2a", [P(SymmCtx), vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp])
     sig("tdist_ep_counts", [P(SymmCtx), vp, i32, i32, vp, vp, vp, vp, vp])
     sig("tdist_ep_dispatch", [P(SymmCtx), i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp,

@@ -66,6 +66,10 @@ def ag_group_gemm(x: torch.Tensor, w: torch.Tensor, topk_ids: torch.Tensor, ctx:
     W, r = ctx.num_ranks, ctx.rank
     m_loc = x.shape[0]
     assert m_loc * W <= ctx.max_ntokens and m_loc == ctx.max_ntokens // W, "token count must match the context (max_ntokens / W per rank)"
+    if W > 1 and x.is_cuda:
+        # symm_ag / symm_ids are single-buffered: no rank may push call N+1 into them while a slower rank still sorts or
+        # gathers from call N (the reference opens the op the same way: barrier, copy, barrier — :44-81)
+        _symm.get_heap().barrier_all()
     ctx.symm_ag[r].copy_(x)
     ctx.symm_ids[r, :m_loc * ctx.topk].copy_(topk_ids.to(torch.int32).reshape(-1))
     if W > 1:

@@ -91,11 +91,12 @@ def _launch(ctx: FastAllGatherContext, symm_buffer: torch.Tensor, mode: int) -> 
     ctx.signal_target += 1
     if mode in (AG_LL, AG_LL_MC):
         assert nbytes * 2 <= ctx.max_buffer_size, f"LL all-gather payload {nbytes} B exceeds max_buffer_size/2"
-        # packets: [2 parity][W][shard/8] x 16 B  -> parity stride must equal W*shard*2 bytes inside ll_buffer
+        # packets: two parity halves of ll_buffer, each [W][shard/8] x 16 B; the halves are half the buffer apart
+        # whatever the size of this call (a fast rank's next call must not land on packets a slow rank still reads)
         rc = _lib.lib().tdist_allgather(ctypes.byref(heap.ctx), mode, mine, ctx.ll_buffer.data_ptr(), base, shard,
-                                        st.flags_ptr, st.phase_ptr, st.done_ptr, ctx.max_ctas, _lib.stream_ptr())
+                                        ctx.ll_buffer.numel() * ctx.ll_buffer.element_size(), st.flags_ptr, st.phase_ptr, st.done_ptr, ctx.max_ctas, _lib.stream_ptr())
     else:
-        rc = _lib.lib().tdist_allgather(ctypes.byref(heap.ctx), mode, mine, base, None, shard, st.flags_ptr, st.phase_ptr,
+        rc = _lib.lib().tdist_allgather(ctypes.byref(heap.ctx), mode, mine, base, None, shard, 0, st.flags_ptr, st.phase_ptr,
                                         st.done_ptr, ctx.max_ctas, _lib.stream_ptr())
     _lib.check(rc, "fast_allgather")
     return symm_buffer

@@ -75,7 +75,8 @@ def run_moe_reduce_rs(h_sorted: torch.Tensor, w: torch.Tensor, sort: MoESortResu
     heap = _symm.get_heap()
     st = ctx.state
     _lib.check(_lib.lib().tdist_moe_reduce_rs(ctypes.byref(heap.ctx), _lib.dtype_code(y.dtype), y.data_ptr(),
-                                              ctx.scatter_buf.data_ptr(), out.data_ptr(), sort.pair_to_row.data_ptr(),
+                                              ctx.scatter_buf.data_ptr(), ctx.scatter_buf.numel() * ctx.scatter_buf.element_size(),
+                                              out.data_ptr(), sort.pair_to_row.data_ptr(),
                                               wts.data_ptr(), tokens, sort.topk, y.shape[1] * y.element_size(), st.flags_ptr,
                                               st.phase_ptr, st.done_ptr, 64, _lib.stream_ptr()), "moe_reduce_rs")
     return out

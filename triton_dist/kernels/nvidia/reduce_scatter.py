@@ -119,7 +119,8 @@ def reduce_scatter_2d_op(input: torch.Tensor, ctx: ReduceScatter2DContext, outpu
     heap = _symm.get_heap()
     st = ctx.state
     _lib.check(_lib.lib().tdist_reduce_scatter(ctypes.byref(heap.ctx), _lib.dtype_code(inp.dtype), inp.data_ptr(),
-                                               ctx.scatter_buf.data_ptr(), output.data_ptr(), seg_bytes, st.flags_ptr,
+                                               ctx.scatter_buf.data_ptr(), ctx.scatter_buf.numel() * ctx.scatter_buf.element_size(),
+                                               output.data_ptr(), seg_bytes, st.flags_ptr,
                                                st.phase_ptr, st.done_ptr, ctx.num_reduction_sms, _lib.stream_ptr()),
                "reduce_scatter")
     return output

@@ -82,6 +82,28 @@ def check_close(x: torch.Tensor, ref_fp32: torch.Tensor, dtype, what: str = "") 
     return bad == 0
 
 
+def logits_close(lg: torch.Tensor, ref: torch.Tensor, dtype, what: str = "") -> bool:
+    """Model-level check against a reference implementation's logits [rows, vocab]. Probabilities of a random-init model
+    are all ~1/vocab, so comparing softmax outputs with an absolute tolerance can hardly fail; instead
+      * every logit must agree within a tolerance that is a fraction of the SPREAD of the reference logits of its row
+        (10 % for 16-bit runs: activations are rounded to 16 bit in every layer; 0.2 % in fp32), and
+      * the greedy token must be the same wherever the reference's top-1 leads its runner-up by more than that tolerance.
+    A wrong weight shard, a missing all-reduce or a stale KV row moves logits by about one spread and fails both."""
+    lg, ref = lg.float(), ref.float()
+    spread = ref.std(dim=-1, keepdim=True).clamp_min(1e-6)
+    tol = (0.10 if dtype in (torch.bfloat16, torch.float16) else 2e-3) * spread
+    err = (lg - ref).abs()
+    ok_val = bool((err <= tol).all())
+    top2 = ref.topk(2, dim=-1).values
+    decided = (top2[:, 0] - top2[:, 1]) > 2 * tol[:, 0]
+    ok_top = bool((lg.argmax(-1)[decided] == ref.argmax(-1)[decided]).all())
+    if not (ok_val and ok_top):
+        dist_print(f"{what}: max |logit err| / spread = {float((err / spread).max()):.4g} (limit {float((tol / spread).max()):.3g}), "
+                   f"top-1 agreement on decided rows: {ok_top} ({int(decided.sum())}/{decided.numel()} rows decided)",
+                   allowed_ranks="all", prefix=True)
+    return ok_val and ok_top
+
+
 def skew(enabled: bool) -> None:
     """Race/hang provocation: delay this rank by a random amount (reference allgather.py:74-78)."""
     if enabled and torch.cuda.is_available():

@@ -38,6 +38,7 @@ def cases(suite: str, world: int):
         (T + "test_tp_e2e", ["--model", "qwen3", "--check"]),
         (T + "test_tp_e2e", ["--model", "llama", "--check"]),
         (T + "test_tp_e2e", ["--model", "qwen3_moe", "--check"]),
+        (T + "test_tp_e2e", ["--model", "qwen3", "--check", "--corrupt", "--modes", "torch,triton_dist_AR"]),
         (M + "test_qwen3", []),
         (M + "test_qwen3", ["--unfused"]),
     ]

@@ -23,15 +23,18 @@ if __name__ == "__main__":
         line = f"{nbytes:>7d} B/rank:"
         for mode in modes:
             buf = symm_tensor((world, n), torch.int32)
+            get_heap().barrier_all()  # every rank has zero-filled its new buffer before anybody pushes into it
             good = True
             for it in range(args.verify_iters):
                 buf.zero_()
                 buf[rank].fill_(rank * 1000 + it + 1)
+                get_heap().barrier_all()  # a faster peer must not push into `buf` before the zero fill above has run
                 fast_allgather(buf, ctx, mode=mode)
                 if dev == "cuda":
                     torch.cuda.synchronize()
                 exp = (torch.arange(world, device=buf.device, dtype=torch.int32) * 1000 + it + 1)[:, None].expand(world, n)
                 good = good and bool(torch.equal(buf, exp))
+                get_heap().barrier_all()  # all ranks have checked before the next iteration wipes the buffer
             ok = all_ok(good) and ok
             if dev == "cuda" and not args.check:
                 _, t = perf_func_max_over_ranks(lambda: fast_allgather(buf, ctx, mode=mode), args.iters, args.warmup, use_graph=True)

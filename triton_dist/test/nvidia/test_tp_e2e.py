@@ -8,7 +8,7 @@ import torch
 import torch.distributed as dist
 
 from triton_dist.models import DenseLLM, KV_Cache, ModelConfig, Qwen3MoE
-from triton_dist.test.common import all_ok, finish, setup
+from triton_dist.test.common import all_ok, finish, logits_close, setup
 from triton_dist.utils import dist_print
 
 
@@ -41,6 +41,9 @@ if __name__ == "__main__":
     ap.add_argument("--decode-steps", type=int, default=3)
     ap.add_argument("--modes", default="torch,triton_dist_AR,triton_dist_gemm_ar,triton_dist")
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--corrupt", action="store_true",
+                    help="self-test of the comparison: 1 %% of the LM-head rows are swapped, the run passes only if every mode is "
+                         "reported as a MISMATCH")
     args = ap.parse_args()
     group, rank, world = setup()
     dev = "cuda" if torch.cuda.is_available() else "cpu"
@@ -51,12 +54,17 @@ if __name__ == "__main__":
     cls = Qwen3MoE if args.model == "qwen3_moe" else DenseLLM
     model = cls(cfg, group, hf_model=hf)
     hf = hf.to(dev)
+    if args.corrupt:  # a small, structured fault: ten vocabulary rows of the LM head exchanged with their neighbours
+        model.lm_head = model.lm_head.clone()  # on CPU the model's LM head aliases the HF module's weight
+        rows = torch.arange(0, 1000, 100, device=model.lm_head.device)
+        tmp = model.lm_head[rows].clone()
+        model.lm_head[rows] = model.lm_head[rows + 1]
+        model.lm_head[rows + 1] = tmp
     bsz = (args.bsz + world - 1) // world * world
     torch.manual_seed(7)
     ids = torch.randint(0, 1024, (bsz, args.seq), device=dev)
     with torch.inference_mode():
         ref_all = hf(ids).logits.float()  # teacher forcing: logits at every position
-    tol = 3e-2 if dtype == torch.bfloat16 else 2e-4
     ok = True
     for mode in args.modes.split(","):
         if mode == "triton_dist" and args.model == "qwen3_moe" and world == 1 and dev == "cpu":
@@ -68,7 +76,7 @@ if __name__ == "__main__":
         model.set_fwd("torch")
         pos = torch.arange(n_pre, device=dev)[None, :].expand(bsz, -1)
         logits = model.inference(ids[:, :n_pre], pos, kv)
-        good = torch.allclose(torch.softmax(logits[:, -1], -1), torch.softmax(ref_all[:, n_pre - 1], -1), atol=tol, rtol=tol)
+        good = logits_close(logits[:, -1], ref_all[:, n_pre - 1], dtype, f"mode {mode} prefill")
         kv.kv_offset.fill_(n_pre)
         if mode == "triton_dist":
             model.set_fwd("triton_dist")
@@ -89,14 +97,13 @@ if __name__ == "__main__":
             ref = ref_all[:, p]
             if mode == "triton_dist":
                 ref = ref.split(bsz // world, dim=0)[rank]
-            step_ok = torch.allclose(torch.softmax(lg, -1), torch.softmax(ref, -1), atol=tol, rtol=tol)
-            if not step_ok:
-                err = (torch.softmax(lg, -1) - torch.softmax(ref, -1)).abs().max().item()
-                dist_print(f"mode {mode} decode step {step}: softmax max err {err:.4g}", allowed_ranks="all", prefix=True)
+            step_ok = logits_close(lg, ref, dtype, f"mode {mode} decode step {step}")
             good = good and step_ok
             kv.inc_offset()
         model.finalize()
         good = all_ok(good)
         dist_print(f"[{args.model}] mode {mode:22s}: {'ok' if good else 'MISMATCH'}")
-        ok = ok and good
+        ok = ok and (good if not args.corrupt else not good)
+    if args.corrupt:
+        dist_print("corrupted LM head detected by every mode" if ok else "a corrupted LM head went UNNOTICED")
     finish(ok)

@@ -24,6 +24,24 @@ __device__ __forceinline__ void cta_barrier_all(const SymmCtx& c, uint32_t* flag
   barrier_all_block(c, flags + blockIdx.x * TDIST_MAX_RANKS, phase);
 }
 
+// Bulk loops keep kIlp independent 16-byte loads per thread in flight before the first store: a single load per
+// thread and iteration left the large-message kernels latency-bound (64 MB reduce-scatter 214 us vs NCCL 139 us; the
+// link probe reaches the NVLS rate with 8 loads in flight on 148 CTAs, profiles/README.md).
+constexpr int kIlp = 8;
+template <typename LoadF, typename StoreF>
+__device__ __forceinline__ void bulk_loop(size_t beg, size_t end, LoadF load, StoreF store) {
+  const size_t stride = blockDim.x;
+  size_t i = beg + threadIdx.x;
+  for (; i + (kIlp - 1) * stride < end; i += kIlp * stride) {
+    int4 v[kIlp];
+#pragma unroll
+    for (int u = 0; u < kIlp; ++u) v[u] = load(i + u * stride);
+#pragma unroll
+    for (int u = 0; u < kIlp; ++u) store(i + u * stride, v[u]);
+  }
+  for (; i < end; i += stride) store(i, load(i));
+}
+
 // ------------------------------------------------------------------ barrier
 __global__ void barrier_all_kernel(SymmCtx c, uint32_t* flags, PhaseState ps) {
   const uint32_t base = phase_begin(ps);
@@ -117,10 +135,10 @@ __global__ void __launch_bounds__(512) ar_one_shot_mc_kernel(SymmCtx c, const in
   const size_t beg = blockIdx.x * per_cta;
   const size_t end = min(beg + per_cta, n_vec);
   if (!in_place)
-    for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) ptx::st_v4(buf + i, ptx::ld_nc_v4(in + i));
+    bulk_loop(beg, end, [&](size_t i) { return ptx::ld_nc_v4(in + i); }, [&](size_t i, const int4& v) { ptx::st_v4(buf + i, v); });
   cta_barrier_all(c, flags, phase);
   const int4* mc = mc_ptr(c, buf);
-  for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) out[i] = Pack<Tag>::mc_ld_reduce(mc + i);
+  bulk_loop(beg, end, [&](size_t i) { return Pack<Tag>::mc_ld_reduce(mc + i); }, [&](size_t i, const int4& v) { out[i] = v; });
   if (in_place) cta_barrier_all(c, flags, phase + 1);  // nobody may overwrite symm before all ranks read it
   phase_end(ps, base, 2);
 }
@@ -141,16 +159,17 @@ __global__ void __launch_bounds__(512) ar_two_shot_mc_kernel(SymmCtx c, const in
   const size_t len = end > beg ? end - beg : 0;
   const size_t per_rank = (len + W - 1) / W;
   if (!in_place)
-    for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) ptx::st_v4(buf + i, ptx::ld_nc_v4(in + i));
+    bulk_loop(beg, end, [&](size_t i) { return ptx::ld_nc_v4(in + i); }, [&](size_t i, const int4& v) { ptx::st_v4(buf + i, v); });
   cta_barrier_all(c, flags, base + 1);
   {
     int4* mc = mc_ptr(c, buf);
     const size_t sb = min(beg + c.rank * per_rank, end), se = min(sb + per_rank, end);
-    for (size_t i = sb + threadIdx.x; i < se; i += blockDim.x) ptx::multimem_st_v4(mc + i, Pack<Tag>::mc_ld_reduce(mc + i));
+    bulk_loop(sb, se, [&](size_t i) { return Pack<Tag>::mc_ld_reduce(mc + i); },
+              [&](size_t i, const int4& v) { ptx::multimem_st_v4(mc + i, v); });
   }
   cta_barrier_all(c, flags, base + 2);
   if (out != buf)
-    for (size_t i = beg + threadIdx.x; i < end; i += blockDim.x) out[i] = ptx::ld_v4(buf + i);
+    bulk_loop(beg, end, [&](size_t i) { return ptx::ld_v4(buf + i); }, [&](size_t i, const int4& v) { out[i] = v; });
   phase_end(ps, base, 2);
 }
 
@@ -265,6 +284,31 @@ __global__ void __launch_bounds__(512) reduce_scatter_kernel(SymmCtx c, const in
     for (int p = 1; p < W; ++p) Pack<Tag>::add(acc, ptx::ld_v4(buf + ((c.rank + p) % W) * seg_vecs + i));
     out[i] = Pack<Tag>::cvt(acc);
   }
+  phase_end(ps, base, 2);
+}
+
+// NVLS reduce-scatter: every rank copies its W segments into the symmetric buffer (same layout everywhere), CTA b of
+// all ranks meet, then each rank sums ITS segment across ranks in the switch. 1/W of the data enters each GPU instead
+// of (W-1)/W, and nothing is reduced on the SMs.
+template <typename Tag>
+__global__ void __launch_bounds__(512) reduce_scatter_mc_kernel(SymmCtx c, const int4* __restrict__ in, int4* scat,
+                                                                int4* out, size_t seg_vecs, size_t parity_vecs,
+                                                                uint32_t* flags, PhaseState ps) {
+  const uint32_t base = phase_begin(ps);
+  const int W = c.world;
+  int4* buf = scat + ((base >> 1) & 1) * parity_vecs;
+  const size_t per_cta = (seg_vecs + gridDim.x - 1) / gridDim.x;
+  const size_t beg = blockIdx.x * per_cta;
+  const size_t end = min(beg + per_cta, seg_vecs);
+#pragma unroll 1
+  for (int s = 0; s < W; ++s) {
+    const int4* src = in + s * seg_vecs;
+    int4* dst = buf + s * seg_vecs;
+    bulk_loop(beg, end, [&](size_t i) { return ptx::ld_nc_v4(src + i); }, [&](size_t i, const int4& v) { ptx::st_v4(dst + i, v); });
+  }
+  cta_barrier_all(c, flags, base + 1);
+  const int4* mc = mc_ptr(c, buf) + c.rank * seg_vecs;
+  bulk_loop(beg, end, [&](size_t i) { return Pack<Tag>::mc_ld_reduce(mc + i); }, [&](size_t i, const int4& v) { out[i] = v; });
   phase_end(ps, base, 2);
 }
 
@@ -446,11 +490,19 @@ int tdist_reduce_scatter(const tdist_symm_ctx* ctx, int dtype, const void* in, v
     return -1;
   }
   if (max_ctas > TDIST_MAX_CTAS) max_ctas = TDIST_MAX_CTAS;
+  // NVLS from 1 MB per segment (below, the barrier + copy-in costs more than the one-hop scatter saves)
+  const bool nvls = c.mc_base != nullptr && c.world > 1 && seg_bytes >= (512u << 10) && getenv("TDIST_RS_NO_NVLS") == nullptr;
+  if (nvls && max_ctas < 64) max_ctas = TDIST_MAX_CTAS < 148 ? TDIST_MAX_CTAS : 148;  // the pull needs the whole GPU's loads in flight
   int grid = pick_grid(n, max_ctas, 512);
   TDIST_DISPATCH_DTYPE(dtype, {
-    reduce_scatter_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
-        c, static_cast<const int4*>(in), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), n, parity_vecs, flags,
-        PhaseState{phase, done});
+    if (nvls)
+      reduce_scatter_mc_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+          c, static_cast<const int4*>(in), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), n, parity_vecs, flags,
+          PhaseState{phase, done});
+    else
+      reduce_scatter_kernel<Tag><<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+          c, static_cast<const int4*>(in), static_cast<int4*>(scatter_ws), static_cast<int4*>(out), n, parity_vecs, flags,
+          PhaseState{phase, done});
   });
   return check_launch("reduce_scatter");
 }

@@ -481,8 +481,15 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
       set_error("gemm_ar: workspace too small (need 2 * M * ldc elements)");
       return -1;
     }
-    if (comm < 0) comm = 8;
-    if (comm < 1) comm = 1;
+    // no SM is reserved: warps 2 / 3 of every GEMM CTA reduce / publish (f->num_comm_ctas is accepted and ignored)
+    comm = 0;
+    p.rs_unit_rows = env_int("TDIST_RS_UNIT_ROWS", 16);
+    if (p.rs_unit_rows != 8 && p.rs_unit_rows != 16 && p.rs_unit_rows != 32) p.rs_unit_rows = 16;
+    if (f->flags2 == nullptr) {
+      set_error("gemm_ar: flags2 (>= 64 symmetric words) is required");
+      return -1;
+    }
+    p.counters = f->flags2 + 32;  // a local word behind the W closing flags
     if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
     tiles_m = (a->M + kBlockM - 1) / kBlockM;
   } else {
@@ -502,6 +509,11 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     return cm < p.ag_slices ? p.ag_slices : cm;
   };
   auto check_rs_flags = [&](int bn) {
+    if (f->mode == TDIST_GEMM_AR && f->flags_words > 0 &&
+        f->flags_words < size_t(W) * ((a->M + kBlockM - 1) / kBlockM) * ((a->N + bn - 1) / bn)) {
+      set_error("gemm_ar: flag area too small (need W * ceil(M/128) * ceil(N/BLOCK_N) words)");
+      return -1;
+    }
     if (f->mode != TDIST_GEMM_RS || p.variant != VARIANT_NVLS || f->flags_words == 0) return 0;
     const size_t need = size_t(W) * ((p.rows_per_rank + kBlockM - 1) / kBlockM) * ((a->N + bn - 1) / bn);
     if (f->flags_words >= need) return 0;

@@ -438,57 +438,60 @@ __device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epo
   }
 }
 
-// AR consumer (comm CTAs): for each tile in production order wait until every
-// rank has published it, then reduce it across ranks into `out`.
-// flags (AR): [tiles] on each rank, value = epoch when the tile is stored.
+// AR consumer: run by warp 2 of every GEMM CTA (no SM is reserved for communication). Tiles go to a symmetric buffer;
+// warp 3 of the producing CTA flags them (GPU-scope fence + plain system store, see the RS publisher). A unit is
+// rs_unit_rows rows of one tile, dealt round-robin to the reducer warps of the grid in production order.
+//   one-shot (decode sizes): every rank sums every tile itself (flags are broadcast to all ranks);
+//   two-shot (prefill sizes): rank r sums the tiles t with t % W == r and broadcasts the result with multimem.st; a
+//   closing exchange of one "all my tiles are out" word per rank makes `out` complete on every rank at kernel end.
+// flags (AR): [W src][tiles] on each rank; flags2: [W] closing words.
 template <typename Tag, int BLOCK_N>
-__device__ __forceinline__ void ar_consume_body(const GemmParams& p, uint32_t epoch, int comm_idx, int num_comm,
-                                                int tiles_m, int tiles_n) {
+__device__ __forceinline__ void ar_reduce_body(const GemmParams& p, uint32_t epoch, int cw, int ncw, int tiles_m, int tiles_n) {
   const int W = p.ctx.world;
+  const int lane = threadIdx.x & 31;
   const int tiles = tiles_m * tiles_n;
-  constexpr int vec_per_row = BLOCK_N / 8;
   const int parity = (epoch >> 1) & 1;
+  const int unit_rows = p.rs_unit_rows;
+  const int kSub = kBlockM / unit_rows;
   char* sym_c = static_cast<char*>(p.c) + size_t(parity) * p.ws_parity_bytes;
   char* out = static_cast<char*>(p.out);
-  for (int t = comm_idx; t < tiles; t += num_comm) {
-    if (!p.ar_one_shot && (t % W) != p.ctx.rank) continue;
+  const int owned = p.ar_one_shot ? tiles : (tiles - p.ctx.rank + W - 1) / W;
+  const int units = owned * kSub;
+  constexpr int kBatch = 8;
+  for (int u = cw; u < units; u += ncw) {
+    const int k = u / kSub, sc = u - k * kSub;
+    const int t = p.ar_one_shot ? k : p.ctx.rank + k * W;
     const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
-    if (threadIdx.x < W) wait_ge_sys(symm_at(p.ctx, p.flags + t, threadIdx.x), epoch);
-    __syncthreads();
-    const int rows = min(kBlockM, p.M - tc.row0);
-    const int cols_v = min(vec_per_row, (p.N - tc.n_blk * BLOCK_N) / 8);
-    // kArBatch independent multimem loads per thread are issued before the first one is used: the NVLS round trip is
-    // ~2-3 us, one load in flight per thread left a 64 KB tile at ~20 us (measured at M = 2048: the whole op was 10x
-    // slower than cuBLAS + NCCL)
-    constexpr int kArBatch = 8;
-    for (int i0 = threadIdx.x; i0 < rows * vec_per_row; i0 += blockDim.x * kArBatch) {
-      size_t off[kArBatch];
-      bool on[kArBatch];
-      int4 v[kArBatch];
+    const int r0 = tc.row0 + sc * unit_rows;
+    if (r0 >= p.M) continue;
+    if (lane < W) wait_ge_sys_poll_relaxed(p.flags + size_t(lane) * tiles + t, epoch);
+    __syncwarp();
+    const int rows = min(unit_rows, p.M - r0);
+    const int col0 = tc.n_blk * BLOCK_N;
+    const int vpr = min(BLOCK_N, p.N - col0) / 8;
+    const int n_vec = rows * vpr;
+    for (int i0 = lane; i0 < n_vec; i0 += 32 * kBatch) {
+      int4 v[kBatch];
+      size_t off[kBatch];
 #pragma unroll
-      for (int b = 0; b < kArBatch; ++b) {
-        const int idx = i0 + b * blockDim.x;
-        const int r = idx / vec_per_row, cv = idx % vec_per_row;
-        on[b] = idx < rows * vec_per_row && cv < cols_v;
-        off[b] = (size_t(tc.row0 + r) * p.ldc + size_t(tc.n_blk) * BLOCK_N) * 2 + size_t(cv) * 16;
-      }
-      if (p.use_mc) {
-#pragma unroll
-        for (int b = 0; b < kArBatch; ++b)
-          if (on[b]) v[b] = Pack<Tag>::mc_ld_reduce(mc_ptr(p.ctx, sym_c) + off[b]);
-      } else {
-#pragma unroll
-        for (int b = 0; b < kArBatch; ++b) {
-          if (!on[b]) continue;
-          float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int b = 0; b < kBatch; ++b) {
+        const int i = i0 + b * 32;
+        if (i < n_vec) {
+          const int r = i / vpr, cv = i - r * vpr;
+          off[b] = (size_t(r0 + r) * p.ldc + col0) * 2 + size_t(cv) * 16;
+          if (p.use_mc) {
+            v[b] = Pack<Tag>::mc_ld_reduce(mc_ptr(p.ctx, sym_c) + off[b]);
+          } else {
+            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll 1
-          for (int s2 = 0; s2 < W; ++s2) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, sym_c, (p.ctx.rank + s2) % W) + off[b]));
-          v[b] = Pack<Tag>::cvt(acc);
+            for (int s2 = 0; s2 < W; ++s2) Pack<Tag>::add(acc, ptx::ld_v4(symm_at(p.ctx, sym_c, (p.ctx.rank + s2) % W) + off[b]));
+            v[b] = Pack<Tag>::cvt(acc);
+          }
         }
       }
 #pragma unroll
-      for (int b = 0; b < kArBatch; ++b) {
-        if (!on[b]) continue;
+      for (int b = 0; b < kBatch; ++b) {
+        if (i0 + b * 32 >= n_vec) continue;
         if (p.ar_one_shot) {
           *reinterpret_cast<int4*>(out + off[b]) = v[b];
         } else if (p.use_mc) {
@@ -499,15 +502,21 @@ __device__ __forceinline__ void ar_consume_body(const GemmParams& p, uint32_t ep
         }
       }
     }
-    __syncthreads();
-    if (!p.ar_one_shot && threadIdx.x < W) {
-      ptx::fence_acq_rel_sys();
-      notify(p.ctx, p.flags2 + t, threadIdx.x, epoch);
-    }
   }
   if (!p.ar_one_shot) {
-    // every reduced tile must have landed in my `out` before the kernel may finish
-    for (int t = comm_idx * blockDim.x + threadIdx.x; t < tiles; t += num_comm * blockDim.x) wait_ge_sys(p.flags2 + t, epoch);
+    // closing exchange: the last reducer warp of this rank to finish tells every rank that all my tiles are out
+    __syncwarp();
+    if (lane == 0) {
+      ptx::fence_acq_rel_sys();
+      if (ptx::atom_add_acq_rel_gpu(p.counters, 1) == static_cast<uint32_t>(ncw - 1)) {
+        *p.counters = 0;
+        ptx::fence_acq_rel_sys();
+        for (int s2 = 0; s2 < W; ++s2) ptx::st_relaxed_sys(symm_at(p.ctx, p.flags2 + p.ctx.rank, (p.ctx.rank + s2) % W), epoch);
+      }
+    }
+    __syncwarp();
+    if (lane < W) wait_ge_sys_poll_relaxed(p.flags2 + lane, epoch);
+    __syncwarp();
   }
 }
 
@@ -540,11 +549,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
         ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
       else
         ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
-    } else if (p.mode == GEMM_AR) {
-      if (p.is_bf16)
-        ar_consume_body<BF16, BLOCK_N>(p, epoch, blockIdx.x, p.num_comm_ctas, tiles_m, tiles_n);
-      else
-        ar_consume_body<F16, BLOCK_N>(p, epoch, blockIdx.x, p.num_comm_ctas, tiles_m, tiles_n);
     }
   } else {
     // ------------------------------------------------------------ GEMM CTA
@@ -789,7 +793,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             }
           }
         }
-        if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
+        if ((p.mode == GEMM_RS && p.variant == VARIANT_NVLS) || p.mode == GEMM_AR) {
           // The partial tile is in local memory. Telling the owner needs a system-scope fence, and that fence also
           // waits for whatever else this SM has in flight (measured: 24 us of the 8-rank op when the epilogue issued
           // it while the reducer warp's NVLS loads were outstanding). So the epilogue only counts the tile; warp 3
@@ -799,7 +803,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             __threadfence_block();
             atomicAdd(stored_count, 1u);
           }
-        } else if (p.mode == GEMM_RS || p.mode == GEMM_AR) {
+        } else if (p.mode == GEMM_RS) {
           // all 4 epilogue warps have issued their stores; remember the tile, publish it one tile later
           asm volatile("bar.sync 1, 128;" ::: "memory");
           pend_t = t;
@@ -843,6 +847,35 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           rs_pull_body<BF16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_n, false);
         else
           rs_pull_body<F16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_n, false);
+      }
+    }
+    else if (p.mode == GEMM_AR) {
+      if (warp == 3) {
+        // ====================================================== warp 3: publishes this CTA's finished tiles
+        if (lane == 0) {
+          uint32_t k = 0;
+          const int W = p.ctx.world;
+          for (int t = gemm_cta; t < tiles; t += num_gemm, ++k) {
+            while (*reinterpret_cast<volatile uint32_t*>(stored_count) <= k) {
+            }
+            __threadfence_block();
+            ptx::fence_acq_rel_gpu();  // the tile is in this GPU's memory: see the RS publisher
+            uint32_t* flag = p.flags + size_t(p.ctx.rank) * tiles + t;
+            if (!p.ar_one_shot) {
+              ptx::st_relaxed_sys(symm_at(p.ctx, flag, t % W), epoch);
+            } else if (p.use_mc) {
+              ptx::multimem_st_b32(mc_ptr(p.ctx, flag), epoch);
+            } else {
+              for (int s2 = 0; s2 < W; ++s2) ptx::st_relaxed_sys(symm_at(p.ctx, flag, (p.ctx.rank + s2) % W), epoch);
+            }
+          }
+        }
+      } else {
+        // ====================================================== warp 2: cross-rank reducer
+        if (p.is_bf16)
+          ar_reduce_body<BF16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_m, tiles_n);
+        else
+          ar_reduce_body<F16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_m, tiles_n);
       }
     }
     // teardown of the GEMM roles

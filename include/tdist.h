@@ -119,8 +119,8 @@ typedef struct tdist_fused_args {
   int mode;
   void* ws;           /* AG: symm gather workspace [2][M][K]; RS: symm scatter [2][W][M/W][N]; AR: symm tiles [2][M][ldc] */
   void* out;          /* RS: [M/W, N]; AR: [M, ldc] (symmetric when !ar_one_shot) */
-  uint32_t* flags;    /* symmetric, zero initialised, >= W*ceil(M/W/128) (AG/RS) or #tiles (AR) entries */
-  uint32_t* flags2;   /* AR two-shot only: symmetric, #tiles entries */
+  uint32_t* flags;    /* symmetric, zero initialised, >= W*ceil(M/W/128) (AG/RS point-to-point) or W * #tiles (AR) entries */
+  uint32_t* flags2;   /* AR: symmetric, zero initialised, >= 64 words (closing flags + a local counter) */
   uint32_t* counters; /* RS: local, zero initialised, W*ceil(M/W/128) entries */
   uint32_t* phase;    /* device counter pair, zero initialised */
   uint32_t* done;

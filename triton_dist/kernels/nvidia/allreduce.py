@@ -133,7 +133,7 @@ def all_reduce(x: torch.Tensor, output: Optional[torch.Tensor] = None, method: A
         method = AllReduceMethod.OneShot if _NATIVE_CODE[method] == 5 else AllReduceMethod.TwoShot
     _run_straggler(ctx, straggler_option)
     if max_sm <= 0:
-        max_sm = 8 if nbytes <= 256 * 1024 else (32 if nbytes <= 8 * 2**20 else 64)
+        max_sm = 8 if nbytes <= 256 * 1024 else (32 if nbytes <= 8 * 2**20 else (64 if nbytes <= 32 * 2**20 else 128))
     if nbytes % 16 != 0:  # pad odd sizes through a scratch copy
         pad = (16 - nbytes % 16) // x.element_size()
         xp = torch.cat([x.reshape(-1), x.new_zeros(pad)])

@@ -16,6 +16,7 @@ context pair — so there is no trailing barrier and the op is graph-capturable.
 from __future__ import annotations
 
 import ctypes
+import os
 import dataclasses
 from typing import List, Optional
 
@@ -51,7 +52,7 @@ class GemmARContext:
             self.symm_gemm_out_buf = heap.alloc((2, self.max_M, self.N), self.dtype, zero=False)
             self.symm_ar_out_buf = heap.alloc((self.max_M, self.N), self.dtype, zero=False)
             n_tiles = ((self.max_M + 127) // 128) * ((self.N + _MIN_BN - 1) // _MIN_BN)
-            self.state = CollectiveState(n_tiles + 64)
+            self.state = CollectiveState(self.world_size * n_tiles + 64)  # one flag per (source rank, tile)
             self.flags2 = heap.alloc((n_tiles + 64,), torch.int32)
             self.use_mc = bool(heap.multicast)
             self.gemv_state = CollectiveState(16 * _lib.MAX_RANKS)  # decode path: GEMV + in-place NVLS all-reduce
@@ -123,7 +124,7 @@ def _launch(ctx: GemmARContext, a: torch.Tensor, b: torch.Tensor, one_shot: bool
     if not ctx.native:
         return torch_gemm_ar(a, b)
     heap = _symm.get_heap()
-    if M <= 16 and one_shot and ctx.use_mc and K % 8 == 0:
+    if M <= 16 and one_shot and ctx.use_mc and K % 8 == 0 and os.environ.get("TDIST_GEMM_AR_DECODE", "fused") == "gemv":
         # decode: the tensor core would idle at <= 16 rows. Weight-streaming GEMV straight into the symmetric buffer,
         # then the NVLS one-shot all-reduce in place (multimem.ld_reduce; no staging copy).
         from .elementwise import gemv
@@ -142,12 +143,14 @@ def _launch(ctx: GemmARContext, a: torch.Tensor, b: torch.Tensor, one_shot: bool
         out = ctx.symm_ar_out_buf[:M]
     # tiles are laid out with row stride N in the symmetric buffer; its two parity halves are max_M * N apart
     sym_c = ctx.symm_gemm_out_buf
+    if block_n == 0 and M <= 16:
+        block_n = int(os.environ.get("TDIST_GEMM_AR_DECODE_BN", 0))  # sweep knob for the decode-size tile width
     args = _gemm_args(a, b, sym_c[0], M, N, K, block_n=block_n, group_m=8)
     st = ctx.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=3, ws=sym_c.data_ptr(), out=out.data_ptr(), flags=st.flags_ptr,
                        flags2=ctx.flags2.data_ptr(), counters=None, phase=st.phase_ptr, done=st.done_ptr,
                        num_comm_ctas=ctx.NUM_COMM_SMS, ar_one_shot=int(one_shot), use_mc=int(ctx.use_mc), variant=0,
-                       ws_bytes=sym_c.numel() * sym_c.element_size(), flags_words=0)
+                       ws_bytes=sym_c.numel() * sym_c.element_size(), flags_words=st.flags.numel())
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "gemm_ar")
     if not one_shot and copy_to_local:
         return out.clone()

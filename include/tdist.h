@@ -113,6 +113,15 @@ typedef struct tdist_gemm_args {
 /* C = A * B^T (kernels/nvidia/allgather_gemm.py:656-720 gemm_persistent) */
 int tdist_gemm(const tdist_gemm_args* a, void* stream);
 
+/* Block-scaled fp8 GEMM (csrc/kernels/gemm_fp8_sm100.cuh; the reference has no fp8 GEMM — fp8 appears there only as the
+ * all-to-all payload, tutorials/04-deepseek-infer-all2all.py:334-427): C[M,N] (bf16/fp16) = dequant(A8) * dequant(B8)^T with
+ * A8 [M,K] / B8 [N,K] e4m3 K-major, sa [M][sa_ld] one fp32 scale per row and 128-wide K block, sb [E][ceil(N/128)][ceil(K/128)]
+ * one per 128 x 128 weight block. Grouped (MoE) form: block_expert[i] = expert of 128-row block i of A8 (negative: padding
+ * block, skipped), B8 = [num_experts * N, K]. lda / ldb in bytes (= elements), ldc in elements. */
+int tdist_gemm_fp8(const void* a8, const float* sa, long long sa_ld, const void* b8, const float* sb, void* c, int M, int N,
+                   int K, long long lda, long long ldb, long long ldc, int out_dtype, const int* block_expert, int num_experts,
+                   int num_sms, void* stream);
+
 enum { TDIST_GEMM_AG = 1, TDIST_GEMM_RS = 2, TDIST_GEMM_AR = 3 };
 typedef struct tdist_fused_args {
   tdist_symm_ctx ctx;

@@ -142,6 +142,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_signal_set", [vp, u32, i32, vp])
     sig("tdist_signal_wait", [vp, u32, i32, vp])
     f32, ll = ctypes.c_float, ctypes.c_longlong
+    sig("tdist_gemm_fp8", [vp, vp, ll, vp, vp, vp, i32, i32, i32, ll, ll, ll, i32, vp, i32, i32, vp])
     sig("tdist_gemv", [i32, vp, vp, vp, vp, i32, i32, i32, ll, ll, ll, vp])
     sig("tdist_rmsnorm", [i32, vp, vp, vp, vp, i32, i32, f32, ll, ll, vp])
     sig("tdist_silu_mul", [i32, vp, vp, ll, i32, vp])

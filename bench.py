@@ -192,9 +192,48 @@ def decode_section(rank: int, world: int, steps: int):
     except Exception as e:  # noqa: BLE001
         out["task_profile"] = f"unavailable: {e}"
     mega.finalize()
+    # same-box comparators: the other three columns of the reference's table (docs/mega_triton_kernel.md:29-33), through
+    # Engine's CUDA-graph decode step on the SAME weights: torch (cuBLAS + NCCL), triton_dist_AR, triton_dist_gemm_ar
+    if os.environ.get("TDIST_BENCH_ENGINE", "1") != "0":
+        out["engine_graph_ms_per_token"] = engine_comparators(dense, cfg, steps)
+        ref_ms = out["engine_graph_ms_per_token"].get("torch")
+        if isinstance(ref_ms, float):
+            out["megakernel_vs_torch_graph"] = round(ref_ms / ms, 3)
     del dense
     torch.cuda.empty_cache()
     return out
+
+
+def engine_comparators(dense, cfg, steps: int) -> dict:
+    import torch
+
+    from triton_dist.models import Engine
+    from triton_dist.utils import perf_func_max_over_ranks
+
+    res = {}
+    ids = torch.randint(0, 32000, (1, 512), device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
+    for backend in ("torch", "triton_dist_AR", "triton_dist_gemm_ar"):
+        try:
+            eng = Engine(cfg, model=dense)
+            eng.backend = backend
+            with torch.inference_mode():
+                eng._init_kv_cache(bsz=1)
+                eng.kv_cache.clear()
+                dense.set_fwd(mode="torch")  # prefill on the torch path, as Engine.serve does
+                dense.inference(input_ids=ids, position_ids=eng.get_ctx(ids), kv_cache=eng.kv_cache)
+                eng.kv_cache.kv_offset.fill_(512)
+                eng.set_backend(backend, 1)
+                run = eng._init_cuda_graph(1)
+                tok = torch.full((1, 1), 1225, dtype=torch.long, device="cuda")
+                pos = torch.full((1, 1), 512, dtype=torch.long, device="cuda")
+                _, ms = perf_func_max_over_ranks(lambda: run(tok, pos), steps, 3)
+            res[backend] = round(ms, 4)
+            eng.kv_cache = None
+        except Exception as e:  # noqa: BLE001 - one comparator failing must not cost the others
+            res[backend] = f"error: {type(e).__name__}: {e}"[:200]
+        torch.cuda.empty_cache()
+    dense.set_fwd(mode="torch")
+    return res
 
 
 def main() -> None:

@@ -1017,8 +1017,15 @@ __global__ void __launch_bounds__(kThreads, 1) megakernel(const __grid_constant_
     __syncthreads();
     if (threadIdx.x == 0) {
       if (t.out_slot >= 0) {
+#ifdef TDIST_MEGA_SC_FENCE
         __threadfence();
         atomicAdd(p.scoreboard + t.out_slot, 1u);
+#else
+        // acq_rel fence + fire-and-forget reduction instead of __threadfence() (a sequentially consistent fence) +
+        // atomicAdd (which waits for the old value): this thread signals hundreds of tasks per token
+        ptx::fence_acq_rel_gpu();
+        ptx::red_add_relaxed_gpu(p.scoreboard + t.out_slot, 1u);
+#endif
       }
       if (tr != nullptr) tr[1] = ptx::globaltimer();
     }

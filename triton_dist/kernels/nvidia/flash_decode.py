@@ -50,7 +50,14 @@ def torch_paged_decode(q, k_cache, v_cache, kv_lens, block_table, scale):
 def _decode(q, k_cache, v_cache, kv_lens, block_table, scale, kv_split, output_split, out16, out_lse):
     B, Hq, D = q.shape
     _, page_size, Hkv, _ = k_cache.shape
-    splits = 32 if kv_split in (-1, None) else int(kv_split)
+    if kv_split in (-1, None):
+        # enough CTAs to keep ~4 per SM in flight (a CTA holds only 16 KB of K/V loads: 32 splits x 8 kv heads left a
+        # 512K-token decode at 2.2 TB/s), but at least 256 positions per split; no host read of kv_lens: the cache
+        # capacity bounds the length
+        cap = block_table.shape[1] * page_size
+        splits = max(4, min(256, (6 * 148) // max(1, B * Hkv), max(1, cap // 256)))
+    else:
+        splits = int(kv_split)
     if not (q.is_cuda and q.dtype in (torch.bfloat16, torch.float16) and D == 128):
         o, lse = torch_paged_decode(q, k_cache, v_cache, kv_lens, block_table, scale)
         if out16 is not None:
@@ -103,7 +110,7 @@ def dense_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
         out.copy_(o.to(q.dtype))
         return out
     if kv_split in (-1, None):  # enough CTAs to fill the GPU, at least ~256 positions per split
-        kv_split = max(1, min(64, S // 256, max(1, 296 // max(B * Hkv, 1))))
+        kv_split = max(1, min(256, S // 256, max(1, (6 * 148) // max(B * Hkv, 1))))  # ~6 CTAs per SM (16 KB of loads each)
     partial = torch.empty((B, Hq, kv_split, D + 1), dtype=torch.float32, device=q.device)
     _lib.check(_lib.lib().tdist_flash_decode(
         _lib.dtype_code(q.dtype), q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), kv_lens.data_ptr(), partial.data_ptr(),

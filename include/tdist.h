@@ -243,6 +243,16 @@ int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vo
  *      kernels/nvidia/sp_ag_attention_intra_node.py:186-425) ------------------------------------------------ */
 /* varlen causal GQA flash-attention of this rank's query shard over the all-gathered K/V (global token order).
  * q/out [total_q_local, Hq, 128]; k/v gathered [total_k_global, Hkv, 128]; cu_q local / cu_k global offsets [B+1]. */
+/* The same attention on tcgen05 / TMEM / TMA (csrc/kernels/sp_attn_sm100.cu): 128-row query tiles, S = Q K^T and P V on
+ * tcgen05.mma with TMEM accumulators, K/V tiles by TMA; V is consumed as an MN-major operand from its [keys][d] layout.
+ * total_q / total_k: rows of the q / k / v buffers; q_row_stride / kv_row_stride: elements between consecutive tokens
+ * (>= heads * 128, so views into a fused qkv tensor or a KV cache work). Rows of k/v behind a sequence need not be
+ * initialised. world = 1, rank = 0 gives plain varlen attention whose queries are the LAST rows of each sequence (prefill,
+ * chunked prefill: TP_Attn). */
+int tdist_attn_fwd_tc(const void* q, const void* k, const void* v, void* out, const int* cu_q, const int* cu_k, int B,
+                      int max_q_local, int total_q, int total_k, int Hq, int Hkv, int head_dim, long long q_row_stride,
+                      long long kv_row_stride, int k_batch_stride /* > 0: keys of sequence b start at row b * stride (dense
+                      cache), 0: at cu_k[b] */, int rank, int world, int causal, int zigzag, float sm_scale, void* stream);
 int tdist_sp_attn_fwd(const void* q, const void* k_gathered, const void* v_gathered, void* out, const int* cu_q, const int* cu_k,
                       int B, int max_q_local, int Hq, int Hkv, int head_dim, int rank, int world, int causal, int zigzag,
                       float sm_scale, void* stream);

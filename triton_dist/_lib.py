@@ -163,6 +163,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_ep_dispatch", [P(SymmCtx), i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp,
                               i32, vp])
     sig("tdist_ep_combine", [P(SymmCtx), i32, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
+    sig("tdist_attn_fwd_tc", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, ll, ll, i32, i32, i32, i32, i32, f32, vp])
     sig("tdist_sp_attn_fwd", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp])
     sig("tdist_sp_kv_scatter", [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp])
     sig("tdist_mega_create", [i32, i32, i32, P(vp)])

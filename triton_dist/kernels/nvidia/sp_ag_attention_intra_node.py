@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import dataclasses
 import math
+import os
 from typing import Optional
 
 import torch
@@ -129,6 +130,31 @@ def _gather_kv(ctx, k_shard, v_shard, cu_k, rank, world, zigzag):
     cur.wait_stream(ctx.ag_stream)
 
 
+def flash_attn_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_q: torch.Tensor, cu_k: torch.Tensor, max_q: int,
+                      causal: bool = True, out: Optional[torch.Tensor] = None, scale: Optional[float] = None, rank: int = 0,
+                      world: int = 1, zigzag: bool = False, k_batch_stride: int = 0) -> torch.Tensor:
+    """Varlen GQA flash attention forward on tcgen05 (csrc/kernels/sp_attn_sm100.cu), head_dim 128, bf16.
+
+    q [total_q, Hq, 128], k / v [total_k, Hkv, 128] (token-major; a view with a larger token stride is fine, e.g. a slice of
+    a fused qkv tensor), cu_q / cu_k int32 [B+1]. With ``world`` > 1, q holds this rank's share of every sequence and the
+    causal mask uses each row's GLOBAL position (plain or zig-zag sharding, as in ``fused_sp_ag_attn_intra_node``); with
+    one rank the queries of a sequence are its last rows (prefill: Lq == L; chunked prefill: Lq < L).
+    ``k_batch_stride`` > 0: k / v are a dense cache flattened to [B * S, Hkv, 128]; sequence b starts at row b * S and
+    cu_k only carries the lengths."""
+    total_q, Hq, D = q.shape
+    total_k, Hkv = k.shape[0], k.shape[1]
+    assert q.is_cuda and q.dtype == torch.bfloat16 and D == 128 and k.dtype == v.dtype == torch.bfloat16
+    assert q.stride(2) == 1 and q.stride(1) == D and k.stride(2) == 1 and k.stride(1) == D and v.stride() == k.stride()
+    if out is None:
+        out = torch.empty((total_q, Hq, D), dtype=q.dtype, device=q.device)
+    assert out.is_contiguous()
+    _lib.check(_lib.lib().tdist_attn_fwd_tc(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), cu_q.data_ptr(), cu_k.data_ptr(),
+                                            cu_q.numel() - 1, max_q, total_q, total_k, Hq, Hkv, D, q.stride(0), k.stride(0), k_batch_stride, rank, world,
+                                            int(causal), int(zigzag), float(scale if scale is not None else 1.0 / math.sqrt(D)),
+                                            _lib.stream_ptr()), "attn_fwd_tc")
+    return out
+
+
 def fused_sp_ag_attn_intra_node(ctx: SPAllGatherAttentionContextIntraNode, q_shard: torch.Tensor, k_shard: torch.Tensor,
                                 v_shard: torch.Tensor, output: Optional[torch.Tensor], cu_seqlens_q: torch.Tensor,
                                 cu_seqlens_k: torch.Tensor, max_seqlen_q: int, max_seqlen_k: int, rank: int, world_size: int,
@@ -150,6 +176,9 @@ def fused_sp_ag_attn_intra_node(ctx: SPAllGatherAttentionContextIntraNode, q_sha
         output.copy_(o.to(output.dtype))
         return output
     B = cu_q.numel() - 1
+    if os.environ.get("TDIST_ATTN_LEGACY", "0") != "1":
+        return flash_attn_varlen(q_shard, ctx.ag_k_buffer, ctx.ag_v_buffer, cu_q, cu_k, max_seqlen_q, is_causal, out=output,
+                                 rank=rank, world=world_size, zigzag=enable_zig_zag)
     _lib.check(_lib.lib().tdist_sp_attn_fwd(q_shard.contiguous().data_ptr(), ctx.ag_k_buffer.data_ptr(), ctx.ag_v_buffer.data_ptr(),
                                             output.data_ptr(), cu_q.data_ptr(), cu_k.data_ptr(), B, max_seqlen_q, q_shard.shape[1],
                                             k_shard.shape[1], D, rank, world_size, int(is_causal), int(enable_zig_zag), scale,

@@ -38,6 +38,12 @@ struct AttnTcParams {
   float scale_log2;
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ int attn_q_pos(int i, int Lq, int L, int rank, int world, int zigzag) {
   if (world == 1) return i + (L - Lq);  // one rank: the queries are the LAST Lq positions of the sequence (prefill / chunked prefill)
   if (!zigzag) return rank * (L / world) + i;
@@ -68,7 +74,8 @@ struct AttnSmem {
 __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_tc_kernel(const __grid_constant__ AttnTcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.z, h = blockIdx.y, qt = blockIdx.x;
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int qt = gridDim.x - 1 - blockIdx.x;  // causal: the last query tiles see the most keys, start them first
   const int q_beg = p.cu_q[b], Lq = p.cu_q[b + 1] - q_beg;
   const int L = p.cu_k[b + 1] - p.cu_k[b];
   const int k_beg = p.k_batch_stride > 0 ? b * p.k_batch_stride : p.cu_k[b];  // dense cache [B][S] or packed varlen
@@ -250,8 +257,13 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_tc_kernel(const __grid
       const bool full = k0 + 64 <= vis_end;  // no masking needed in my half tile
       float mx = -CUDART_INF_F;
       if (full) {
+        float m4[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};  // four independent chains
 #pragma unroll
-        for (int i = 0; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(sv[i]));
+        for (int i = 0; i < 64; i += 4) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) m4[u] = fmaxf(m4[u], __uint_as_float(sv[i + u]));
+        }
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       } else {
 #pragma unroll
         for (int i = 0; i < 64; ++i)
@@ -263,26 +275,27 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_tc_kernel(const __grid
       const float m_new = fmaxf(m_i, mx * p.scale_log2);
       const float alpha = m_new == -CUDART_INF_F ? 1.f : exp2f(m_i - m_new);
       const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
-      // P = exp2(S * scale - m) -> bf16 -> shared memory (K-major panel `half`, 128B swizzle)
-      if (j > 0) ptx::mbar_wait(p_empty, (j - 1) & 1);  // P_{j-1} V_{j-1} has finished reading the P buffer
-      float l_add = 0.f;
-      uint8_t* prow = sP + half * kAtPanel + row * 128;
+      // P = exp2(S * scale - m) -> bf16, kept in registers until the tensor core has finished reading the previous P
+      // (the exponentials are the long part of a tile: they must not wait for P_{j-1} V_{j-1})
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t pk[32];
 #pragma unroll
-      for (int c = 0; c < 64; c += 8) {
-        uint32_t pk[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float p0 = exp2f(fmaf(__uint_as_float(sv[c + 2 * i]), p.scale_log2, -m_use));
-          float p1 = exp2f(fmaf(__uint_as_float(sv[c + 2 * i + 1]), p.scale_log2, -m_use));
-          if (!full) {
-            if (k0 + c + 2 * i >= vis_end) p0 = 0.f;
-            if (k0 + c + 2 * i + 1 >= vis_end) p1 = 0.f;
-          }
-          l_add += p0 + p1;
-          pk[i] = ptx::pack_bf16x2(p0, p1);
+      for (int i = 0; i < 32; ++i) {
+        float p0 = ex2_approx(fmaf(__uint_as_float(sv[2 * i]), p.scale_log2, -m_use));
+        float p1 = ex2_approx(fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2, -m_use));
+        if (!full) {
+          if (k0 + 2 * i >= vis_end) p0 = 0.f;
+          if (k0 + 2 * i + 1 >= vis_end) p1 = 0.f;
         }
-        *reinterpret_cast<int4*>(prow + (((c >> 3) ^ (row & 7)) << 4)) = make_int4(pk[0], pk[1], pk[2], pk[3]);
+        l4[i & 3] += p0 + p1;
+        pk[i] = ptx::pack_bf16x2(p0, p1);
       }
+      const float l_add = (l4[0] + l4[1]) + (l4[2] + l4[3]);
+      if (j > 0) ptx::mbar_wait(p_empty, (j - 1) & 1);  // P_{j-1} V_{j-1} has finished reading the P buffer
+      uint8_t* prow = sP + half * kAtPanel + row * 128;  // K-major panel `half`, 128B swizzle
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<int4*>(prow + ((c ^ (row & 7)) << 4)) = make_int4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       if (j * kAtBN + kAtBN > L) {
         // keys beyond the sequence get probability 0, but 0 * (whatever lies behind the sequence in the buffer) must
         // not produce NaN: clear those V rows of this tile (each thread: its key row, its 64 dims)
@@ -293,7 +306,7 @@ __global__ void __launch_bounds__(kAtThreads, 1) attn_fwd_tc_kernel(const __grid
           for (int i = 0; i < 8; ++i) vr[i] = make_int4(0, 0, 0, 0);
         }
       }
-      ptx::fence_proxy_async();  // generic-proxy writes (P, cleared V rows) -> visible to the tensor core's reads
+      ptx::fence_proxy_async_shared();  // generic-proxy writes to shared memory (P, cleared V rows) -> visible to the tensor core
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(p_full);
       l_i = l_i * alpha + l_add;

@@ -60,6 +60,12 @@ __device__ __forceinline__ void fence_proxy_async_shared() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// programmatic dependent launch (reference: backends/nvidia/backend/driver.py:296-339 sets the launch attribute,
+// Triton's gdc_wait / gdc_launch_dependents are the device side): a kernel launched with the attribute may start while
+// its predecessor in the stream is still running; everything before gdc_wait() overlaps with the predecessor's tail.
+__device__ __forceinline__ void gdc_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void gdc_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- scoped ld / st / atom (32 and 64 bit)
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;

@@ -71,6 +71,8 @@ template <typename T, int MAXM>
 __global__ void __launch_bounds__(256) gemv_kernel(const T* __restrict__ x, const T* __restrict__ w,
                                                    const T* __restrict__ bias, T* __restrict__ y, int M, int N, int K,
                                                    long long ldx, long long ldw, long long ldy) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   constexpr int UN = 4;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warps_per_cta = blockDim.x >> 5;
@@ -132,6 +134,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) rmsnorm_kernel(const T* __restrict__ x, T* residual, const T* __restrict__ weight,
                                                       T* __restrict__ y, int hidden, float eps, long long ldx,
                                                       long long ldy) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   extern __shared__ float sh_row[];  // hidden floats + 32 scratch
   float* scratch = sh_row + hidden;
   const size_t row = blockIdx.x;
@@ -172,6 +176,8 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(const T* __restrict__ x, T
 template <typename T>
 __global__ void __launch_bounds__(256) silu_mul_kernel(const T* __restrict__ gate_up, T* __restrict__ out, int inter,
                                                        long long total_vec) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   const int iv = inter >> 3;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total_vec;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -190,6 +196,8 @@ __global__ void __launch_bounds__(256) silu_mul_kernel(const T* __restrict__ gat
 template <typename T>
 __global__ void __launch_bounds__(256) add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ out,
                                                   long long n_vec) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec; i += (long long)gridDim.x * blockDim.x) {
     float x[8], y[8];
     unpack8<T>(reinterpret_cast<const int4*>(a)[i], x);
@@ -211,6 +219,8 @@ __global__ void __launch_bounds__(256) qk_norm_rope_kv_kernel(
     T* __restrict__ q_out, T* k_cache, T* v_cache, int T_tokens, int Hq, int Hkv, float eps, long long kv_batch_stride,
     long long kv_seq_stride, long long kv_head_stride, const int* __restrict__ block_table, int page_size,
     int max_pages) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   const int heads = Hq + 2 * Hkv;
   if (warp >= T_tokens * heads) return;
@@ -277,6 +287,8 @@ __global__ void __launch_bounds__(128) flash_decode_split_kernel(
     const int* __restrict__ kv_lens, float* __restrict__ partial, int Hq, int Hkv, int splits, float sm_scale,
     long long kv_batch_stride, long long kv_seq_stride, long long kv_head_stride, const int* __restrict__ block_table,
     int page_size, int max_pages, int g_total, int g_offset) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   constexpr int D = 128;
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -391,6 +403,8 @@ template <typename T>
 __global__ void __launch_bounds__(128) flash_decode_combine_kernel(const float* __restrict__ partial, T* out16,
                                                                    float* out_f32, int H, int splits, long long sb,
                                                                    long long sh, long long ss) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   constexpr int D = 128;
   const int h = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
   const float* base = partial + size_t(b) * sb + size_t(h) * sh;
@@ -416,6 +430,8 @@ __global__ void __launch_bounds__(128) flash_decode_combine_kernel(const float* 
 template <typename T>
 __global__ void __launch_bounds__(256) embedding_kernel(const long long* __restrict__ ids, const T* __restrict__ table,
                                                         T* __restrict__ out, int hidden) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   const size_t t = blockIdx.x;
   const int4* src = reinterpret_cast<const int4*>(table + size_t(ids[t]) * hidden);
   int4* dst = reinterpret_cast<int4*>(out + t * hidden);
@@ -425,6 +441,8 @@ __global__ void __launch_bounds__(256) embedding_kernel(const long long* __restr
 template <typename T>
 __global__ void __launch_bounds__(1024) argmax_kernel(const T* __restrict__ logits, long long* __restrict__ out, int vocab,
                                                       long long ld) {
+  ptx::gdc_wait();  // programmatic dependent launch: the inputs come from the previous kernel in the stream
+  ptx::gdc_launch_dependents();
   __shared__ float sv[32];
   __shared__ int si[32];
   const T* row = logits + size_t(blockIdx.x) * ld;
@@ -483,9 +501,36 @@ struct FlashDecodeArgs {
   const int* block_table;
   int page_size, max_pages;
 };
+// Launch with the programmatic-dependent-launch attribute (off with TDIST_PDL=0): the decode path is a chain of ~10 small
+// kernels per layer, each of which starts with gdc_wait(), so the launch + prologue of kernel i+1 overlaps the tail of
+// kernel i (same effect inside a captured CUDA graph: the edges become programmatic).
+struct PdlLaunch {
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[1];
+  PdlLaunch(dim3 grid, dim3 block, size_t smem, cudaStream_t s) {
+    static const bool on = [] {
+      const char* e = getenv("TDIST_PDL");
+      return e == nullptr || atoi(e) != 0;
+    }();
+    cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = on ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  template <typename... KArgs, typename... Args>
+  void operator()(void (*kern)(KArgs...), Args&&... args) {
+    cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+  }
+};
+
 template <typename T, int G>
 static void launch_fd_pass(const FlashDecodeArgs& a, int g_total, int g_off, cudaStream_t s) {
-  flash_decode_split_kernel<T, G><<<dim3(a.splits, a.Hkv, a.B), 128, 0, s>>>(
+  PdlLaunch(dim3(a.splits, a.Hkv, a.B), 128, 0, s)(flash_decode_split_kernel<T, G>, 
       static_cast<const T*>(a.q), static_cast<const T*>(a.k), static_cast<const T*>(a.v), a.kv_lens, a.partial, a.Hq,
       a.Hkv, a.splits, a.sm_scale, a.sb, a.ss, a.sh, a.block_table, a.page_size, a.max_pages, g_total, g_off);
 }
@@ -510,7 +555,7 @@ static void launch_flash_decode(const FlashDecodeArgs& a, cudaStream_t s) {
     }
   }
   if (a.out16 != nullptr || a.out_lse != nullptr) {
-    flash_decode_combine_kernel<T><<<dim3(a.Hq, a.B), 128, 0, s>>>(a.partial, static_cast<T*>(a.out16), a.out_lse, a.Hq,
+    PdlLaunch(dim3(a.Hq, a.B), 128, 0, s)(flash_decode_combine_kernel<T>, a.partial, static_cast<T*>(a.out16), a.out_lse, a.Hq,
                                                                    a.splits, (long long)a.Hq * a.splits * 129,
                                                                    (long long)a.splits * 129, 129);
   }
@@ -549,15 +594,15 @@ int tdist_gemv(int dtype, const void* x, const void* w, const void* bias, void* 
     const T* bp = static_cast<const T*>(bias);
     T* yp = static_cast<T*>(y);
     if (M <= 1)
-      gemv_kernel<T, 1><<<grid, warps * 32, 0, s>>>(xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
+      PdlLaunch(grid, warps * 32, 0, s)(gemv_kernel<T, 1>, xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
     else if (M <= 2)
-      gemv_kernel<T, 2><<<grid, warps * 32, 0, s>>>(xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
+      PdlLaunch(grid, warps * 32, 0, s)(gemv_kernel<T, 2>, xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
     else if (M <= 4)
-      gemv_kernel<T, 4><<<grid, warps * 32, 0, s>>>(xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
+      PdlLaunch(grid, warps * 32, 0, s)(gemv_kernel<T, 4>, xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
     else if (M <= 8)
-      gemv_kernel<T, 8><<<grid, warps * 32, 0, s>>>(xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
+      PdlLaunch(grid, warps * 32, 0, s)(gemv_kernel<T, 8>, xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
     else
-      gemv_kernel<T, 16><<<grid, warps * 32, 0, s>>>(xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
+      PdlLaunch(grid, warps * 32, 0, s)(gemv_kernel<T, 16>, xp, wp, bp, yp, M, N, K, ldx, ldw, ldy);
   });
   return check_launch("gemv");
 }
@@ -579,7 +624,7 @@ int tdist_rmsnorm(int dtype, const void* x, void* residual, const void* weight, 
       cudaFuncSetAttribute(rmsnorm_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
       attr = true;
     }
-    rmsnorm_kernel<T><<<rows, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+    PdlLaunch(rows, 256, smem, static_cast<cudaStream_t>(stream))(rmsnorm_kernel<T>, 
         static_cast<const T*>(x), static_cast<T*>(residual), static_cast<const T*>(weight), static_cast<T*>(y), hidden,
         eps, ldx, ldy);
   });
@@ -596,7 +641,7 @@ int tdist_silu_mul(int dtype, const void* gate_up, void* out, long long tokens, 
   if (grid > 148 * 8) grid = 148 * 8;
   if (grid < 1) grid = 1;
   DISPATCH_16(dtype, {
-    silu_mul_kernel<T><<<int(grid), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(gate_up),
+    PdlLaunch(int(grid), 256, 0, static_cast<cudaStream_t>(stream))(silu_mul_kernel<T>, static_cast<const T*>(gate_up),
                                                                                 static_cast<T*>(out), inter, total);
   });
   return check_launch("silu_mul");
@@ -612,7 +657,7 @@ int tdist_add(int dtype, const void* a, const void* b, void* out, long long nume
   if (grid > 148 * 8) grid = 148 * 8;
   if (grid < 1) grid = 1;
   DISPATCH_16(dtype, {
-    add_kernel<T><<<int(grid), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(a),
+    PdlLaunch(int(grid), 256, 0, static_cast<cudaStream_t>(stream))(add_kernel<T>, static_cast<const T*>(a),
                                                                            static_cast<const T*>(b), static_cast<T*>(out), nv);
   });
   return check_launch("add");
@@ -631,7 +676,7 @@ int tdist_qk_norm_rope_kv(int dtype, const void* qkv, const void* q_norm_w, cons
   const int grid = int((warps * 32 + 255) / 256);
   if (grid == 0) return 0;
   DISPATCH_16(dtype, {
-    qk_norm_rope_kv_kernel<T><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    PdlLaunch(grid, 256, 0, static_cast<cudaStream_t>(stream))(qk_norm_rope_kv_kernel<T>, 
         static_cast<const T*>(qkv), static_cast<const T*>(q_norm_w), static_cast<const T*>(k_norm_w), cos_sin, positions,
         batch_idx, static_cast<T*>(q_out), static_cast<T*>(k_cache), static_cast<T*>(v_cache), tokens, Hq, Hkv, eps,
         kv_batch_stride, kv_seq_stride, kv_head_stride, block_table, page_size, max_pages);
@@ -656,7 +701,7 @@ int tdist_flash_decode(int dtype, const void* q, const void* k_cache, const void
 int tdist_flash_decode_combine(int dtype, const float* partial, void* out16, float* out_lse, int B, int H, int splits,
                                long long stride_b, long long stride_h, long long stride_s, void* stream) {
   DISPATCH_16(dtype, {
-    flash_decode_combine_kernel<T><<<dim3(H, B), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+    PdlLaunch(dim3(H, B), 128, 0, static_cast<cudaStream_t>(stream))(flash_decode_combine_kernel<T>, 
         partial, static_cast<T*>(out16), out_lse, H, splits, stride_b, stride_h, stride_s);
   });
   return check_launch("flash_decode_combine");
@@ -669,7 +714,7 @@ int tdist_embedding(int dtype, const long long* ids, const void* table, void* ou
   }
   if (tokens == 0) return 0;
   DISPATCH_16(dtype, {
-    embedding_kernel<T><<<tokens, 256, 0, static_cast<cudaStream_t>(stream)>>>(ids, static_cast<const T*>(table),
+    PdlLaunch(tokens, 256, 0, static_cast<cudaStream_t>(stream))(embedding_kernel<T>, ids, static_cast<const T*>(table),
                                                                               static_cast<T*>(out), hidden);
   });
   return check_launch("embedding");
@@ -678,7 +723,7 @@ int tdist_embedding(int dtype, const long long* ids, const void* table, void* ou
 int tdist_argmax(int dtype, const void* logits, long long* out, int rows, int vocab, long long ld, void* stream) {
   if (rows == 0) return 0;
   DISPATCH_16(dtype, {
-    argmax_kernel<T><<<rows, 1024, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(logits), out, vocab, ld);
+    PdlLaunch(rows, 1024, 0, static_cast<cudaStream_t>(stream))(argmax_kernel<T>, static_cast<const T*>(logits), out, vocab, ld);
   });
   return check_launch("argmax");
 }

@@ -40,9 +40,14 @@ if __name__ == "__main__":
     ref = torch_ag_gemm(A.float(), B.float())
     rows.append(dict(op="ag_gemm", cfg="torch NCCL+cuBLAS", ms=t_ref, ok=True))
     dist_print(f"ag_gemm  torch NCCL+cuBLAS: {t_ref:.4f} ms")
-    ag_cfgs = [(0, 0, -1, 8, 1)] if args.quick or world == 1 else [(2, 2, 8, 8, 1), (2, 1, 8, 8, 1), (2, 2, 8, 8, 2), (2, 2, 4, 4, 1)] if args.ablate else [(2, 2, 8, 8, 1), (2, 2, 16, 16, 1), (2, 2, 16, 8, 1), (2, 1, 8, 8, 1), (1, 2, -1, 8, 1), (1, 1, -1, 8, 1)] if True else [
-        (2, 2, 8, 8, 1), (2, 2, 8, 8, 2), (2, 2, 8, 8, 4), (2, 2, 4, 4, 1), (2, 2, 4, 4, 2), (2, 2, 16, 16, 1), (2, 2, 16, 16, 2),
-        (2, 2, 16, 16, 4), (2, 1, 8, 8, 1), (2, 1, 8, 8, 2), (1, 2, -1, 8, 1)]
+    # (variant, cta_group, push CTAs, row slices per block, K slabs)
+    if args.quick or world == 1:
+        ag_cfgs = [(0, 0, -1, 8, 1)]
+    elif args.ablate:
+        ag_cfgs = [(2, 2, 8, 8, 1), (2, 1, 8, 8, 1), (2, 2, 8, 8, 2), (2, 2, 4, 4, 1)]
+    else:
+        ag_cfgs = [(0, 0, -1, 8, 1), (2, 2, 8, 8, 1), (2, 2, 16, 16, 1), (2, 2, 16, 8, 1), (2, 1, 8, 8, 1), (2, 2, 8, 8, 2),
+                   (1, 2, -1, 8, 1), (1, 1, -1, 8, 1)]
     for variant, cta_group, comm, slices, slabs in ag_cfgs:
         os.environ["TDIST_AG_SLICES"] = str(slices)
         os.environ["TDIST_AG_KSLABS"] = str(slabs)
@@ -65,7 +70,7 @@ if __name__ == "__main__":
     ref2 = torch_gemm_rs(A2.float(), B2.float())
     rows.append(dict(op="gemm_rs", cfg="torch cuBLAS+NCCL", ms=t_ref, ok=True))
     dist_print(f"gemm_rs  torch cuBLAS+NCCL: {t_ref:.4f} ms")
-    rs_cfgs = [(0, 0, 0, 8)] if args.quick or world == 1 else [(2, 2, 0, 8), (2, 2, 0, 16), (2, 1, 0, 8), (1, 2, 0, 8), (1, 1, 0, 8)]
+    rs_cfgs = [(0, 0, 0, 16)] if args.quick or world == 1 else [(0, 0, 0, 16), (2, 2, 0, 8), (2, 2, 0, 16), (2, 1, 0, 16), (1, 2, 0, 16), (1, 1, 0, 16)]
     if args.ablate:
         rs_cfgs = [(2, 2, 0, 16, d) for d in (0, 4, 8)] + [(2, 2, 0, 8, 0), (2, 1, 0, 8, 0)]
     for cfg in rs_cfgs:

@@ -124,6 +124,10 @@ def _launch(ctx: GemmARContext, a: torch.Tensor, b: torch.Tensor, one_shot: bool
     if not ctx.native:
         return torch_gemm_ar(a, b)
     heap = _symm.get_heap()
+    if ctx.world_size == 1:  # nothing to reduce: the plain linear (GEMV for decode sizes, tcgen05 GEMM otherwise)
+        from .elementwise import linear
+
+        return linear(a, b)
     if M <= 16 and one_shot and ctx.use_mc and K % 8 == 0 and os.environ.get("TDIST_GEMM_AR_DECODE", "fused") == "gemv":
         # decode: the tensor core would idle at <= 16 rows. Weight-streaming GEMV straight into the symmetric buffer,
         # then the NVLS one-shot all-reduce in place (multimem.ld_reduce; no staging copy).

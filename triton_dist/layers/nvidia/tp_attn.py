@@ -10,6 +10,7 @@ activations) | dist_triton_AR_fwd | dist_triton_gemm_ar_fwd."""
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -152,6 +153,20 @@ class TP_Attn:
             out = dense_decode(q, k_cache, v_cache, kv_lens, scale)  # [B, Hq, D]
             return out.view(bsz, self.q_size)
         # prefill: causal attention over the cache prefix [0, last_pos]
+        if (q.is_cuda and q.dtype == torch.bfloat16 and self.head_dim == 128 and k_cache.is_contiguous()
+                and os.environ.get("TDIST_ATTN_SDPA", "0") != "1"):
+            # own tcgen05 flash attention (csrc/kernels/sp_attn_sm100.cu) straight on the dense cache: the queries of a
+            # sequence are the last q_len of its kv_len positions (fresh prompt or chunked prefill); no host read
+            from ...kernels.nvidia.sp_ag_attention_intra_node import flash_attn_varlen
+
+            S = k_cache.shape[1]
+            lens = (position_ids[:, -1] + 1).to(torch.int32)
+            cu_k = torch.zeros(bsz + 1, dtype=torch.int32, device=q.device)
+            cu_k[1:] = torch.cumsum(lens, 0)
+            cu_q = torch.arange(bsz + 1, dtype=torch.int32, device=q.device) * q_len
+            out = flash_attn_varlen(q.view(bsz * q_len, self.num_q_heads, self.head_dim), k_cache.view(-1, self.num_kv_heads, self.head_dim),
+                                    v_cache.view(-1, self.num_kv_heads, self.head_dim), cu_q, cu_k, q_len, causal=True, k_batch_stride=S)
+            return out.view(bsz * q_len, self.q_size)
         kv_len = int(position_ids.max().item()) + 1
         g = self.num_q_heads // self.num_kv_heads
         qh = q.view(bsz, q_len, self.num_q_heads, self.head_dim).transpose(1, 2)

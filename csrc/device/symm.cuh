@@ -80,49 +80,53 @@ __device__ __forceinline__ void notify_local(uint32_t* flag, uint32_t value) { p
     __trap();                                                                                                          \
   }
 #else
-#define TDIST_SPIN_GUARD_DECL
-#define TDIST_SPIN_GUARD(flag, have, want)
+// Always-on bound (release builds): every 2^20 polls of one flag the wall clock is read; a wait that has lasted longer
+// than TDIST_SPIN_TIMEOUT_S seconds (default 60; a healthy wait is micro- to milliseconds) prints the flag and traps, so
+// a dead or wedged peer turns into a CUDA error within a minute instead of hanging the node until the NCCL watchdog
+// (1800 s). Cost: one counter increment per poll.
+#ifndef TDIST_SPIN_TIMEOUT_S
+#define TDIST_SPIN_TIMEOUT_S 60
+#endif
+#define TDIST_SPIN_GUARD_DECL    \
+  unsigned int tdist_spins_ = 0; \
+  unsigned long long tdist_t0_ = 0
+#define TDIST_SPIN_GUARD(flag, have, want)                                                                             \
+  if ((++tdist_spins_ & 0xFFFFFu) == 0) {                                                                              \
+    const unsigned long long now_ = ::tdist::ptx::globaltimer();                                                       \
+    if (tdist_t0_ == 0) {                                                                                              \
+      tdist_t0_ = now_;                                                                                                \
+    } else if (now_ - tdist_t0_ > 1000000000ull * TDIST_SPIN_TIMEOUT_S) {                                              \
+      printf("tdist: wait timed out after %d s: flag %p holds %u, waiting for %u (block %d thread %d)\n",              \
+             int(TDIST_SPIN_TIMEOUT_S), (const void*)(flag), (have), (want), int(blockIdx.x), int(threadIdx.x));       \
+      __trap();                                                                                                        \
+    }                                                                                                                  \
+  }
 #endif
 
 // Spin until *flag == value (acquire, system scope). One lane polls.
 __device__ __forceinline__ void wait_eq_sys(const uint32_t* flag, uint32_t value) {
-#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while ((v = ptx::ld_acquire_sys(flag)) != value) {
     TDIST_SPIN_GUARD(flag, v, value)
   }
-#else
-  while (ptx::ld_acquire_sys(flag) != value) {
-  }
-#endif
 }
 __device__ __forceinline__ void wait_ge_sys(const uint32_t* flag, uint32_t value) {
-#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while (static_cast<int32_t>((v = ptx::ld_acquire_sys(flag)) - value) < 0) {
     TDIST_SPIN_GUARD(flag, v, value)
   }
-#else
-  while (static_cast<int32_t>(ptx::ld_acquire_sys(flag) - value) < 0) {
-  }
-#endif
 }
 // Same wait, polling with RELAXED loads and ending with one acquire load of the flag. Inside a kernel that keeps many
 // loads in flight (TMA pipelines, NVLS loads) an acquire in every poll iteration is expensive: a system-scope acquire
 // also waits for the SM's other outstanding memory traffic (measured on the fused GEMM+RS at 8 ranks, profiles/README.md).
 __device__ __forceinline__ void wait_ge_sys_poll_relaxed(const uint32_t* flag, uint32_t value) {
-#ifdef TDIST_SPIN_LIMIT
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while (static_cast<int32_t>((v = ptx::ld_relaxed_sys(flag)) - value) < 0) {
     TDIST_SPIN_GUARD(flag, v, value)
   }
-#else
-  while (static_cast<int32_t>(ptx::ld_relaxed_sys(flag) - value) < 0) {
-  }
-#endif
   (void)ptx::ld_acquire_sys(flag);
 }
 // Warp-collective wait on n consecutive flags (n <= 32): the first n lanes of
@@ -283,8 +287,7 @@ __device__ __forceinline__ void barrier_all_block(const SymmCtx& c, uint32_t* fl
   if (t < c.world) {
     ptx::fence_acq_rel_sys();
     ptx::st_release_sys(symm_at(c, flags + c.rank, t), phase);  // tell rank t that I arrived
-    while (static_cast<int32_t>(ptx::ld_acquire_sys(flags + t) - phase) < 0) {
-    }  // wait until rank t arrived here
+    wait_ge_sys(flags + t, phase);  // wait until rank t arrived here
   }
   __syncthreads();
 }

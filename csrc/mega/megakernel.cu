@@ -54,17 +54,12 @@ __device__ __forceinline__ float block_sum(float v, float* scratch) {
 
 __device__ __forceinline__ void wait_slot(const uint32_t* sb, int slot, uint32_t target) {
   if (slot < 0) return;
-#ifdef TDIST_SPIN_LIMIT
+  // (polling with ld.volatile + one trailing fence instead of ld.acquire was measured slower: 4.60 vs 4.27 ms/token)
   TDIST_SPIN_GUARD_DECL;
   uint32_t v;
   while (static_cast<int32_t>((v = ptx::ld_acquire_gpu(sb + slot)) - target) < 0) {
     TDIST_SPIN_GUARD(sb + slot, v, target)
   }
-#else
-  // (polling with ld.volatile + one trailing fence instead of ld.acquire was measured slower: 4.60 vs 4.27 ms/token)
-  while (static_cast<int32_t>(ptx::ld_acquire_gpu(sb + slot) - target) < 0) {
-  }
-#endif
 }
 
 // ------------------------------------------------------------------ LINEAR (skinny GEMM, M <= 8 rows)

@@ -19,6 +19,7 @@ from __future__ import annotations
 
 import ctypes
 import dataclasses
+import os
 from typing import List, Optional
 
 import torch
@@ -166,12 +167,42 @@ def ag_gemm(a: torch.Tensor, b: torch.Tensor, ctx: AllGatherGEMMTensorParallelCo
         torch.cuda._sleep(int(straggler_option[1]))
     if ctx.for_correctness:  # shake out ordering bugs: random skew between ranks
         torch.cuda._sleep(int(torch.randint(0, 2_000_000, (1,)).item()))
+    if autotune:
+        # launch knobs come from the contextual autotuner: inside contextual_autotune(...) every combination is tried (the
+        # winner = smallest MAX-over-ranks time is cached per shape), outside it the cached winner (or the defaults) runs
+        return _ag_gemm_tuned(a, b, ctx, out)
+    return _ag_gemm_launch(a, b, ctx, out, ctx.variant, ctx.cta_group, ctx.num_comm_sms)
+
+
+def _ag_gemm_launch(a, b, ctx, out, variant, cta_group, num_comm_sms):
+    M_per_rank, K = a.shape
+    N = b.shape[0]
+    M = M_per_rank * ctx.num_ranks
     heap = _symm.get_heap()
-    args = _gemm_args(a, b, out, M, N, K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_SIZE_M, cta_group=ctx.cta_group)
+    args = _gemm_args(a, b, out, M, N, K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_SIZE_M, cta_group=cta_group)
     st = ctx.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=1, ws=ctx.symm_workspace.data_ptr(), out=None, flags=st.flags_ptr, flags2=None,
-                       counters=None, phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=ctx.num_comm_sms, ar_one_shot=0,
-                       use_mc=0, variant=ctx.variant, ws_bytes=ctx.symm_workspace.numel() * ctx.symm_workspace.element_size(),
+                       counters=None, phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=num_comm_sms, ar_one_shot=0,
+                       use_mc=0, variant=variant, ws_bytes=ctx.symm_workspace.numel() * ctx.symm_workspace.element_size(),
                        flags_words=ctx.flags_words)
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "ag_gemm")
     return out
+
+
+def _ag_key(a, b, ctx, out=None, **_):
+    return ("ag_gemm", a.shape[0] * ctx.num_ranks, b.shape[0], a.shape[1], ctx.num_ranks, str(a.dtype))
+
+
+# the space the reference tunes its consumer GEMM over (allgather_gemm.py:396-414: tile shapes / stages / warps) becomes,
+# for ahead-of-time compiled kernels: protocol (1 point-to-point, 2 NVLS; 0 = built-in choice), tile kind (CTA pair or
+# single CTA) and number of push CTAs. Without a multicast mapping an NVLS entry runs the built-in choice instead.
+from ...autotuner import tunable  # noqa: E402
+
+_AG_SPACE = {"variant": [0, 1, 2], "cta_group": [2, 1], "num_comm_sms": [-1, 8, 16]}
+
+
+@tunable("ag_gemm", _AG_SPACE, key=_ag_key)
+def _ag_gemm_tuned(a, b, ctx, out, variant=0, cta_group=0, num_comm_sms=-1):
+    if variant == 2 and not _symm.get_heap().multicast:
+        variant = 0
+    return _ag_gemm_launch(a, b, ctx, out, variant, cta_group, num_comm_sms)

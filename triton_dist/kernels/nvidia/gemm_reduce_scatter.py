@@ -80,7 +80,7 @@ def torch_gemm_rs(a: torch.Tensor, b: torch.Tensor, group=None) -> torch.Tensor:
 
 
 def gemm_rs_op(input: torch.Tensor, weight: torch.Tensor, ctx: GEMMReduceScatterTensorParallelContext, persistent: bool = True,
-               fuse_scatter: bool = True, output: Optional[torch.Tensor] = None) -> torch.Tensor:
+               fuse_scatter: bool = True, output: Optional[torch.Tensor] = None, autotune: bool = False) -> torch.Tensor:
     _check_operands(input, weight)
     M, local_K = input.shape
     N = weight.shape[0]
@@ -91,18 +91,37 @@ def gemm_rs_op(input: torch.Tensor, weight: torch.Tensor, ctx: GEMMReduceScatter
         return torch_gemm_rs(input, weight)
     if output is None:
         output = torch.empty((M // W, N), dtype=ctx.output_dtype, device=input.device)
+    if autotune:  # see allgather_gemm.ag_gemm: knobs from the contextual autotuner (protocol, tile kind)
+        return _gemm_rs_tuned(input, weight, ctx, output)
+    return _gemm_rs_launch(input, weight, ctx, output, ctx.variant, ctx.cta_group)
+
+
+def _gemm_rs_launch(input, weight, ctx, output, variant, cta_group):
+    M, local_K = input.shape
+    N = weight.shape[0]
+    rs = ctx.rs_ctx
     heap = _symm.get_heap()
-    args = _gemm_args(input, weight, output, M, N, local_K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_M, cta_group=ctx.cta_group)
+    args = _gemm_args(input, weight, output, M, N, local_K, block_n=ctx.BLOCK_N, group_m=ctx.GROUP_M, cta_group=cta_group)
     st = rs.state
     f = _lib.FusedArgs(ctx=heap.ctx, mode=2, ws=rs.scatter_buf.data_ptr(), out=output.data_ptr(), flags=st.flags_ptr,
                        flags2=None, counters=ctx.counters.data_ptr(), phase=st.phase_ptr, done=st.done_ptr, num_comm_ctas=0,
-                       ar_one_shot=0, use_mc=0, variant=ctx.variant,
+                       ar_one_shot=0, use_mc=0, variant=variant,
                        ws_bytes=rs.scatter_buf.numel() * rs.scatter_buf.element_size(), flags_words=st.flags.numel())
     _lib.check(_lib.lib().tdist_gemm_fused(ctypes.byref(args), ctypes.byref(f), _lib.stream_ptr()), "gemm_rs")
     return output
 
 
 def gemm_rs(a: torch.Tensor, b: torch.Tensor, ctx: GEMMReduceScatterTensorParallelContext, persistent: bool = True,
-            fuse_scatter: bool = True) -> torch.Tensor:
+            fuse_scatter: bool = True, autotune: bool = False) -> torch.Tensor:
     """c[M/W, N] = reduce_scatter(a[M, K/W] @ b[N, K/W]^T)."""
-    return gemm_rs_op(a, b, ctx, persistent, fuse_scatter)
+    return gemm_rs_op(a, b, ctx, persistent, fuse_scatter, autotune=autotune)
+
+
+from ...autotuner import tunable  # noqa: E402
+
+
+@tunable("gemm_rs", {"variant": [0, 1, 2], "cta_group": [2, 1]},
+         key=lambda input, weight, ctx, output=None, **_: ("gemm_rs", input.shape[0], weight.shape[0], input.shape[1],
+                                                           ctx.rs_ctx.world_size, str(input.dtype)))
+def _gemm_rs_tuned(input, weight, ctx, output, variant=0, cta_group=0):
+    return _gemm_rs_launch(input, weight, ctx, output, variant, cta_group)

@@ -16,6 +16,8 @@ def cases(suite: str, world: int):
     core = [
         (T + "test_ag_gemm", [2048 * world, 512 * world, 1024, "--check", "--stress", "--alternate"]),
         (T + "test_ag_gemm", [200 * world, 136 * world, 520, "--check", "--verify-iters", 2]),
+        (T + "test_ag_gemm", [512 * world, 256 * world, 512, "--check", "--verify-iters", 1, "--autotune"]),
+        (T + "test_gemm_rs", [512 * world, 512, 256 * world, "--check", "--verify-iters", 1, "--autotune"]),
         (T + "test_gemm_rs", [2048 * world, 1024, 512 * world, "--check", "--stress", "--alternate"]),
         (T + "test_gemm_rs", [200 * world, 136, 72 * world, "--check", "--verify-iters", 2]),
         (T + "test_gemm_ar", [64, 1024, 512 * world, "--check", "--low-latency", "--stress"]),

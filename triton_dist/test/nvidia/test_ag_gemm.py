@@ -16,6 +16,7 @@ if __name__ == "__main__":
     p.add_argument("--block-n", type=int, default=0)
     p.add_argument("--comm-sms", type=int, default=-1)
     p.add_argument("--alternate", action="store_true", help="two sizes back to back on one context, rank skew, no host sync")
+    p.add_argument("--autotune", action="store_true", help="sweep the launch knobs under the contextual autotuner, then check the winner")
     args = p.parse_args()
     group, rank, world = setup()
     dtype = DTYPES[args.dtype]
@@ -49,6 +50,13 @@ if __name__ == "__main__":
             outs.append(ag_gemm(a_in, B, ctx))
         for it, (a_in, c_out) in enumerate(zip(ins, outs)):
             ok = all_ok(check_close(c_out, torch_ag_gemm(a_in.float(), B.float()), dtype, f"ag_gemm alternate {it}")) and ok
+    if ok and args.autotune:
+        from triton_dist.autotuner import _REGISTRY, contextual_autotune
+
+        A = rand(A.shape, dtype)
+        C = contextual_autotune(is_dist=True, warmup=2, iters=5)(lambda: ag_gemm(A, B, ctx, autotune=True))()
+        ok = all_ok(check_close(C, torch_ag_gemm(A.float(), B.float()), dtype, "ag_gemm autotuned"))
+        dist_print(f"ag_gemm autotune winner: {list(_REGISTRY['ag_gemm'].best.values())}")
     if ok and not args.check:
         A = rand((m_loc, args.K), dtype)
         t_fused = bench(lambda: ag_gemm(A, B, ctx), args)

@@ -15,6 +15,7 @@ if __name__ == "__main__":
     p.add_argument("K", type=int)
     p.add_argument("--block-n", type=int, default=0)
     p.add_argument("--alternate", action="store_true", help="two sizes back to back on one context, rank skew, no host sync")
+    p.add_argument("--autotune", action="store_true", help="sweep the launch knobs under the contextual autotuner, then check the winner")
     args = p.parse_args()
     group, rank, world = setup()
     dtype = DTYPES[args.dtype]
@@ -43,6 +44,13 @@ if __name__ == "__main__":
             outs.append(gemm_rs(a_in, B, ctx))
         for it, (a_in, c_out) in enumerate(zip(ins, outs)):
             ok = all_ok(check_close(c_out, torch_gemm_rs(a_in.float(), B.float()), dtype, f"gemm_rs alternate {it}")) and ok
+    if ok and args.autotune:
+        from triton_dist.autotuner import _REGISTRY, contextual_autotune
+
+        A = rand(A.shape, dtype)
+        C = contextual_autotune(is_dist=True, warmup=2, iters=5)(lambda: gemm_rs(A, B, ctx, autotune=True))()
+        ok = all_ok(check_close(C, torch_gemm_rs(A.float(), B.float()), dtype, "gemm_rs autotuned"))
+        dist_print(f"gemm_rs autotune winner: {list(_REGISTRY['gemm_rs'].best.values())}")
     if ok and not args.check:
         A = rand((args.M, k_loc), dtype)
         t_fused = bench(lambda: gemm_rs(A, B, ctx), args)

@@ -66,6 +66,7 @@ if __name__ == "__main__":
     with torch.inference_mode():
         ref_all = hf(ids).logits.float()  # teacher forcing: logits at every position
     ok = True
+    frac = 0.5 if (args.model == "qwen3_moe" and dtype != torch.float32) else None  # see logits_close: expert flips in 16 bit
     for mode in args.modes.split(","):
         if mode == "triton_dist" and args.model == "qwen3_moe" and world == 1 and dev == "cpu":
             pass
@@ -76,7 +77,7 @@ if __name__ == "__main__":
         model.set_fwd("torch")
         pos = torch.arange(n_pre, device=dev)[None, :].expand(bsz, -1)
         logits = model.inference(ids[:, :n_pre], pos, kv)
-        good = logits_close(logits[:, -1], ref_all[:, n_pre - 1], dtype, f"mode {mode} prefill")
+        good = logits_close(logits[:, -1], ref_all[:, n_pre - 1], dtype, f"mode {mode} prefill", frac)
         kv.kv_offset.fill_(n_pre)
         if mode == "triton_dist":
             model.set_fwd("triton_dist")
@@ -97,7 +98,7 @@ if __name__ == "__main__":
             ref = ref_all[:, p]
             if mode == "triton_dist":
                 ref = ref.split(bsz // world, dim=0)[rank]
-            step_ok = logits_close(lg, ref, dtype, f"mode {mode} decode step {step}")
+            step_ok = logits_close(lg, ref, dtype, f"mode {mode} decode step {step}", frac)
             good = good and step_ok
             kv.inc_offset()
         model.finalize()

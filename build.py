@@ -28,7 +28,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 
 
 def sources():
-    cu = sorted((SRC / "kernels").glob("*.cu")) + sorted((SRC / "mega").glob("*.cu"))
+    cu = sorted((SRC / "kernels").glob("*.cu")) + sorted((SRC / "mega").glob("*.cu")) + sorted((SRC / "tutorials").glob("*.cu"))
     cc = sorted((SRC / "runtime").glob("*.cc")) + sorted((SRC / "mega").glob("*.cc"))
     return cu, cc
 

@@ -43,6 +43,7 @@ if __name__ == "__main__":
         # kernel all-gather (NVLS push) of the same data
         sb = symm_tensor((world, m * args.K), dtype)
         sb[rank].copy_(x.reshape(-1))
+        nvshmem_barrier_all_on_stream()  # every rank has zero-filled its new buffer before any peer pushes into it
         fast_allgather(sb, gctx, mode="push_multimem")
         torch.cuda.synchronize()
         good = good and bool(torch.equal(sb.view(args.M, args.K), torch.cat(ref)))

@@ -7,6 +7,7 @@ from __future__ import annotations
 from typing import Optional
 
 import torch
+import torch.distributed as dist
 
 from ...kernels.nvidia.gemm_allreduce import (create_gemm_ar_context, create_ll_gemm_ar_context, gemm_allreduce_op,
                                               low_latency_gemm_allreduce_op)
@@ -19,8 +20,13 @@ class GemmARLayer(torch.nn.Module):
                  NUM_COMM_SMS: int = 8, user_gemm_config=None):
         super().__init__()
         self.tp_group = tp_group
-        self.rank = tp_group.rank() if tp_group is not None else 0
-        self.world_size = tp_group.size() if tp_group is not None else 1
+        # no explicit group = the default (world) group, as everywhere else in the layers
+        if tp_group is not None:
+            self.rank, self.world_size = tp_group.rank(), tp_group.size()
+        elif dist.is_initialized():
+            self.rank, self.world_size = dist.get_rank(), dist.get_world_size()
+        else:
+            self.rank, self.world_size = 0, 1
         self.local_world_size = local_world_size if local_world_size != -1 else self.world_size
         self.max_M, self.N, self.K = max_M, N, K
         self.input_dtype, self.output_dtype = input_dtype, output_dtype

@@ -294,6 +294,19 @@ int tdist_mega_get_trace(void* builder, unsigned long long* out, size_t cap_word
 int tdist_mega_get_queue(void* builder, int cta, int* out_8ints_per_task, int cap);
 int tdist_mega_destroy(void* builder);
 
+/* ---- tutorial-size kernels (csrc/tutorials; run and explained by tutorials/01, 07, 08 — not used by the library) ----
+ * queue: rank r streams n_items items of item_vecs 16-byte vectors into the `out` of rank r+1 through a queue of `slots`
+ *   slots in r+1's heap (queue [slots][item_vecs] int4, full / empty [slots] u32: symmetric, zeroed once; base = sum of
+ *   ceil(n_items / slots) over earlier calls on these buffers).
+ * ag_gemm: C[W * rows, N] = all_gather(a[rows, K]) * b[N, K]^T, ws symmetric [2][W * rows][K], flags [W][ceil(rows/64)].
+ * gemm_rs: out[M/W, N] = reduce_scatter(a[M, Kl] * b[N, Kl]^T), part symmetric [2][M][N], flags [W][M/W/64][N/64]. */
+int tdist_tutorial_queue(const tdist_symm_ctx* ctx, const void* in, void* out, void* queue, uint32_t* full, uint32_t* empty,
+                         int n_items, int item_vecs, int slots, uint32_t base, void* stream);
+int tdist_tutorial_ag_gemm(const tdist_symm_ctx* ctx, const void* a, const void* b, void* c, void* ws, uint32_t* flags,
+                           uint32_t* phase, uint32_t* done, int rows, int N, int K, int push_ctas, int ctas, void* stream);
+int tdist_tutorial_gemm_rs(const tdist_symm_ctx* ctx, const void* a, const void* b, void* out, void* part, uint32_t* flags,
+                           uint32_t* phase, uint32_t* done, int M, int N, int Kl, int ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

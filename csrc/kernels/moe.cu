@@ -83,6 +83,30 @@ __global__ void __launch_bounds__(256) moe_gather_rows_kernel(const int4* __rest
   }
 }
 
+// Stage-filtered form for the stage-gated AG + grouped GEMM (allgather_group_gemm.py, overlap mode): only the rows of
+// blocks whose LAST needed shard arrives at `stage` (block_stage[i / block_m] == stage) are written; all other rows of
+// dst are left untouched, so consecutive stages fill disjoint row blocks of the same buffer.
+__global__ void __launch_bounds__(256) moe_gather_rows_stage_kernel(const int4* __restrict__ src, int4* __restrict__ dst,
+                                                                    const int* __restrict__ sorted_pair_ids,
+                                                                    const int* __restrict__ meta,
+                                                                    const int* __restrict__ block_stage, int stage, int block_m,
+                                                                    int num_pairs, int topk, int row_vecs) {
+  const int rows = meta[0];
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int i = warp; i < rows; i += nwarps) {
+    if (block_stage[i / block_m] != stage) continue;
+    const int p = sorted_pair_ids[i];
+    int4* d = dst + size_t(i) * row_vecs;
+    if (p >= num_pairs) {
+      for (int v = lane; v < row_vecs; v += 32) d[v] = make_int4(0, 0, 0, 0);
+    } else {
+      const int4* s = src + size_t(p / topk) * row_vecs;
+      for (int v = lane; v < row_vecs; v += 32) d[v] = ptx::ld_nc_v4(s + v);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ top-k weighted reduce
 // out[t, :] = sum_k w[t, k] * y[pair_to_row[t * topk + k], :]. One warp per token.
 template <typename Tag>
@@ -254,6 +278,21 @@ int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids
   moe_gather_rows_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int4*>(src), static_cast<int4*>(dst), sorted_pair_ids, meta, num_pairs, topk, row_bytes / 16);
   return check_launch("moe_gather_rows");
+}
+
+int tdist_moe_gather_rows_stage(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, const int* block_stage,
+                                int stage, int block_m, int num_pairs, int topk, int row_bytes, int max_rows, void* stream) {
+  if (row_bytes % 16 != 0 || block_m < 1) {
+    set_error("moe_gather_rows_stage: row bytes must be a multiple of 16");
+    return -1;
+  }
+  int grid = (max_rows + 7) / 8;
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  moe_gather_rows_stage_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const int4*>(src), static_cast<int4*>(dst), sorted_pair_ids, meta, block_stage, stage, block_m, num_pairs, topk,
+      row_bytes / 16);
+  return check_launch("moe_gather_rows_stage");
 }
 
 int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,

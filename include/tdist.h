@@ -168,6 +168,10 @@ int tdist_moe_tile_swizzle(const int* sorted_pair_ids, const int* meta, int num_
                            int max_blocks, void* stream);
 int tdist_moe_gather_rows(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, int num_pairs,
                           int topk, int row_bytes, int max_rows, void* stream);
+/* Same gather restricted to the row blocks with block_stage[row / block_m] == stage (other rows of dst are not written):
+ * the stage-gated AG + grouped GEMM fills one buffer stage by stage as the token shards arrive. */
+int tdist_moe_gather_rows_stage(const void* src, void* dst, const int* sorted_pair_ids, const int* meta, const int* block_stage,
+                                int stage, int block_m, int num_pairs, int topk, int row_bytes, int max_rows, void* stream);
 int tdist_moe_topk_reduce(int dtype, const void* y, void* out, const int* pair_to_row, const float* weights, int tokens,
                           int topk, int row_bytes, void* stream);
 /* fused top-k reduce + reduce-scatter over token segments (moe_reduce_rs.py:292-376) */

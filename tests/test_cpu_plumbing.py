@@ -58,6 +58,16 @@ def test_tp_moe_cpu():
     run_dist(N + "test_tp_moe", ["--check", "--verify-iters", 1, "-M", 64, "--hidden", 64, "--inter", 32, "-E", 4, "--topk", 2], 2)
 
 
+@pytest.mark.parametrize("world", [2, 4])
+def test_moe_overlap_schedules_cpu(world):
+    """Stage-gated AG + grouped GEMM (per-stage block masks, stage-filtered gather) and the column-chunked MoE + RS give the
+    same results as the per-expert torch loop: the orchestration of the opt-in overlap schedules, on their CPU paths."""
+    run_dist(N + "test_ag_moe", ["--check", "--verify-iters", 2, "--overlap", "-M", 512, "-E", 8, "--topk", 2, "--hidden", 256,
+                                 "--inter", 512], world)
+    run_dist(N + "test_moe_reduce_rs", ["--check", "--verify-iters", 2, "--overlap", "-M", 512, "-E", 8, "--topk", 2,
+                                        "--hidden", 1024, "--inter", 256], world)
+
+
 def test_sp_flash_decode_cpu():
     run_dist(N + "test_sp_decode_attn", ["--check", "--verify-iters", 1, "--kv-len", 256, "--q-heads", 4, "--kv-heads", 2], 2)
 

@@ -86,6 +86,27 @@ def moe_gather_rows(x: torch.Tensor, sort: MoESortResult, out: Optional[torch.Te
     return out
 
 
+def moe_gather_rows_stage(x: torch.Tensor, sort: MoESortResult, block_stage: torch.Tensor, stage: int, out: torch.Tensor,
+                          block_m: int = BLOCK_M) -> torch.Tensor:
+    """``moe_gather_rows`` restricted to the row blocks b with ``block_stage[b] == stage``; other rows of ``out`` are
+    left as they are (the stage-gated AG + grouped GEMM fills ``out`` stage by stage as token shards arrive)."""
+    if not x.is_cuda:
+        rows = int(sort.meta[0])
+        row_stage = torch.repeat_interleave(block_stage[:rows // block_m].long(), block_m)
+        ids = sort.sorted_pair_ids[:rows].long()
+        sel = row_stage == stage
+        pad = sel & (ids >= sort.num_pairs)
+        val = sel & (ids < sort.num_pairs)
+        out[:rows][pad] = 0
+        out[:rows][val] = x[ids[val] // sort.topk]
+        return out
+    _lib.check(_lib.lib().tdist_moe_gather_rows_stage(x.data_ptr(), out.data_ptr(), sort.sorted_pair_ids.data_ptr(),
+                                                      sort.meta.data_ptr(), block_stage.data_ptr(), int(stage), block_m,
+                                                      sort.num_pairs, sort.topk, x.shape[1] * x.element_size(), sort.max_rows,
+                                                      _lib.stream_ptr()), "moe_gather_rows_stage")
+    return out
+
+
 def reduce_topk(y_sorted: torch.Tensor, sort: MoESortResult, weights: Optional[torch.Tensor] = None,
                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[t] = sum_k weights[t, k] * y_sorted[row of pair (t, k)] (fp32 accumulate)."""
@@ -104,24 +125,32 @@ def reduce_topk(y_sorted: torch.Tensor, sort: MoESortResult, weights: Optional[t
     return out
 
 
-def grouped_gemm(a_sorted: torch.Tensor, w: torch.Tensor, sort: MoESortResult, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+def grouped_gemm(a_sorted: torch.Tensor, w: torch.Tensor, sort: MoESortResult, out: Optional[torch.Tensor] = None,
+                 block_expert: Optional[torch.Tensor] = None, num_sms: int = 0) -> torch.Tensor:
     """y[i] = a_sorted[i] @ w[expert(i)]^T; a_sorted [max_rows, K], w [E, N, K] -> [max_rows, N].
-    tcgen05 GEMM engine with a per-128-row-block expert table (padding blocks are skipped on the device)."""
+    tcgen05 GEMM engine with a per-128-row-block expert table (padding blocks are skipped on the device).
+    ``block_expert`` overrides the table of ``sort`` (entries < 0 = skip the block and leave its rows of ``out`` as they
+    are: how the stage-gated AG + MoE computes one arrival stage per launch); ``num_sms`` > 0 limits the grid (leaves SMs to
+    a concurrent reduce-scatter kernel)."""
     import ctypes
 
     E, N, K = w.shape
-    if out is None:
+    fresh = out is None
+    if fresh:
         out = torch.empty((sort.max_rows, N), dtype=a_sorted.dtype, device=a_sorted.device)
+    if block_expert is None:
+        block_expert = sort.block_expert
     if not a_sorted.is_cuda:
-        out.zero_()
+        if fresh:
+            out.zero_()
         for b in range(sort.max_rows // BLOCK_M):
-            e = int(sort.block_expert[b])
+            e = int(block_expert[b])
             if e >= 0:
                 out[b * BLOCK_M:(b + 1) * BLOCK_M] = (a_sorted[b * BLOCK_M:(b + 1) * BLOCK_M].float() @ w[e].float().t()).to(out.dtype)
         return out
     assert a_sorted.is_contiguous() and w.is_contiguous()
     args = _lib.GemmArgs(a=a_sorted.data_ptr(), b=w.data_ptr(), c=out.data_ptr(), M=sort.max_rows, N=N, K=K, lda=K, ldb=K, ldc=N,
-                         dtype=_lib.dtype_code(a_sorted.dtype), block_n=0, group_m=1, num_sms=0, transpose_out=0,
-                         block_expert=sort.block_expert.data_ptr(), num_experts=E, cta_group=1)
+                         dtype=_lib.dtype_code(a_sorted.dtype), block_n=0, group_m=1, num_sms=int(num_sms), transpose_out=0,
+                         block_expert=block_expert.data_ptr(), num_experts=E, cta_group=1)
     _lib.check(_lib.lib().tdist_gemm(ctypes.byref(args), _lib.stream_ptr()), "grouped_gemm")
     return out

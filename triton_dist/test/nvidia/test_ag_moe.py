@@ -14,12 +14,13 @@ if __name__ == "__main__":
     p.add_argument("--inter", type=int, default=1024, help="FFN dim (sharded over ranks)")
     p.add_argument("-E", type=int, default=16)
     p.add_argument("--topk", type=int, default=4)
+    p.add_argument("--overlap", action="store_true", help="stage-gated / column-chunked schedule (transfer overlaps the grouped GEMM)")
     args = p.parse_args()
     group, rank, world = setup()
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     dtype = DTYPES[args.dtype] if dev == "cuda" else torch.float32
     m_loc, n_loc = args.M // world, args.inter // world
-    ctx = create_ag_group_gemm_context(args.M, args.hidden, args.E, args.topk, rank, world, dtype=dtype)
+    ctx = create_ag_group_gemm_context(args.M, args.hidden, args.E, args.topk, rank, world, dtype=dtype, overlap=args.overlap)
     torch.manual_seed(5 + rank)
     w = rand((args.E, n_loc, args.hidden), dtype) * 0.1
     ok = True

@@ -16,12 +16,13 @@ if __name__ == "__main__":
     p.add_argument("--inter", type=int, default=1024, help="FFN dim (sharded over ranks)")
     p.add_argument("-E", type=int, default=16)
     p.add_argument("--topk", type=int, default=4)
+    p.add_argument("--overlap", action="store_true", help="stage-gated / column-chunked schedule (transfer overlaps the grouped GEMM)")
     args = p.parse_args()
     group, rank, world = setup()
     dev = "cuda" if torch.cuda.is_available() else "cpu"
     dtype = DTYPES[args.dtype] if dev == "cuda" else torch.float32
     i_loc, m_loc = args.inter // world, args.M // world
-    ctx = create_moe_rs_context(rank, world, world, args.M, args.hidden, args.E, args.topk, dtype)
+    ctx = create_moe_rs_context(rank, world, world, args.M, args.hidden, args.E, args.topk, dtype, overlap=args.overlap)
     torch.manual_seed(9 + rank)
     w = rand((args.E, args.hidden, i_loc), dtype) * 0.1  # this rank's FFN shard of every expert's down projection
     ok = True

@@ -56,9 +56,10 @@ call. With monotone values a rank that is already in call n+1 cannot be mistaken
 with no barrier in between and the launch can be captured in a CUDA graph. Every fused op of this library uses the same
 trick (``PhaseState`` in symm.cuh keeps the counter on the device).
 
-STEP 5 — the host side of the same protocol: ``set_signal`` / ``wait_eq`` enqueue ``cuStreamWriteValue32`` /
-``cuStreamWaitValue32`` on the current stream: a copy-engine transfer into a peer view followed by ``set_signal`` is a
-put-with-signal without any kernel, and ``wait_eq`` blocks the STREAM (not the CPU) until the flag arrives.
+STEP 5 — the host side of the same protocol: ``set_signal`` / ``wait_eq`` enqueue a flag write / a flag wait on the
+current stream (one-thread kernels by default, so that they can be captured in CUDA graphs; ``use_memops=True`` selects
+``cuStreamWriteValue32`` / ``cuStreamWaitValue32``): a copy into a peer view followed by ``set_signal`` is a
+put-with-signal in stream order, and ``wait_eq`` blocks the STREAM (not the CPU) until the flag arrives.
 """
 import ctypes
 import sys
@@ -119,7 +120,7 @@ data = symm_tensor((1024,), torch.float32)
 flag = symm_tensor((world,), torch.int32)
 nvshmem_barrier_all_on_stream()
 symm_peer_view(data, nxt).fill_(float(rank))                      # put: a fill kernel writing rank nxt's memory
-set_signal(symm_peer_view(flag, nxt)[rank:rank + 1], 1)          # stream-ordered after the put: cuStreamWriteValue32
+set_signal(symm_peer_view(flag, nxt)[rank:rank + 1], 1)          # stream-ordered after the put
 wait_eq(flag[prv:prv + 1], 1, cmp=CMP_GE)                        # my STREAM waits for my left neighbour's signal
 got = data[0].item()                                             # .item() synchronises the stream
 dist_print(f"rank {rank}: host-side put + signal delivered {got} from rank {prv}", allowed_ranks="all")

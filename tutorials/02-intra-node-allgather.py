@@ -15,10 +15,11 @@ be consumed before everything has arrived.
 STEP 1 — copy engines + stream signals (``cp_engine_producer_all_gather_intra_node``). Every rank owns a symmetric
 ``[W * m, K]`` buffer; ``bufs[p]`` is rank p's instance mapped into this process. On a side stream, for every source
 rank: ``cudaMemcpyAsync`` of that rank's shard out of ITS buffer into mine (a pull over NVLink by a copy engine, no SM
-involved), followed by ``cuStreamWriteValue32(signal[src], 1)``. A consumer stream enqueues
-``cuStreamWaitValue32(signal[src])`` before the work that needs shard ``src``: per-shard readiness without a kernel
-and without the host. This is the reference's default producer; its cost is ~2-3 us of launch / DMA set-up per copy
-(W-1 copies), so it is the right tool for LARGE shards when the SMs are busy with a GEMM.
+involved), followed by ``cuStreamWriteValue32(signal[src], epoch)``. A consumer stream enqueues a wait on
+``signal[src]`` before the work that needs shard ``src`` (``wait_eq``: by default a one-thread kernel, which can be
+captured in a CUDA graph; ``use_memops=True`` selects ``cuStreamWaitValue32``): per-shard readiness without the host.
+This is the reference's default producer; its cost is ~2-3 us of launch / DMA set-up per copy (W-1 copies), so it is the
+right tool for LARGE shards when the SMs are busy with a GEMM.
 
 STEP 2 — one push kernel over P2P stores (mode ``push2d`` / ``push3d``): each CTA owns a slice of the shard, loads it once
 and stores it into the same offset of every peer's buffer (``symm_at``), 8 independent 16-byte loads in flight per thread.
@@ -92,7 +93,7 @@ def copy_engine_all_gather():
     cp_engine_producer_all_gather_intra_node(rank, world, x, bufs, ag_stream, sigs, signal_target=epoch)
     for src in range(world):
         if src != rank:
-            wait_eq(sigs[rank][src:src + 1], epoch, cmp=CMP_GE)   # cuStreamWaitValue32: the STREAM waits, not the host
+            wait_eq(sigs[rank][src:src + 1], epoch, cmp=CMP_GE)   # the STREAM waits for the DMA's signal, not the host
             # ... a GEMM over rows [src * m, (src + 1) * m) would be enqueued here ...
     return bufs[rank]
 

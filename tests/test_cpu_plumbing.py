@@ -68,6 +68,12 @@ def test_moe_overlap_schedules_cpu(world):
                                         "--hidden", 1024, "--inter", 256], world)
 
 
+def test_moe_overlap_single_device_cpu():
+    """Stage-gated schedule as every rank of a pretend world of 4 (masks partition the blocks, results bit-identical to the
+    one-shot form) and the chunked MoE + RS pipeline at world size 1."""
+    run_dist(N + "test_moe_overlap_single_gpu", [], 1)
+
+
 def test_sp_flash_decode_cpu():
     run_dist(N + "test_sp_decode_attn", ["--check", "--verify-iters", 1, "--kv-len", 256, "--q-heads", 4, "--kv-heads", 2], 2)
 

@@ -205,3 +205,28 @@ def test_kernel_tile_walk_matches_python_restatement():
     n = lib.tdist_gemm_tile_order(0, 1000, 1032, 1, 0, 128, 8, out, 4096)
     got = {(out[3 * t + 1], out[3 * t + 2]) for t in range(n)}
     assert n == 8 * 9 and got == {(m, c) for m in range(8) for c in range(9)}
+
+
+def test_launch_metadata_labels(monkeypatch):
+    """TDIST_NVTX=1 wraps an op in an NVTX range named after the op with its shape / flops / bytes fields (counterpart of the
+    reference kernels' launch_metadata); without the variable the decorator returns the function itself."""
+    import torch
+
+    import triton_dist.utils as U
+
+    def op(a, b):
+        return a.shape[0] + b.shape[0]
+
+    assert U.launch_metadata("gemm")(op) is op or U._NVTX  # default: no wrapper at all
+    labels = []
+    monkeypatch.setattr(U, "_NVTX", True)
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda s: labels.append(("push", s)))
+    monkeypatch.setattr(torch.cuda.nvtx, "range_pop", lambda: labels.append(("pop", None)))
+    wrapped = U.launch_metadata("gemm", lambda a, b: U.gemm_metadata(a.shape[0], b.shape[0], a.shape[1]))(op)
+    assert wrapped(torch.zeros(4, 8), torch.zeros(6, 8)) == 10
+    assert labels == [("push", "gemm[M=4,N=6,K=8,W=1,flops=384,bytes=208,link_bytes=0]"), ("pop", None)]
+    # a describe() that fails must not break the op
+    labels.clear()
+    assert U.launch_metadata("x", lambda *a: 1 / 0)(op)(torch.zeros(1, 1), torch.zeros(2, 1)) == 3
+    assert labels[0] == ("push", "x")

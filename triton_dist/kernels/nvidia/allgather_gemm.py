@@ -27,6 +27,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import gemm_metadata, launch_metadata
 from ..common_ops import CollectiveState
 from .allgather import AllGatherMethod, get_auto_all_gather_method
 
@@ -45,6 +46,7 @@ def _check_operands(a: torch.Tensor, b: torch.Tensor) -> None:
     assert a.stride(1) == 1 and b.stride(1) == 1, "operands must be K-major (row-major [rows, K])"
 
 
+@launch_metadata("gemm", lambda a, b, *_, **__: gemm_metadata(a.shape[0], b.shape[0], a.shape[1], a.element_size()))
 def gemm_persistent(a: torch.Tensor, b: torch.Tensor, ctx=None, out: Optional[torch.Tensor] = None, block_n: int = 0,
                     num_sms: int = 0, cta_group: int = 0, **_ignored) -> torch.Tensor:
     """C = A @ B^T on the tcgen05 engine (single GPU; reference :656-688)."""
@@ -150,6 +152,8 @@ def torch_ag_gemm(a: torch.Tensor, b: torch.Tensor, group=None) -> torch.Tensor:
     return torch.matmul(full, b.t())
 
 
+@launch_metadata("ag_gemm", lambda a, b, ctx, *_, **__: gemm_metadata(a.shape[0] * ctx.num_ranks, b.shape[0], a.shape[1], a.element_size(), ctx.num_ranks,
+                                                                     (ctx.num_ranks - 1) * a.numel() * a.element_size()))
 def ag_gemm(a: torch.Tensor, b: torch.Tensor, ctx: AllGatherGEMMTensorParallelContext, persistent: bool = True,
             autotune: bool = False, straggler_option=None, use_cooperative: bool = True,
             out: Optional[torch.Tensor] = None) -> torch.Tensor:

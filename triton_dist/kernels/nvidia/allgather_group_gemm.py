@@ -30,6 +30,7 @@ import torch.distributed as dist
 import os
 
 from ...runtime import symm as _symm
+from ...utils import gemm_metadata, launch_metadata
 from ..common_ops import CMP_GE, wait_eq
 from . import low_latency_allgather as _ag
 from .allgather import cp_engine_producer_all_gather_intra_node
@@ -93,6 +94,8 @@ def create_ag_group_gemm_context(max_ntokens: int, hidden: int, num_experts: int
                                                       dtype=dtype, overlap=overlap)
 
 
+@launch_metadata("ag_group_gemm", lambda x, w, ids, ctx, *_, **__: gemm_metadata(x.shape[0] * ctx.num_ranks * ctx.topk, w.shape[1], w.shape[2], x.element_size(),
+                                                                                 ctx.num_ranks, (ctx.num_ranks - 1) * x.numel() * x.element_size()))
 def ag_group_gemm(x: torch.Tensor, w: torch.Tensor, topk_ids: torch.Tensor, ctx: MoEAllGatherGroupGEMMTensorParallelContext):
     """x [M/W, K] local tokens, w [E, N/W, K] local expert shards, topk_ids [M/W, topk] local routing.
     Returns (y_sorted [max_rows, N/W], sort): expert-sorted activations of ALL M tokens and the sort layout."""

@@ -21,6 +21,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import launch_metadata
 from ..allreduce import AllReduceMethod
 from ..common_ops import CollectiveState
 
@@ -115,6 +116,7 @@ def _native_allreduce(ctx: AllReduceContext, x: torch.Tensor, out: torch.Tensor,
                f"all_reduce({method.name})")
 
 
+@launch_metadata("all_reduce", lambda x, *_, **__: {"shape": "x".join(map(str, x.shape)), "bytes": x.numel() * x.element_size()})
 def all_reduce(x: torch.Tensor, output: Optional[torch.Tensor] = None, method: AllReduceMethod = AllReduceMethod.Unknown,
                ctx: Optional[AllReduceContext] = None, max_sm: int = -1, straggler_option=None) -> torch.Tensor:
     """Sum ``x`` over all ranks into ``output``; large inputs are processed in workspace-sized chunks."""

@@ -19,6 +19,7 @@ import torch.distributed as dist
 from ... import _lib
 from ...runtime import symm as _symm
 from ...utils import all_to_all_compat
+from ...utils import launch_metadata
 from ..common_ops import CollectiveState
 
 
@@ -123,6 +124,7 @@ def _torch_dispatch(ctx: EPContext, x: torch.Tensor, ids: torch.Tensor):
     ctx.num_recv.fill_(acc)
 
 
+@launch_metadata("ep_dispatch", lambda ctx, x, ids, *_, **__: {"tokens": x.shape[0], "hidden": x.shape[1], "topk": ids.shape[-1], "W": ctx.world_size})
 def ep_dispatch(ctx: EPContext, x: torch.Tensor, topk_ids: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """x [T, hidden], topk_ids [T, topk] (global expert ids). Returns (recv_buf [capacity, hidden] (first num_recv rows
     valid, ordered by local expert), recv_expert_counts [experts_per_rank], num_recv [1]) — all on the device."""
@@ -148,6 +150,7 @@ def ep_dispatch(ctx: EPContext, x: torch.Tensor, topk_ids: torch.Tensor) -> Tupl
     return ctx.recv_buf, ctx.recv_expert_counts, ctx.num_recv
 
 
+@launch_metadata("ep_combine", lambda ctx, y, *_, **__: {"rows": y.shape[0], "hidden": y.shape[1], "W": ctx.world_size})
 def ep_combine(ctx: EPContext, expert_out: torch.Tensor, topk_weights: Optional[torch.Tensor] = None) -> torch.Tensor:
     """expert_out [>= num_recv, hidden] in dispatch row order -> [T, hidden] = sum_k w[t,k] * expert_out(pair (t,k))."""
     T, ids = ctx._last_tokens, ctx._last_ids

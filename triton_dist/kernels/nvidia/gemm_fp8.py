@@ -13,6 +13,7 @@ from typing import Optional, Tuple
 import torch
 
 from ... import _lib
+from ...utils import gemm_metadata, launch_metadata
 
 FP8 = torch.float8_e4m3fn
 FP8_MAX = 448.0
@@ -50,6 +51,7 @@ def dequant_128x128(w8: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
     return w8.float() * s
 
 
+@launch_metadata("gemm_fp8", lambda a8, sa, b8, *_, **__: gemm_metadata(a8.shape[0], b8.shape[-2], a8.shape[1], 1))
 def gemm_fp8(a8: torch.Tensor, sa: torch.Tensor, b8: torch.Tensor, sb: torch.Tensor, out: Optional[torch.Tensor] = None,
              out_dtype: torch.dtype = torch.bfloat16, block_expert: Optional[torch.Tensor] = None, num_sms: int = 0) -> torch.Tensor:
     """out[M, N] = dequant(a8, sa) @ dequant(b8, sb)^T.

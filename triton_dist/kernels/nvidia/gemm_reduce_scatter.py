@@ -32,6 +32,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import gemm_metadata, launch_metadata
 from .allgather_gemm import _check_operands, _gemm_args
 from .reduce_scatter import ReduceScatter2DContext, create_reduce_scater_2d_ctx, torch_reduce_scatter
 
@@ -79,6 +80,8 @@ def torch_gemm_rs(a: torch.Tensor, b: torch.Tensor, group=None) -> torch.Tensor:
     return torch_reduce_scatter(torch.matmul(a, b.t()), group)
 
 
+@launch_metadata("gemm_rs", lambda a, b, ctx, *_, **__: gemm_metadata(a.shape[0], b.shape[0], a.shape[1], a.element_size(), ctx.world_size,
+                                                                     a.shape[0] * b.shape[0] * a.element_size() * (ctx.world_size - 1) // max(ctx.world_size, 1)))
 def gemm_rs_op(input: torch.Tensor, weight: torch.Tensor, ctx: GEMMReduceScatterTensorParallelContext, persistent: bool = True,
                fuse_scatter: bool = True, output: Optional[torch.Tensor] = None, autotune: bool = False) -> torch.Tensor:
     _check_operands(input, weight)

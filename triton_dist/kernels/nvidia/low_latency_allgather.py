@@ -24,6 +24,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import launch_metadata
 from ..common_ops import CollectiveState
 
 AG_PULL, AG_PUSH, AG_PUSH_MC, AG_LL, AG_LL_MC = range(5)
@@ -161,6 +162,7 @@ _forward_push_numa_2d_ll_kernel = fast_allgather_push_numa_2d_ll
 _forward_push_numa_2d_ll_multinode_kernel = fast_allgather_push_numa_2d_ll_multinode
 
 
+@launch_metadata("fast_allgather", lambda buf, *_, mode="pull", **__: {"mode": mode, "bytes": buf.numel() * buf.element_size()})
 def fast_allgather(symm_buffer: torch.Tensor, ctx: Optional[FastAllGatherContext] = None, rank=None, node=None,
                    num_ranks=None, num_nodes=None, mode: str = "pull") -> torch.Tensor:
     assert mode in FAST_ALLGATHER_FUNC_DISPATCH, f"unknown mode {mode}"

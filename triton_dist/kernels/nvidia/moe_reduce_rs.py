@@ -26,6 +26,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import gemm_metadata, launch_metadata
 from ..common_ops import CollectiveState
 from .moe_utils import MoESortResult, grouped_gemm, reduce_topk
 from .reduce_scatter import torch_reduce_scatter
@@ -107,6 +108,8 @@ def _pick_chunks(hidden: int, want: int) -> int:
     return 1
 
 
+@launch_metadata("moe_reduce_rs", lambda h, w, sort, wts, ctx, *_, **__: gemm_metadata(sort.num_pairs, w.shape[1], w.shape[2], h.element_size(), ctx.world_size,
+                                                                                     sort.num_pairs // sort.topk * w.shape[1] * h.element_size()))
 def run_moe_reduce_rs(h_sorted: torch.Tensor, w: torch.Tensor, sort: MoESortResult, topk_weights: torch.Tensor,
                       ctx: MoEReduceRSContext, n_chunks: int = 4) -> torch.Tensor:
     """h_sorted [max_rows, I/W] (expert-sorted), w [E, H, I/W], topk_weights [M, topk] for ALL tokens.

@@ -21,6 +21,7 @@ import torch.distributed as dist
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import launch_metadata
 from ..common_ops import BarrierAllContext, CollectiveState
 
 
@@ -101,6 +102,7 @@ def torch_reduce_scatter(x: torch.Tensor, group=None) -> torch.Tensor:
     return out
 
 
+@launch_metadata("reduce_scatter", lambda x, ctx, *_, **__: {"M": x.shape[0], "N": x.shape[1], "W": ctx.world_size, "bytes": x.numel() * x.element_size()})
 def reduce_scatter_2d_op(input: torch.Tensor, ctx: ReduceScatter2DContext, output: Optional[torch.Tensor] = None) -> torch.Tensor:
     """output[M/W, N] = sum over ranks of input[rank*M/W:(rank+1)*M/W] (input: [M, N] per rank)."""
     M, N = input.shape

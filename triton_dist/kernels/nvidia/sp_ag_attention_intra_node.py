@@ -20,6 +20,7 @@ import torch.nn.functional as F
 
 from ... import _lib
 from ...runtime import symm as _symm
+from ...utils import launch_metadata
 
 
 @dataclasses.dataclass
@@ -130,6 +131,7 @@ def _gather_kv(ctx, k_shard, v_shard, cu_k, rank, world, zigzag):
     cur.wait_stream(ctx.ag_stream)
 
 
+@launch_metadata("flash_attn_varlen", lambda q, k, *_, **__: {"q": "x".join(map(str, q.shape)), "k": "x".join(map(str, k.shape))})
 def flash_attn_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_q: torch.Tensor, cu_k: torch.Tensor, max_q: int,
                       causal: bool = True, out: Optional[torch.Tensor] = None, scale: Optional[float] = None, rank: int = 0,
                       world: int = 1, zigzag: bool = False, k_batch_stride: int = 0) -> torch.Tensor:

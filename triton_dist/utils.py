@@ -411,6 +411,46 @@ def CUDA_CHECK(err) -> None:
 
 
 # --------------------------------------------------------------------------- profiling
+_NVTX = os.environ.get("TDIST_NVTX", "0") == "1"
+
+
+def launch_metadata(name: str, describe: Optional[Callable[..., dict]] = None):
+    """Name the launches of an op for profilers, the way the reference's kernels carry ``launch_metadata`` (kernel name with
+    M / N / K, flops, bytes: allgather_gemm.py:145-155) for Proton. With ``TDIST_NVTX=1`` every call of the decorated op is
+    wrapped in an NVTX range ``name[k=v,...]`` (visible in ncu / Nsight Systems next to the kernels it launched);
+    ``describe(*args, **kwargs)`` returns the fields (shapes, ``flops``, ``bytes``). Without the variable the decorator
+    returns the function itself: no wrapper, no cost."""
+
+    def deco(fn):
+        if not _NVTX:
+            return fn
+
+        @functools.wraps(fn)
+        def wrapper(*args, **kwargs):
+            if not torch.cuda.is_available():
+                return fn(*args, **kwargs)
+            label = name
+            if describe is not None:
+                try:
+                    label = f"{name}[{','.join(f'{k}={v}' for k, v in describe(*args, **kwargs).items())}]"
+                except Exception:  # noqa: BLE001 - a label must never break the op
+                    pass
+            torch.cuda.nvtx.range_push(label)
+            try:
+                return fn(*args, **kwargs)
+            finally:
+                torch.cuda.nvtx.range_pop()
+
+        return wrapper
+
+    return deco
+
+
+def gemm_metadata(M: int, N: int, K: int, elt: int = 2, world: int = 1, comm_bytes: int = 0) -> dict:
+    """Fields of a GEMM-bearing op: per-rank flops, HBM bytes of the operands and the bytes that cross NVLink."""
+    return {"M": M, "N": N, "K": K, "W": world, "flops": 2 * M * N * K, "bytes": (M * K + N * K + M * N) * elt, "link_bytes": comm_bytes}
+
+
 def get_torch_prof_ctx(do_prof: bool):
     if not do_prof:
         return contextlib.nullcontext()

@@ -88,6 +88,13 @@ def test_mega_suite_cpu():
     run_dist(N + "run_suite", ["--suite", "mega"], 2, timeout=1200)
 
 
+@pytest.mark.parametrize("name", ["test_add", "test_rms_norm", "test_mlp_layer", "test_allreduce", "test_page_attn"])
+def test_mega_per_op_scripts_cpu(name):
+    """The per-op megakernel scripts (same file names as the reference's mega_triton_kernel/test/ops): their oracles agree
+    with the builder's eager fallback, so on a GPU any mismatch points at the task body."""
+    run_dist("triton_dist.mega_triton_kernel.test.ops." + name, [], 2)
+
+
 @pytest.mark.parametrize("world", [2, 4])
 def test_team_split_cpu(world):
     """EP x PP team split, rank translation, strided split (reference test_team_split.py)."""

@@ -230,3 +230,93 @@ def test_launch_metadata_labels(monkeypatch):
     labels.clear()
     assert U.launch_metadata("x", lambda *a: 1 / 0)(op)(torch.zeros(1, 1), torch.zeros(2, 1)) == 3
     assert labels[0] == ("push", "x")
+
+
+class _FakeTensor:
+    def __init__(self, ptr):
+        self._ptr = ptr
+
+    def data_ptr(self):
+        return self._ptr
+
+    def zero_(self):
+        return self
+
+
+def _bare_heap(monkeypatch, nbytes):
+    """A SymmetricHeap object with only its allocator state (no CUDA): alloc / free are pure offset arithmetic."""
+    import torch
+
+    from triton_dist.runtime import symm
+
+    heap = object.__new__(symm.SymmetricHeap)
+    heap.rank, heap.world, heap.nbytes = 0, 1, nbytes
+    heap.base = [1 << 40]
+    heap.device = torch.device("cpu")
+    heap._free, heap._live = [(0, nbytes)], {}
+    monkeypatch.setattr(symm, "tensor_from_ptr", lambda ptr, shape, dtype, device, owner=None: _FakeTensor(ptr))
+    return heap
+
+
+def test_symmetric_heap_allocator_invariants(monkeypatch):
+    """Random alloc / free sequences on the heap's first-fit allocator: live blocks never overlap, stay inside the heap and
+    are 256-byte aligned; freeing everything merges the free list back into one block; exhaustion raises MemoryError.
+    (Every rank runs the same sequence, so identical behaviour = identical offsets = symmetric addresses.)"""
+    import random
+
+    import torch
+
+    nbytes = 1 << 20
+    heap = _bare_heap(monkeypatch, nbytes)
+    rng = random.Random(7)
+    live = {}
+    for step in range(3000):
+        if live and (rng.random() < 0.45 or len(live) > 64):
+            ptr = rng.choice(list(live))
+            heap.free(_FakeTensor(ptr))
+            del live[ptr]
+        else:
+            n = rng.choice([1, 7, 256, 1000, 4096, 40000])
+            try:
+                t = heap.alloc((n,), torch.uint8, zero=bool(rng.getrandbits(1)))
+            except MemoryError:
+                assert sum(live.values()) + n > nbytes // 2  # only a (fragmented) nearly full heap may refuse
+                continue
+            off = t.data_ptr() - heap.base[0]
+            size = (n + 255) // 256 * 256
+            assert off % 256 == 0 and 0 <= off and off + size <= nbytes
+            for o, s in live.items():
+                assert off + size <= o - heap.base[0] or o - heap.base[0] + s <= off, "live blocks overlap"
+            live[t.data_ptr()] = size
+        free_bytes = sum(s for _, s in heap._free)
+        assert free_bytes + sum(live.values()) == nbytes
+        assert all(a[0] + a[1] < b[0] for a, b in zip(heap._free, heap._free[1:])), "free list not sorted / not merged"
+    for ptr in list(live):
+        heap.free(_FakeTensor(ptr))
+    assert heap._free == [(0, nbytes)] and not heap._live
+    import pytest
+
+    with pytest.raises(MemoryError):
+        heap.alloc((nbytes + 1,), torch.uint8)
+    heap.free(_FakeTensor(12345))  # unknown pointer: ignored
+    assert heap._free == [(0, nbytes)]
+
+
+def test_symmetric_heap_same_sequence_same_offsets(monkeypatch):
+    """Two ranks that run the same alloc / free sequence get the same offsets: the property that makes ``symm_at`` pure
+    pointer arithmetic."""
+    import torch
+
+    seqs = []
+    for rank_base in (1 << 40, 5 << 40):
+        heap = _bare_heap(monkeypatch, 1 << 20)
+        heap.base = [rank_base]
+        offs, held = [], []
+        for i, n in enumerate([100, 5000, 300, 70000, 256, 9000]):
+            t = heap.alloc((n,), torch.uint8)
+            held.append(t)
+            offs.append(t.data_ptr() - rank_base)
+            if i % 2 == 1:
+                heap.free(held.pop(0))
+        seqs.append(offs)
+    assert seqs[0] == seqs[1]

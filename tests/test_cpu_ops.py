@@ -320,3 +320,32 @@ def test_symmetric_heap_same_sequence_same_offsets(monkeypatch):
                 heap.free(held.pop(0))
         seqs.append(offs)
     assert seqs[0] == seqs[1]
+
+
+def test_perf_models_reproduce_the_bench_roofline():
+    """gemm_perf_model / comm_perf_model give the roofline that bench.py and profiles/README.md quote for BASELINE config 2
+    at TP8: 0.0763 ms per op = 56 MiB over 770 GB/s (the transfer bounds it, not the FLOPs)."""
+    import torch
+
+    from triton_dist.kernels.nvidia.comm_perf_model import (estimate_all_gather_time_ms, estimate_all_reduce_time_ms,
+                                                            estimate_reduce_scatter_time_ms, fused_op_roofline_ms, get_nvlink_gbps)
+    from triton_dist.kernels.nvidia.gemm_perf_model import estimate_gemm_sol_time_ms, get_dram_gbps, get_tensorcore_tflops
+
+    M, K, N, W = 8192, 4096, 14336, 8
+    link_bytes = (W - 1) * (M // W) * K * 2
+    t_ag = estimate_all_gather_time_ms((M // W) * K * 2, W, gbps=770.0)
+    assert abs(t_ag - link_bytes / (770.0 * 1e6)) < 1e-9 and abs(t_ag - 0.0763) < 5e-4
+    assert abs(estimate_reduce_scatter_time_ms(M * 4096 * 2, W, gbps=770.0) - 0.0763) < 5e-4  # the down projection's partial
+    flops_per_gpu = 2.0 * M * (N // W) * K
+    assert abs(fused_op_roofline_ms(flops_per_gpu, link_bytes, 1699.5, 770.0) - 0.0763) < 5e-4  # link-bound
+    assert fused_op_roofline_ms(flops_per_gpu, 0, 1699.5) == flops_per_gpu / (1699.5 * 1e9)      # compute-bound without traffic
+    assert estimate_all_reduce_time_ms(1 << 26, W, 770.0, nvls=True) < estimate_all_reduce_time_ms(1 << 26, W, 770.0, nvls=False)
+    assert get_nvlink_gbps(measured=False) == 900.0
+    # nominal tables: B200 dense bf16 2.25 PFLOP/s, fp8 twice that; a large square GEMM is compute-bound, a GEMV memory-bound
+    assert get_tensorcore_tflops(torch.bfloat16, "NVIDIA B200", measured=False) == 2250.0
+    assert get_tensorcore_tflops(torch.float8_e4m3fn, "NVIDIA B200", measured=False) == 4500.0
+    assert get_dram_gbps("NVIDIA B200") == 7700.0
+    big = estimate_gemm_sol_time_ms(8192, 8192, 8192, torch.bfloat16, "NVIDIA B200")
+    assert abs(big - 2.0 * 8192**3 / (2250.0 * 1e9)) < 1e-9
+    gemv = estimate_gemm_sol_time_ms(1, 5120, 25600, torch.bfloat16, "NVIDIA B200")
+    assert abs(gemv - (25600 + 5120 * 25600 + 5120) * 2 / (7700.0 * 1e6)) < 1e-9

@@ -99,3 +99,43 @@ def test_mega_per_op_scripts_cpu(name):
 def test_team_split_cpu(world):
     """EP x PP team split, rank translation, strided split (reference test_team_split.py)."""
     run_dist(N + "test_team_split", [], world)
+
+
+def test_model_server_and_chat_cpu():
+    """model_server (2 ranks, random-init Qwen3-0.6B on the builder's eager path) answers a request sent by the chat client:
+    prompt broadcast to all ranks, token-by-token prefill + greedy decode, JSON reply (reference model_server.py / chat.py)."""
+    import os
+    import subprocess
+    import sys
+    import time
+
+    from conftest import ROOT, free_port
+
+    port = free_port()
+    env = dict(os.environ)
+    env["PYTHONPATH"] = str(ROOT) + os.pathsep + env.get("PYTHONPATH", "")
+    env["RANDOM_PARAMS"] = "1"
+    env.setdefault("OMP_NUM_THREADS", "2")
+    server = subprocess.Popen([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                               "127.0.0.1", "--master-port", str(free_port()), "-m",
+                               "triton_dist.mega_triton_kernel.test.models.model_server", "--model", "Qwen/Qwen3-0.6B", "--port", str(port),
+                               "--max-length", "64", "--max-requests", "1"], cwd=str(ROOT), env=env, stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True)
+    try:
+        deadline = time.time() + 600
+        for line in server.stdout:  # wait until rank 0 listens
+            if "model_server listening" in line:
+                break
+            assert time.time() < deadline, "server did not come up"
+        else:
+            raise AssertionError("server exited before listening")
+        client = subprocess.run([sys.executable, "-m", "triton_dist.mega_triton_kernel.test.models.chat", "--port", str(port),
+                                 "--prompt-ids", "11,22,33", "--max-new-tokens", "4"], cwd=str(ROOT), env=env, capture_output=True,
+                                text=True, timeout=600)
+        assert client.returncode == 0, client.stdout + client.stderr
+        ids = eval(client.stdout.strip().splitlines()[-1])  # the client prints the list of generated token ids
+        assert isinstance(ids, list) and len(ids) == 4 and all(isinstance(t, int) and 0 <= t < 151936 for t in ids), client.stdout
+        assert server.wait(timeout=300) == 0
+    finally:
+        if server.poll() is None:
+            server.kill()

@@ -1,0 +1,169 @@
+// sim_runtime.h — the "GPU" of the protocol simulator.
+//  * one OS thread per CTA; the CUDA threads of a CTA are fibers (ucontext) scheduled round-robin on that OS thread, and
+//    __syncthreads() is "yield until every fiber of the CTA has arrived". ThreadSanitizer therefore sees one thread per
+//    CTA: it checks exactly what crosses CTAs and ranks (the flag protocols), reliably — with one OS thread per CUDA thread
+//    a run has thousands of threads, more than the sanitizer's 256 thread slots, and it starts to forget accesses.
+//    (Build with --param=tsan-instrument-func-entry-exit=0: the sanitizer must not keep a shadow call stack across fiber
+//    switches.)
+//  * every rank owns a slice of one contiguous heap (rank p at heap + p * bytes, which is what the VMM mapping gives on the
+//    real node) and issues its launches from its own OS thread, one after the other, like a stream.
+#pragma once
+#include <pthread.h>
+#include <ucontext.h>
+
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <vector>
+
+#include "kernels/common.cuh"
+
+thread_local sim_dim3 threadIdx, blockIdx, blockDim, gridDim;
+thread_local SimCta* sim_cta = nullptr;
+thread_local unsigned sim_rng = 1;
+
+namespace sim {
+
+constexpr size_t kFiberStack = 64 << 10;
+
+struct Fiber {
+  ucontext_t ctx;
+  std::unique_ptr<char[]> stack;
+  bool done = false, at_barrier = false;
+};
+struct CtaRun {
+  const std::function<void()>* kernel;
+  int rank, cta, ctas, threads;
+  SimCta state;
+  ucontext_t sched;
+  std::vector<Fiber> fibers;
+  int cur = 0;
+};
+inline thread_local CtaRun* tl_cta = nullptr;
+
+inline void fiber_main() {
+  CtaRun* r = tl_cta;
+  (*r->kernel)();
+  r->fibers[r->cur].done = true;  // returning resumes the scheduler through uc_link
+}
+
+inline void* cta_thread(void* p) {
+  CtaRun* r = static_cast<CtaRun*>(p);
+  tl_cta = r;
+  sim_cta = &r->state;
+  blockIdx.x = r->cta;
+  blockDim.x = r->threads;
+  gridDim.x = r->ctas;
+  sim_rng = 2654435761u * unsigned(r->rank * 100003 + r->cta * 1009 + 1);
+  r->fibers.resize(r->threads);
+  for (int t = 0; t < r->threads; ++t) {
+    Fiber& f = r->fibers[t];
+    f.stack.reset(new char[kFiberStack]);
+    getcontext(&f.ctx);
+    f.ctx.uc_stack.ss_sp = f.stack.get();
+    f.ctx.uc_stack.ss_size = kFiberStack;
+    f.ctx.uc_link = &r->sched;
+    makecontext(&f.ctx, fiber_main, 0);
+  }
+  for (;;) {
+    int alive = 0, waiting = 0;
+    for (int t = 0; t < r->threads; ++t) {
+      Fiber& f = r->fibers[t];
+      if (f.done) continue;
+      ++alive;
+      if (f.at_barrier) {
+        ++waiting;
+        continue;
+      }
+      r->cur = t;
+      threadIdx.x = t;
+      swapcontext(&r->sched, &f.ctx);  // runs fiber t until it reaches a barrier or returns
+      if (!f.done && f.at_barrier) ++waiting;
+      if (f.done) --alive;
+    }
+    if (alive == 0) break;
+    if (waiting == alive)  // everybody has arrived: open the barrier
+      for (auto& f : r->fibers) f.at_barrier = false;
+  }
+  return nullptr;
+}
+
+}  // namespace sim
+
+// called by the kernel source (declared in the shim)
+void sim_syncthreads() {
+  sim::CtaRun* r = sim::tl_cta;
+  sim::Fiber& f = r->fibers[r->cur];
+  f.at_barrier = true;
+  swapcontext(&f.ctx, &r->sched);
+}
+
+namespace sim {
+
+// One kernel launch of one rank: returns when every CTA has finished (launches of a rank are sequential, like a stream).
+inline void launch(int rank, int ctas, int threads, const std::function<void()>& kernel) {
+  std::vector<std::unique_ptr<CtaRun>> runs(ctas);
+  std::vector<pthread_t> th(ctas);
+  for (int c = 0; c < ctas; ++c) {
+    runs[c].reset(new CtaRun);
+    runs[c]->kernel = &kernel;
+    runs[c]->rank = rank;
+    runs[c]->cta = c;
+    runs[c]->ctas = ctas;
+    runs[c]->threads = threads;
+    if (pthread_create(&th[c], nullptr, cta_thread, runs[c].get()) != 0) {
+      perror("pthread_create");
+      abort();
+    }
+  }
+  for (auto& t : th) pthread_join(t, nullptr);
+}
+
+// The node: W heaps in one allocation, zero-filled once (flags start at zero and are never reset afterwards).
+struct Node {
+  int world;
+  size_t bytes;
+  char* heap;
+  Node(int w, size_t per_rank) : world(w), bytes((per_rank + 4095) / 4096 * 4096) {
+    heap = static_cast<char*>(aligned_alloc(4096, bytes * w));
+    std::memset(heap, 0, bytes * w);
+  }
+  ~Node() { free(heap); }
+  char* base(int r) const { return heap + size_t(r) * bytes; }
+  tdist::SymmCtx ctx(int r) const {
+    tdist::SymmCtx c;
+    for (int q = 0; q < TDIST_MAX_RANKS; ++q) c.base[q] = q < world ? base(q) : nullptr;
+    c.mc_base = nullptr;  // no multicast mapping: kernels take their point-to-point paths
+    c.bytes = bytes;
+    c.rank = r;
+    c.world = world;
+    return c;
+  }
+};
+
+// Every rank runs `driver(rank)` on its own OS thread: ranks issue their launches independently of each other.
+inline void run_ranks(int world, const std::function<void(int)>& driver) {
+  struct Arg {
+    const std::function<void(int)>* f;
+    int r;
+  };
+  std::vector<Arg> args(world);
+  std::vector<pthread_t> th(world);
+  for (int r = 0; r < world; ++r) {
+    args[r] = Arg{&driver, r};
+    pthread_create(&th[r], nullptr, [](void* p) -> void* {
+      auto* a = static_cast<Arg*>(p);
+      (*a->f)(a->r);
+      return nullptr;
+    }, &args[r]);
+  }
+  for (auto& t : th) pthread_join(t, nullptr);
+}
+
+// deterministic pseudo-random test data in [-1, 1)
+inline float unit_rand(unsigned& s) {
+  s = s * 1664525u + 1013904223u;
+  return float(int(s >> 8) & 0xffff) / 32768.f - 1.f;
+}
+
+}  // namespace sim

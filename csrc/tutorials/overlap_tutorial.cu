@@ -49,17 +49,24 @@ __device__ void tile_gemm(const __nv_bfloat16* A, long long lda, int a_rows, con
 //     then block 0 of every remote shard, block 1, ... = the order in which the blocks arrive — and before touching a
 //     remote block they spin on ITS flag only.
 // Flags carry a monotone `epoch` (never reset) and the workspace has two halves used alternately, so calls can follow
-// each other without any barrier between them.
-// ws: [2][W * rows][K] symmetric; flags: [W][blocks] symmetric, zero initialised once.
+// each other without any barrier between them. The halves are `parity_elems` apart — HALF THE WORKSPACE, a constant of the
+// buffer and not a size of this call: with a stride of W * rows * K a call with fewer rows would put its half inside the
+// region a slower rank is still reading for the previous, larger call (csrc/sim/protocol_sim.cc finds exactly that race).
+// The flag of (source rank, block) sits at [rank * flag_blocks + block] with flag_blocks a constant of the flag array as
+// well: a layout that moved with `rows` would let two ranks that are one call apart write the same word under different
+// meanings — a straggler's older epoch could then overwrite a newer one and a waiter would never wake up (the simulator
+// shows both the race and the hang for the reduce-scatter kernel below when the layout follows the call).
+// ws: [2][parity_elems] symmetric, parity_elems >= W * rows * K; flags: [W][flag_blocks] symmetric, zero initialised once.
 __global__ void __launch_bounds__(kThreads) tut_ag_gemm_kernel(SymmCtx ctx, const __nv_bfloat16* a, const __nv_bfloat16* b,
-                                                               __nv_bfloat16* c, __nv_bfloat16* ws, uint32_t* flags, int rows,
-                                                               int N, int K, int push_ctas, PhaseState ps) {
+                                                               __nv_bfloat16* c, __nv_bfloat16* ws, size_t parity_elems,
+                                                               uint32_t* flags, int flag_blocks, int rows, int N, int K,
+                                                               int push_ctas, PhaseState ps) {
   const uint32_t base = phase_begin(ps);  // the same value in every CTA of this launch
   const uint32_t epoch = base + 2;
   const int parity = (epoch >> 1) & 1;
   const int W = ctx.world, rank = ctx.rank;
   const int blocks = (rows + kTile - 1) / kTile;
-  __nv_bfloat16* my_ws = ws + size_t(parity) * W * rows * K;
+  __nv_bfloat16* my_ws = ws + size_t(parity) * parity_elems;
   if (int(blockIdx.x) < push_ctas) {
     // ---- producer ------------------------------------------------------------------------------------------------
     for (int j = blockIdx.x; j < blocks; j += push_ctas) {
@@ -78,7 +85,7 @@ __global__ void __launch_bounds__(kThreads) tut_ag_gemm_kernel(SymmCtx ctx, cons
       __syncthreads();  // every thread's stores are issued ...
       if (threadIdx.x == 0) {
         fence();  // ... and performed system-wide before the flag can be seen (release pattern)
-        for (int p = 1; p < W; ++p) notify(ctx, flags + rank * blocks + j, (rank + p) % W, epoch);
+        for (int p = 1; p < W; ++p) notify(ctx, flags + rank * flag_blocks + j, (rank + p) % W, epoch);
       }
     }
   } else {
@@ -99,7 +106,7 @@ __global__ void __launch_bounds__(kThreads) tut_ag_gemm_kernel(SymmCtx ctx, cons
       }
       const __nv_bfloat16* A = a;
       if (shard != rank) {
-        if (threadIdx.x == 0) wait_ge_sys(flags + shard * blocks + blk, epoch);  // acquire: the block has landed
+        if (threadIdx.x == 0) wait_ge_sys(flags + shard * flag_blocks + blk, epoch);  // acquire: the block has landed
         __syncthreads();
         A = my_ws + size_t(shard) * rows * K;
       }
@@ -125,17 +132,19 @@ __global__ void __launch_bounds__(kThreads) tut_ag_gemm_kernel(SymmCtx ctx, cons
 //            makes the switch fetch the W copies and add them in fp32 (peer loads + adds without a multicast mapping).
 // In this tutorial kernel phase 2 simply follows phase 1 in every CTA; in gemm_sm100.cuh two otherwise idle warps of
 // every GEMM CTA run phase 2 WHILE the tensor core produces later tiles, and a third warp publishes the flags.
-// part: [2][M][N] symmetric; flags: [W][M/W/64][N/64] symmetric, zero initialised once.
+// part: [2][parity_elems] symmetric, parity_elems >= M * N and independent of this call's M (see the note on the workspace
+// halves above); flags: [W][flag_blocks][N/64] symmetric with flag_blocks >= M/W/64 fixed for the buffer, zero initialised once.
 __global__ void __launch_bounds__(kThreads) tut_gemm_rs_kernel(SymmCtx ctx, const __nv_bfloat16* a, const __nv_bfloat16* b,
-                                                               __nv_bfloat16* out, __nv_bfloat16* part, uint32_t* flags, int M,
-                                                               int N, int Kl, PhaseState ps) {
+                                                               __nv_bfloat16* out, __nv_bfloat16* part, size_t parity_elems,
+                                                               uint32_t* flags, int flag_blocks, int M, int N, int Kl,
+                                                               PhaseState ps) {
   const uint32_t base = phase_begin(ps);
   const uint32_t epoch = base + 2;
   const int parity = (epoch >> 1) & 1;
   const int W = ctx.world, rank = ctx.rank;
   const int rows = M / W;
   const int blocks = (rows + kTile - 1) / kTile, tiles_n = (N + kTile - 1) / kTile;
-  __nv_bfloat16* my_part = part + size_t(parity) * M * N;
+  __nv_bfloat16* my_part = part + size_t(parity) * parity_elems;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   // ---- phase 1: produce ------------------------------------------------------------------------------------------
   const int tiles = W * blocks * tiles_n;
@@ -152,13 +161,13 @@ __global__ void __launch_bounds__(kThreads) tut_gemm_rs_kernel(SymmCtx ctx, cons
     __syncthreads();
     if (threadIdx.x == 0) {
       fence();  // my partial tile is visible system-wide before the owner can see the flag
-      notify(ctx, flags + (size_t(rank) * blocks + blk) * tiles_n + n_blk, owner, epoch);
+      notify(ctx, flags + (size_t(rank) * flag_blocks + blk) * tiles_n + n_blk, owner, epoch);
     }
   }
   // ---- phase 2: reduce my segment ---------------------------------------------------------------------------------
   for (int u = blockIdx.x; u < blocks * tiles_n; u += gridDim.x) {
     const int blk = u % blocks, n_blk = u / blocks;
-    if (threadIdx.x < W) wait_ge_sys(flags + (size_t(threadIdx.x) * blocks + blk) * tiles_n + n_blk, epoch);
+    if (threadIdx.x < W) wait_ge_sys(flags + (size_t(threadIdx.x) * flag_blocks + blk) * tiles_n + n_blk, epoch);
     __syncthreads();
     const int r0 = blk * kTile, c0 = n_blk * kTile;
     const int nrows = min(kTile, rows - r0), vpr = min(kTile, N - c0) / 8;  // N % 8 == 0
@@ -185,33 +194,47 @@ __global__ void __launch_bounds__(kThreads) tut_gemm_rs_kernel(SymmCtx ctx, cons
 using namespace tdist;
 
 extern "C" {
-/* tutorials/07: C[W * rows, N] = all_gather(a[rows, K]) * b[N, K]^T. ws symmetric [2][W * rows][K], flags symmetric
- * [W][ceil(rows/64)] zeroed once, phase/done device counters zeroed once. K % 8 == 0. */
-int tdist_tutorial_ag_gemm(const tdist_symm_ctx* ctx, const void* a, const void* b, void* c, void* ws, uint32_t* flags,
-                           uint32_t* phase, uint32_t* done, int rows, int N, int K, int push_ctas, int ctas, void* stream) {
-  if (K % 8 != 0 || push_ctas < 1 || ctas <= push_ctas) {
-    set_error("tutorial_ag_gemm: K % 8 == 0, 1 <= push_ctas < ctas");
+/* tutorials/07: C[W * rows, N] = all_gather(a[rows, K]) * b[N, K]^T. ws symmetric, ws_bytes >= 2 * W * rows * K * 2 (two
+ * halves ws_bytes / 2 apart, whatever `rows` is), flags symmetric [W][flag_blocks] zeroed once (flag_blocks = ceil(largest rows
+ * / 64), the same for every call on these buffers), phase/done device counters zeroed once. K % 8 == 0. */
+int tdist_tutorial_ag_gemm(const tdist_symm_ctx* ctx, const void* a, const void* b, void* c, void* ws, size_t ws_bytes,
+                           uint32_t* flags, int flag_blocks, uint32_t* phase, uint32_t* done, int rows, int N, int K,
+                           int push_ctas, int ctas, void* stream) {
+  if (K % 8 != 0 || push_ctas < 1 || ctas <= push_ctas || flag_blocks < (rows + tut::kTile - 1) / tut::kTile) {
+    set_error("tutorial_ag_gemm: K % 8 == 0, 1 <= push_ctas < ctas, flag_blocks >= ceil(rows / 64)");
     return -1;
   }
   const SymmCtx cx = to_ctx(ctx);
+  const size_t parity_elems = ws_bytes / 2 / sizeof(__nv_bfloat16) / 8 * 8;
+  if (parity_elems < size_t(cx.world) * rows * K) {
+    set_error("tutorial_ag_gemm: workspace too small (need 2 * W * rows * K elements)");
+    return -1;
+  }
   if (cx.world == 1) push_ctas = 0;  // nothing to push
   tut::tut_ag_gemm_kernel<<<ctas, tut::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       cx, static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), static_cast<__nv_bfloat16*>(c),
-      static_cast<__nv_bfloat16*>(ws), flags, rows, N, K, push_ctas, PhaseState{phase, done});
+      static_cast<__nv_bfloat16*>(ws), parity_elems, flags, flag_blocks, rows, N, K, push_ctas, PhaseState{phase, done});
   return check_launch("tutorial_ag_gemm");
 }
-/* tutorials/08: out[M/W, N] = reduce_scatter(a[M, Kl] * b[N, Kl]^T). part symmetric [2][M][N], flags symmetric
- * [W][ceil(M/W/64)][ceil(N/64)] zeroed once. N % 8 == 0, M % W == 0. All CTAs must be co-resident (ctas <= SM count). */
-int tdist_tutorial_gemm_rs(const tdist_symm_ctx* ctx, const void* a, const void* b, void* out, void* part, uint32_t* flags,
-                           uint32_t* phase, uint32_t* done, int M, int N, int Kl, int ctas, void* stream) {
+/* tutorials/08: out[M/W, N] = reduce_scatter(a[M, Kl] * b[N, Kl]^T). part symmetric, part_bytes >= 2 * M * N * 2 (two
+ * halves part_bytes / 2 apart, whatever M is), flags symmetric [W][flag_blocks][ceil(N/64)] zeroed once (flag_blocks =
+ * ceil(largest M / W / 64), N the same for every call on these buffers). N % 8 == 0, M % W == 0. All CTAs must be co-resident (ctas <= SM count). */
+int tdist_tutorial_gemm_rs(const tdist_symm_ctx* ctx, const void* a, const void* b, void* out, void* part, size_t part_bytes,
+                           uint32_t* flags, int flag_blocks, uint32_t* phase, uint32_t* done, int M, int N, int Kl, int ctas,
+                           void* stream) {
   const SymmCtx cx = to_ctx(ctx);
-  if (N % 8 != 0 || M % cx.world != 0 || ctas < 1) {
-    set_error("tutorial_gemm_rs: N % 8 == 0, M % world == 0");
+  if (N % 8 != 0 || M % cx.world != 0 || ctas < 1 || flag_blocks < (M / cx.world + tut::kTile - 1) / tut::kTile) {
+    set_error("tutorial_gemm_rs: N % 8 == 0, M % world == 0, flag_blocks >= ceil(M / world / 64)");
+    return -1;
+  }
+  const size_t parity_elems = part_bytes / 2 / sizeof(__nv_bfloat16) / 8 * 8;
+  if (parity_elems < size_t(M) * N) {
+    set_error("tutorial_gemm_rs: partial buffer too small (need 2 * M * N elements)");
     return -1;
   }
   tut::tut_gemm_rs_kernel<<<ctas, tut::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       cx, static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), static_cast<__nv_bfloat16*>(out),
-      static_cast<__nv_bfloat16*>(part), flags, M, N, Kl, PhaseState{phase, done});
+      static_cast<__nv_bfloat16*>(part), parity_elems, flags, flag_blocks, M, N, Kl, PhaseState{phase, done});
   return check_launch("tutorial_gemm_rs");
 }
 }

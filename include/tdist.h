@@ -302,14 +302,20 @@ int tdist_mega_destroy(void* builder);
  * queue: rank r streams n_items items of item_vecs 16-byte vectors into the `out` of rank r+1 through a queue of `slots`
  *   slots in r+1's heap (queue [slots][item_vecs] int4, full / empty [slots] u32: symmetric, zeroed once; base = sum of
  *   ceil(n_items / slots) over earlier calls on these buffers).
- * ag_gemm: C[W * rows, N] = all_gather(a[rows, K]) * b[N, K]^T, ws symmetric [2][W * rows][K], flags [W][ceil(rows/64)].
- * gemm_rs: out[M/W, N] = reduce_scatter(a[M, Kl] * b[N, Kl]^T), part symmetric [2][M][N], flags [W][M/W/64][N/64]. */
+ * ag_gemm: C[W * rows, N] = all_gather(a[rows, K]) * b[N, K]^T; ws symmetric, two halves ws_bytes / 2 apart, each >=
+ *   W * rows * K elements; flags symmetric [W][flag_blocks], flag_blocks >= ceil(rows / 64).
+ * gemm_rs: out[M/W, N] = reduce_scatter(a[M, Kl] * b[N, Kl]^T); part symmetric, two halves part_bytes / 2 apart, each >=
+ *   M * N elements; flags symmetric [W][flag_blocks][ceil(N/64)], flag_blocks >= ceil(M / W / 64).
+ *   ws_bytes / part_bytes / flag_blocks (and N for gemm_rs) are constants of the buffers: calls of different sizes on the
+ *   same buffers must see the same layout (csrc/sim/protocol_sim.cc shows what happens otherwise). */
 int tdist_tutorial_queue(const tdist_symm_ctx* ctx, const void* in, void* out, void* queue, uint32_t* full, uint32_t* empty,
                          int n_items, int item_vecs, int slots, uint32_t base, void* stream);
-int tdist_tutorial_ag_gemm(const tdist_symm_ctx* ctx, const void* a, const void* b, void* c, void* ws, uint32_t* flags,
-                           uint32_t* phase, uint32_t* done, int rows, int N, int K, int push_ctas, int ctas, void* stream);
-int tdist_tutorial_gemm_rs(const tdist_symm_ctx* ctx, const void* a, const void* b, void* out, void* part, uint32_t* flags,
-                           uint32_t* phase, uint32_t* done, int M, int N, int Kl, int ctas, void* stream);
+int tdist_tutorial_ag_gemm(const tdist_symm_ctx* ctx, const void* a, const void* b, void* c, void* ws, size_t ws_bytes,
+                           uint32_t* flags, int flag_blocks, uint32_t* phase, uint32_t* done, int rows, int N, int K,
+                           int push_ctas, int ctas, void* stream);
+int tdist_tutorial_gemm_rs(const tdist_symm_ctx* ctx, const void* a, const void* b, void* out, void* part, size_t part_bytes,
+                           uint32_t* flags, int flag_blocks, uint32_t* phase, uint32_t* done, int M, int N, int Kl, int ctas,
+                           void* stream);
 
 #ifdef __cplusplus
 }

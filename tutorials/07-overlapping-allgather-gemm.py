@@ -23,7 +23,11 @@ STEP 2 — flags instead of barriers (csrc/device/symm.cuh). The producer of a b
              one thread: wait_ge_sys(flag, epoch); __syncthreads(); loads
          ``epoch`` grows by 2 with every call of the op and is never reset, and the gather workspace has two halves that
          calls use alternately: a rank that is already in call n+1 writes the OTHER half, so no barrier is needed between
-         calls, and the whole op is one CUDA-graph-capturable launch.
+         calls, and the whole op is one CUDA-graph-capturable launch. Two rules make that safe when calls differ in
+         size: the halves are HALF THE WORKSPACE apart and a flag's position depends only on (rank, block) and the size
+         of the flag array, never on the rows of the current call. The CPU protocol simulator (csrc/sim, run under
+         ThreadSanitizer by tests/test_cpu_protocol_sim.py) executes this very kernel source with 2-8 simulated ranks and
+         shows the race, and the lost wake-up, that either shortcut would cause.
 
 STEP 3 — one kernel, two kinds of CTAs (``tut_ag_gemm_kernel``). The first few CTAs push this rank's shard, one 64-row
          block after the other, to every rank and flag each block. All other CTAs compute output tiles in the order the
@@ -74,13 +78,15 @@ heap.barrier_all()                                                   # everybody
 c = torch.empty(world * rows, N, device="cuda", dtype=torch.bfloat16)
 lib = _lib.lib()
 lib.tdist_tutorial_ag_gemm.restype = ctypes.c_int
-lib.tdist_tutorial_ag_gemm.argtypes = [ctypes.c_void_p] * 8 + [ctypes.c_int] * 5 + [ctypes.c_void_p]
+lib.tdist_tutorial_ag_gemm.argtypes = ([ctypes.c_void_p] * 5 + [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 2 +
+                                       [ctypes.c_int] * 5 + [ctypes.c_void_p])
+flag_blocks = (rows + 63) // 64   # a constant of the flag array, like the half-workspace stride: never a size of one call
 
 
 def tutorial_ag_gemm():
     _lib.check(lib.tdist_tutorial_ag_gemm(ctypes.byref(heap.ctx), a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(),
-                                          state.flags_ptr, state.phase_ptr, state.done_ptr, rows, N, K, 4, 132,
-                                          _lib.stream_ptr()), "tutorial_ag_gemm")
+                                          ws.numel() * ws.element_size(), state.flags_ptr, flag_blocks, state.phase_ptr,
+                                          state.done_ptr, rows, N, K, 4, 132, _lib.stream_ptr()), "tutorial_ag_gemm")
     return c
 
 

@@ -72,13 +72,15 @@ heap.barrier_all()
 out = torch.empty(M // world, N, device="cuda", dtype=torch.bfloat16)
 lib = _lib.lib()
 lib.tdist_tutorial_gemm_rs.restype = ctypes.c_int
-lib.tdist_tutorial_gemm_rs.argtypes = [ctypes.c_void_p] * 8 + [ctypes.c_int] * 4 + [ctypes.c_void_p]
+lib.tdist_tutorial_gemm_rs.argtypes = ([ctypes.c_void_p] * 5 + [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 2 +
+                                       [ctypes.c_int] * 4 + [ctypes.c_void_p])
+flag_blocks = (M // world + 63) // 64   # constants of the buffers (see tutorial 7, step 2): the flag layout and the half-buffer stride
 
 
 def tutorial_gemm_rs():
     _lib.check(lib.tdist_tutorial_gemm_rs(ctypes.byref(heap.ctx), a.data_ptr(), b.data_ptr(), out.data_ptr(), part.data_ptr(),
-                                          state.flags_ptr, state.phase_ptr, state.done_ptr, M, N, Kl, 132, _lib.stream_ptr()),
-               "tutorial_gemm_rs")
+                                          part.numel() * part.element_size(), state.flags_ptr, flag_blocks, state.phase_ptr,
+                                          state.done_ptr, M, N, Kl, 132, _lib.stream_ptr()), "tutorial_gemm_rs")
     return out
 
 

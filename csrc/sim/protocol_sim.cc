@@ -13,11 +13,15 @@
 //
 //   protocol_sim queue   <ranks> <items> <item_vecs> <slots> <calls>
 //   protocol_sim ag_gemm <ranks> <rows> <N> <K> <push_ctas> <ctas> <calls> [alternate: 1 = odd calls use rows / div, 2 = even calls] [div = 2]
+//   protocol_sim coll <op> <ranks> <vecs> <ctas> <calls> [alternate]   op: ar1 ar2 ar1mc ar2mc ar1mc_inplace ag_pull ag_push
+//                                                                    ag_mc ag_ll ag_llmc rs rsmc barrier selftest
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
 #include "tutorials/notify_wait_tutorial.cu"  // tdist::tut::tut_queue_kernel
 #include "tutorials/overlap_tutorial.cu"      // tdist::tut::tut_ag_gemm_kernel, tut_gemm_rs_kernel
+#include "kernels/collectives.cu"             // PRODUCTION: barrier, all-reduce x4, all-gather x5, reduce-scatter x2
+#include "kernels/primitives_selftest.cu"     // PRODUCTION: every NVSHMEM-style device primitive of symm.cuh in one kernel
 
 #include <atomic>
 #include <string>
@@ -175,6 +179,145 @@ int run_gemm_rs(int world, int max_M, int N, int Kl, int ctas, int calls, int al
   return g_errors ? 1 : 0;
 }
 
+
+// ------------------------------------------------------------------ production collectives (csrc/kernels/collectives.cu)
+// fp32 payload with small integer values: sums are exact in any order, so results are compared bit for bit. `vecs` =
+// 16-byte vectors of the message (all-reduce), of one rank's shard (all-gather) or of one segment (reduce-scatter); with
+// `alternate` odd (1) or even (2) calls use a third of it on the SAME workspace, flags and phase counters.
+int run_collective(const std::string& op, int world, int max_vecs, int ctas, int calls, int alternate) {
+  using tdist::F32;
+  const bool mc = op.find("mc") != std::string::npos;
+  const bool is_ag = op.rfind("ag_", 0) == 0, is_rs = op.rfind("rs", 0) == 0, is_ll = op.find("ll") != std::string::npos;
+  const size_t W = world;
+  // symmetric layout per rank: [workspace | flags]
+  size_t ws_vecs;
+  if (is_ag) ws_vecs = is_ll ? 2 * W * size_t(max_vecs) * 2 : 2 * W * size_t(max_vecs);  // LL: packets, two parity halves
+  else if (is_rs) ws_vecs = 2 * W * size_t(max_vecs);
+  else ws_vecs = 2 * (W * (size_t(max_vecs) / W + 1 + 2 * ctas) + size_t(max_vecs)) + 2 * W * size_t(max_vecs);
+  const size_t ws_bytes = ws_vecs * 16, flag_words = size_t(ctas + 1) * TDIST_MAX_RANKS;
+  sim::Node node(world, ws_bytes + flag_words * 4 + 64, mc);
+  if (mc && world == 1) {
+    printf("protocol_sim coll %s: needs more than one rank\n", op.c_str());
+    return 0;
+  }
+  auto vecs_of = [=](int call) { return alternate && (call & 1) == (alternate & 1) ? std::max(max_vecs / 3, 1) : max_vecs; };
+  auto val = [](int call, int rank, size_t i) { return float((call * 7 + rank * 3 + int(i % 11)) % 32); };
+  sim::run_ranks(world, [&](int rank) {
+    const tdist::SymmCtx ctx = node.ctx(rank);
+    int4* ws = reinterpret_cast<int4*>(node.base(rank));
+    uint32_t* flags = reinterpret_cast<uint32_t*>(node.base(rank) + ws_bytes);
+    uint32_t state[2] = {0, 0};
+    const tdist::PhaseState ps{state, state + 1};
+    for (int call = 0; call < calls; ++call) {
+      const size_t n = vecs_of(call);
+      const int grid = int(std::min<size_t>(ctas, std::max<size_t>(1, n / 8)));  // as pick_grid: fewer CTAs for small messages
+      if (op == "barrier") {
+        sim::launch(rank, 1, 32, [=] { tdist::barrier_all_kernel(ctx, flags, ps); });
+        continue;
+      }
+      if (is_ag) {
+        std::vector<float> in(n * 4);
+        for (size_t i = 0; i < n * 4; ++i) in[i] = val(call, rank, i);
+        const float* got;
+        std::vector<float> out;
+        if (is_ll) {  // packets go through the context's buffer (two parity halves inside the kernel), result is local
+          out.assign(W * n * 4, -1.f);
+          const int4* inp = reinterpret_cast<const int4*>(in.data());
+          int4* outp = reinterpret_cast<int4*>(out.data());
+          const size_t n64 = n * 2, parity_pkts = ws_bytes / 16 / 2;
+          const int use_mc = op == "ag_llmc";
+          sim::launch(rank, grid, 64, [=] {
+            tdist::allgather_ll_kernel(ctx, reinterpret_cast<const uint2*>(inp), ws, reinterpret_cast<uint2*>(outp), n64, parity_pkts, ps, use_mc);
+          });
+          got = out.data();
+        } else {
+          // in place, as fast_allgather uses it: slot `rank` of a symmetric [W][n] buffer is filled by the caller, all slots
+          // are valid on return. The BUFFER is the caller's: consecutive calls here use two buffers alternately (a caller
+          // that reuses one buffer puts a barrier between the calls, as ag_group_gemm does).
+          int4* symm = ws + size_t(call & 1) * W * max_vecs;
+          int4* mine = symm + size_t(rank) * n;
+          memcpy(mine, in.data(), n * 16);
+          const int mode = op == "ag_pull" ? 0 : op == "ag_push" ? 1 : 2;
+          sim::launch(rank, grid, 64, [=] { tdist::allgather_kernel(ctx, mine, symm, static_cast<int4*>(nullptr), n, flags, ps, mode); });
+          got = reinterpret_cast<const float*>(symm);
+        }
+        for (size_t s = 0; s < W; ++s)
+          for (size_t i = 0; i < n * 4; ++i)
+            if (got[s * n * 4 + i] != val(call, int(s), i)) mismatch(op.c_str(), rank, call, long(s * n * 4 + i), got[s * n * 4 + i], val(call, int(s), i));
+        continue;
+      }
+      if (is_rs) {
+        // in: [W][n] (segment s goes to rank s); out: [n] = sum over ranks of their segment `rank`
+        std::vector<float> in(W * n * 4), out(n * 4, -1.f);
+        for (size_t sgm = 0; sgm < W; ++sgm)
+          for (size_t i = 0; i < n * 4; ++i) in[sgm * n * 4 + i] = val(call, rank, sgm * 5 + i);
+        const int4* inp = reinterpret_cast<const int4*>(in.data());
+        int4* outp = reinterpret_cast<int4*>(out.data());
+        const size_t parity_vecs = ws_bytes / 16 / 2;
+        if (op == "rsmc")
+          sim::launch(rank, grid, 64, [=] { tdist::reduce_scatter_mc_kernel<F32>(ctx, inp, ws, outp, n, parity_vecs, flags, ps); });
+        else
+          sim::launch(rank, grid, 64, [=] { tdist::reduce_scatter_kernel<F32>(ctx, inp, ws, outp, n, parity_vecs, flags, ps); });
+        for (size_t i = 0; i < n * 4; ++i) {
+          float want = 0.f;
+          for (size_t r = 0; r < W; ++r) want += val(call, int(r), size_t(rank) * 5 + i);
+          if (out[i] != want) mismatch(op.c_str(), rank, call, long(i), out[i], want);
+        }
+        continue;
+      }
+      if (op == "selftest") {
+        // csrc/kernels/primitives_selftest.cu: buf [3W + 2] int4, flags [2W + 1]; the kernel writes `epoch` into buf[3W].x
+        // when every primitive delivered what it should
+        int4* buf = ws;
+        const uint32_t epoch = call + 1;
+        sim::launch(rank, 1, 128, [=] { tdist::primitives_selftest_kernel(ctx, buf, flags, epoch); });
+        const int res = buf[3 * W].x;
+        if (res != int(epoch)) mismatch("selftest", rank, call, 0, float(res), float(epoch));
+        // the test script puts a barrier between epochs (nvshmem_barrier_all_on_stream): buffers are reused
+        sim::launch(rank, 1, 32, [=] { tdist::barrier_all_kernel(ctx, flags + 2 * W + 8, ps); });
+        continue;
+      }
+      // all-reduce: in [n], out [n] = sum over ranks
+      std::vector<float> in(n * 4), out(n * 4, -1.f);
+      for (size_t i = 0; i < n * 4; ++i) in[i] = val(call, rank, i);
+      const int4* inp = reinterpret_cast<const int4*>(in.data());
+      int4* outp = reinterpret_cast<int4*>(out.data());
+      if (op == "ar1") {
+        const size_t slot_vecs = ws_bytes / 16 / 2 / W;
+        sim::launch(rank, grid, 64, [=] { tdist::ar_one_shot_push_kernel<F32>(ctx, inp, outp, ws, slot_vecs, flags, ps, n); });
+      } else if (op == "ar2") {
+        const size_t shard_cap = (n + W - 1) / W + 2 * size_t(grid), parity_vecs = ws_bytes / 16 / 2;
+        sim::launch(rank, grid, 64, [=] { tdist::ar_two_shot_push_kernel<F32>(ctx, inp, outp, ws, parity_vecs, shard_cap, flags, ps, n); });
+      } else if (op == "ar1mc" || op == "ar2mc") {
+        const size_t parity_vecs = ws_bytes / 16 / 2;
+        if (op == "ar1mc")
+          sim::launch(rank, grid, 64, [=] { tdist::ar_one_shot_mc_kernel<F32>(ctx, inp, outp, ws, parity_vecs, flags, ps, n, 0); });
+        else
+          sim::launch(rank, grid, 64, [=] { tdist::ar_two_shot_mc_kernel<F32>(ctx, inp, outp, ws, parity_vecs, flags, ps, n, 0); });
+      } else if (op == "ar1mc_inplace" || op == "ar2mc_inplace") {
+        // the caller's data already lives in the symmetric buffer (GEMV + all-reduce of the decode path): no copy-in, a
+        // closing barrier keeps peers from overwriting it while others still read
+        memcpy(ws, in.data(), n * 16);
+        if (op == "ar1mc_inplace")
+          sim::launch(rank, grid, 64, [=] { tdist::ar_one_shot_mc_kernel<F32>(ctx, ws, outp, ws, 0, flags, ps, n, 1); });
+        else
+          sim::launch(rank, grid, 64, [=] { tdist::ar_two_shot_mc_kernel<F32>(ctx, ws, outp, ws, 0, flags, ps, n, 1); });
+      } else {
+        fprintf(stderr, "unknown collective %s\n", op.c_str());
+        exit(2);
+      }
+      for (size_t i = 0; i < n * 4; ++i) {
+        float want = 0.f;
+        for (size_t r = 0; r < W; ++r) want += val(call, int(r), i);
+        if (out[i] != want) mismatch(op.c_str(), rank, call, long(i), out[i], want);
+      }
+    }
+  });
+  printf("protocol_sim coll %s: %d ranks x %d calls, %d vecs%s, up to %d CTAs: %s\n", op.c_str(), world, calls, max_vecs,
+         alternate ? " (alternating with a third)" : "", ctas, g_errors ? "DATA MISMATCH" : "data ok");
+  return g_errors ? 1 : 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -182,7 +325,8 @@ int main(int argc, char** argv) {
   const std::string what = argc > 1 ? argv[1] : "queue";
   if (what == "queue") return run_queue(arg(2, 3), arg(3, 11), arg(4, 300), arg(5, 3), arg(6, 3));
   if (what == "ag_gemm") return run_ag_gemm(arg(2, 3), arg(3, 96), arg(4, 72), arg(5, 32), arg(6, 2), arg(7, 5), arg(8, 3), arg(9, 0), arg(10, 2));
+  if (what == "coll") return run_collective(argc > 2 ? argv[2] : "ar1", arg(3, 3), arg(4, 96), arg(5, 3), arg(6, 3), arg(7, 0));
   if (what == "gemm_rs") return run_gemm_rs(arg(2, 3), arg(3, 3 * 96), arg(4, 72), arg(5, 32), arg(6, 4), arg(7, 3), arg(8, 0), arg(9, 2));
-  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs [sizes...]\n");
+  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll [sizes...]\n");
   return 2;
 }

@@ -1,0 +1,191 @@
+// Host stand-in for csrc/device/ptx.cuh, used by the protocol simulator: the same function names, implemented with C++
+// atomics and plain accesses so that ThreadSanitizer checks the protocols of the code that calls them.
+//   payload:  ld_v4 / ld_nc_v4 / st_v4                      plain 16-byte accesses (what the sanitizer watches)
+//   flags:    st_release_sys / red_add_release_sys          atomic, release        (relaxed with -DTDIST_SIM_BREAK_RELEASE:
+//             ld_acquire_sys / ld_acquire_gpu               atomic, acquire         the negative control)
+//             ld_relaxed_sys / ld_volatile                  atomic, relaxed
+//   packets:  st_relaxed_sys_v4 / ld_volatile_v4            two relaxed 8-byte atomics {data, flag}: the LL protocol's unit
+//   fences:   compiler barriers — ThreadSanitizer does not model stand-alone fences; the order it checks is carried by the
+//             release store that follows a fence and the acquire load that precedes the data loads, as on the device
+//   NVLS:     multimem_st_* writes every rank's copy, multimem_ld_reduce_* reads every rank's copy and adds in fp32
+// Every flag poll yields to the sibling CUDA threads of the CTA (they are fibers of one OS thread).
+#pragma once
+#include <cuda_runtime.h>
+
+struct SimMc {  // the simulated node's multicast window (set by sim::Node when multicast is enabled)
+  char* mc_base = nullptr;
+  char* heap = nullptr;
+  size_t bytes = 0;
+  int world = 0;
+};
+extern SimMc sim_mc;
+
+namespace tdist {
+namespace ptx {
+
+#ifdef TDIST_SIM_BREAK_RELEASE
+constexpr int kRelease = __ATOMIC_RELAXED, kAcquire = __ATOMIC_RELAXED;
+#else
+constexpr int kRelease = __ATOMIC_RELEASE, kAcquire = __ATOMIC_ACQUIRE;
+#endif
+
+inline int laneid() { return int(threadIdx.x & 31u); }
+inline unsigned long long globaltimer() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (unsigned long long)ts.tv_sec * 1000000000ull + ts.tv_nsec;
+}
+
+// ---- payload
+inline int4 ld_v4(const void* p) { return *static_cast<const int4*>(p); }
+inline int4 ld_nc_v4(const void* p) { return *static_cast<const int4*>(p); }
+inline void st_v4(void* p, const int4& v) { *static_cast<int4*>(p) = v; }
+
+// ---- flags
+inline void st_release_sys(uint32_t* p, uint32_t v) {
+  sim_jitter();
+  sim_straggle(sim_rank);
+  __atomic_store_n(p, v, kRelease);
+}
+inline void st_release_gpu(uint32_t* p, uint32_t v) { st_release_sys(p, v); }
+inline void st_relaxed_sys(uint32_t* p, uint32_t v) { __atomic_store_n(p, v, __ATOMIC_RELAXED); }
+inline void red_add_release_sys(uint32_t* p, uint32_t v) {
+  sim_jitter();
+  sim_straggle(sim_rank);
+  __atomic_fetch_add(p, v, kRelease);
+}
+inline uint32_t atom_add_acq_rel_gpu(uint32_t* p, uint32_t v) { return __atomic_fetch_add(p, v, __ATOMIC_ACQ_REL); }
+inline uint32_t ld_acquire_sys(const uint32_t* p) {
+  sim_yield();
+  return __atomic_load_n(p, kAcquire);
+}
+inline uint32_t ld_acquire_gpu(const uint32_t* p) { return ld_acquire_sys(p); }
+inline uint32_t ld_relaxed_sys(const uint32_t* p) {
+  sim_yield();
+  return __atomic_load_n(p, __ATOMIC_RELAXED);
+}
+inline uint32_t ld_volatile(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
+
+// ---- fences
+inline void fence_acq_rel_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
+inline void fence_acq_rel_gpu() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
+inline void fence_sc_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
+
+// ---- LL packets: a 16-byte packet is {d0, flag, d1, flag}; each 8-byte half carries its own flag
+inline void st_relaxed_sys_v4(void* p, const int4& v) {
+  uint64_t h[2];
+  memcpy(h, &v, 16);
+  __atomic_store_n(static_cast<uint64_t*>(p), h[0], __ATOMIC_RELAXED);
+  __atomic_store_n(static_cast<uint64_t*>(p) + 1, h[1], __ATOMIC_RELAXED);
+}
+inline int4 ld_volatile_v4(const void* p) {
+  sim_yield();
+  uint64_t h[2];
+  h[0] = __atomic_load_n(static_cast<const uint64_t*>(p), __ATOMIC_RELAXED);
+  h[1] = __atomic_load_n(static_cast<const uint64_t*>(p) + 1, __ATOMIC_RELAXED);
+  int4 v;
+  memcpy(&v, h, 16);
+  return v;
+}
+
+// ---- 16-bit float packing
+inline uint16_t f32_to_f16(float f) {
+  uint32_t x;
+  memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  int e = int((x >> 23) & 0xff) - 127 + 15;
+  uint32_t m = x & 0x7fffffu;
+  if (e >= 31) return uint16_t(sign | 0x7c00u | (((x & 0x7fffffffu) > 0x7f800000u) ? 0x200u : 0u));
+  if (e <= 0) {
+    if (e < -10) return uint16_t(sign);
+    m |= 0x800000u;
+    const int shift = 14 - e;
+    uint32_t r = m >> shift;
+    const uint32_t rem = m & ((1u << shift) - 1), half = 1u << (shift - 1);
+    if (rem > half || (rem == half && (r & 1))) ++r;
+    return uint16_t(sign | r);
+  }
+  uint32_t r = (uint32_t(e) << 10) | (m >> 13);
+  const uint32_t rem = m & 0x1fffu;
+  if (rem > 0x1000u || (rem == 0x1000u && (r & 1))) ++r;
+  return uint16_t(sign | r);
+}
+inline float f16_to_f32(uint16_t h) {
+  const uint32_t sign = uint32_t(h & 0x8000u) << 16;
+  int e = (h >> 10) & 0x1f;
+  uint32_t m = h & 0x3ffu, x;
+  if (e == 0) {
+    if (m == 0) {
+      x = sign;
+    } else {
+      e = 1;
+      while (!(m & 0x400u)) {
+        m <<= 1;
+        --e;
+      }
+      x = sign | (uint32_t(e + 112) << 23) | ((m & 0x3ffu) << 13);
+    }
+  } else if (e == 31) {
+    x = sign | 0x7f800000u | (m << 13);
+  } else {
+    x = sign | (uint32_t(e + 112) << 23) | (m << 13);
+  }
+  float f;
+  memcpy(&f, &x, 4);
+  return f;
+}
+inline uint32_t pack_bf16x2(float lo, float hi) { return uint32_t(__float2bfloat16(lo).v) | (uint32_t(__float2bfloat16(hi).v) << 16); }
+inline float2 unpack_bf16x2(uint32_t u) {
+  return make_float2(__bfloat162float(__nv_bfloat16{uint16_t(u & 0xffffu)}), __bfloat162float(__nv_bfloat16{uint16_t(u >> 16)}));
+}
+inline uint32_t pack_f16x2(float lo, float hi) { return uint32_t(f32_to_f16(lo)) | (uint32_t(f32_to_f16(hi)) << 16); }
+inline float2 unpack_f16x2(uint32_t u) { return make_float2(f16_to_f32(uint16_t(u & 0xffffu)), f16_to_f32(uint16_t(u >> 16))); }
+
+// ---- NVLS emulation: `mc` is an address inside the node's multicast window
+inline char* mc_copy(const void* mc, int rank) {
+  return sim_mc.heap + size_t(rank) * sim_mc.bytes + (static_cast<const char*>(mc) - sim_mc.mc_base);
+}
+inline void multimem_st_v4(void* mc, const int4& v) {
+  for (int r = 0; r < sim_mc.world; ++r) st_relaxed_sys_v4(mc_copy(mc, r), v);  // also carries LL packets
+}
+inline void multimem_st_b32(void* mc, uint32_t v) {
+  sim_jitter();
+  sim_straggle(sim_rank);
+  for (int r = 0; r < sim_mc.world; ++r) __atomic_store_n(reinterpret_cast<uint32_t*>(mc_copy(mc, r)), v, kRelease);
+}
+inline void multimem_red_add_u32(void* mc, uint32_t v) {
+  for (int r = 0; r < sim_mc.world; ++r) __atomic_fetch_add(reinterpret_cast<uint32_t*>(mc_copy(mc, r)), v, kRelease);
+}
+template <typename Unpack, typename PackF>
+inline int4 mc_reduce16(const void* mc, Unpack unpack, PackF pack) {
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int r = 0; r < sim_mc.world; ++r) {
+    const int4 v = ld_v4(mc_copy(mc, r));
+    const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = unpack(u[i]);
+      acc[2 * i] += f.x;
+      acc[2 * i + 1] += f.y;
+    }
+  }
+  int4 out;
+  uint32_t* o = reinterpret_cast<uint32_t*>(&out);
+  for (int i = 0; i < 4; ++i) o[i] = pack(acc[2 * i], acc[2 * i + 1]);
+  return out;
+}
+inline int4 multimem_ld_reduce_bf16x8(const void* mc) { return mc_reduce16(mc, unpack_bf16x2, pack_bf16x2); }
+inline int4 multimem_ld_reduce_f16x8(const void* mc) { return mc_reduce16(mc, unpack_f16x2, pack_f16x2); }
+inline int4 multimem_ld_reduce_f32x4(const void* mc) {
+  float acc[4] = {0, 0, 0, 0};
+  for (int r = 0; r < sim_mc.world; ++r) {
+    const int4 v = ld_v4(mc_copy(mc, r));
+    acc[0] += __int_as_float(v.x);
+    acc[1] += __int_as_float(v.y);
+    acc[2] += __int_as_float(v.z);
+    acc[3] += __int_as_float(v.w);
+  }
+  return make_int4(__float_as_int(acc[0]), __float_as_int(acc[1]), __float_as_int(acc[2]), __float_as_int(acc[3]));
+}
+
+}  // namespace ptx
+}  // namespace tdist

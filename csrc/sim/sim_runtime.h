@@ -11,16 +11,22 @@
 #include <pthread.h>
 #include <ucontext.h>
 
+#include <algorithm>
 #include <cstring>
 #include <functional>
 #include <memory>
 #include <vector>
 
-#include "kernels/common.cuh"
+#include "kernels/common.cuh"  // the REAL csrc/kernels/common.cuh (+ device/symm.cuh), staged next to the host ptx.cuh
 
 thread_local sim_dim3 threadIdx, blockIdx, blockDim, gridDim;
 thread_local SimCta* sim_cta = nullptr;
 thread_local unsigned sim_rng = 1;
+thread_local int sim_rank = 0;
+SimMc sim_mc;
+namespace tdist {
+void set_error(const std::string& msg) { fprintf(stderr, "tdist error: %s\n", msg.c_str()); }
+}  // namespace tdist
 
 namespace sim {
 
@@ -29,7 +35,7 @@ constexpr size_t kFiberStack = 64 << 10;
 struct Fiber {
   ucontext_t ctx;
   std::unique_ptr<char[]> stack;
-  bool done = false, at_barrier = false;
+  bool done = false, at_barrier = false, at_warp = false;
 };
 struct CtaRun {
   const std::function<void()>* kernel;
@@ -51,6 +57,7 @@ inline void* cta_thread(void* p) {
   CtaRun* r = static_cast<CtaRun*>(p);
   tl_cta = r;
   sim_cta = &r->state;
+  sim_rank = r->rank;
   blockIdx.x = r->cta;
   blockDim.x = r->threads;
   gridDim.x = r->ctas;
@@ -75,6 +82,7 @@ inline void* cta_thread(void* p) {
         ++waiting;
         continue;
       }
+      if (f.at_warp) continue;
       r->cur = t;
       threadIdx.x = t;
       swapcontext(&r->sched, &f.ctx);  // runs fiber t until it reaches a barrier or returns
@@ -84,18 +92,40 @@ inline void* cta_thread(void* p) {
     if (alive == 0) break;
     if (waiting == alive)  // everybody has arrived: open the barrier
       for (auto& f : r->fibers) f.at_barrier = false;
+    for (int w0 = 0; w0 < r->threads; w0 += 32) {  // warp barriers: all live lanes of a warp have arrived
+      bool open = true, any = false;
+      for (int t = w0; t < std::min(w0 + 32, r->threads); ++t) {
+        const Fiber& f = r->fibers[t];
+        if (f.done) continue;
+        any = true;
+        open = open && f.at_warp;
+      }
+      if (any && open)
+        for (int t = w0; t < std::min(w0 + 32, r->threads); ++t) r->fibers[t].at_warp = false;
+    }
   }
   return nullptr;
 }
 
 }  // namespace sim
 
-// called by the kernel source (declared in the shim)
+// called by the kernel sources through the CUDA stand-ins of stub/cuda_runtime.h
 void sim_syncthreads() {
   sim::CtaRun* r = sim::tl_cta;
   sim::Fiber& f = r->fibers[r->cur];
   f.at_barrier = true;
   swapcontext(&f.ctx, &r->sched);
+}
+void sim_syncwarp() {
+  sim::CtaRun* r = sim::tl_cta;
+  sim::Fiber& f = r->fibers[r->cur];
+  f.at_warp = true;
+  swapcontext(&f.ctx, &r->sched);
+}
+void sim_yield() {  // a polling thread lets its siblings run: on the GPU they run in parallel
+  sim::CtaRun* r = sim::tl_cta;
+  if (r == nullptr) return;
+  swapcontext(&r->fibers[r->cur].ctx, &r->sched);
 }
 
 namespace sim {
@@ -124,16 +154,24 @@ struct Node {
   int world;
   size_t bytes;
   char* heap;
-  Node(int w, size_t per_rank) : world(w), bytes((per_rank + 4095) / 4096 * 4096) {
+  char* mc_window = nullptr;  // address range that stands for the NVLS multicast mapping (never dereferenced)
+  Node(int w, size_t per_rank, bool multicast = false) : world(w), bytes((per_rank + 4095) / 4096 * 4096) {
     heap = static_cast<char*>(aligned_alloc(4096, bytes * w));
     std::memset(heap, 0, bytes * w);
+    if (multicast && w > 1) {
+      mc_window = static_cast<char*>(aligned_alloc(4096, bytes));
+      sim_mc = SimMc{mc_window, heap, bytes, w};
+    }
   }
-  ~Node() { free(heap); }
+  ~Node() {
+    free(heap);
+    free(mc_window);
+  }
   char* base(int r) const { return heap + size_t(r) * bytes; }
   tdist::SymmCtx ctx(int r) const {
     tdist::SymmCtx c;
     for (int q = 0; q < TDIST_MAX_RANKS; ++q) c.base[q] = q < world ? base(q) : nullptr;
-    c.mc_base = nullptr;  // no multicast mapping: kernels take their point-to-point paths
+    c.mc_base = mc_window;  // nullptr: kernels take their point-to-point paths
     c.bytes = bytes;
     c.rank = r;
     c.world = world;

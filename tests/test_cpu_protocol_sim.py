@@ -1,6 +1,11 @@
-"""Flag-protocol checker: the tutorial-size distributed kernels (csrc/tutorials/*.cu — the queue of tutorial 1 and the two
-overlap protocols of tutorials 7 / 8, which the production GEMM kernels follow) are compiled for the CPU against a host
-stand-in of the device headers and run with 1-8 simulated ranks in one process under ThreadSanitizer (csrc/sim/).
+"""Flag-protocol checker: device code of this library is compiled for the CPU and run with 1-8 simulated ranks in one process
+under ThreadSanitizer (csrc/sim/):
+  * the PRODUCTION collectives of csrc/kernels/collectives.cu (barrier, 4 all-reduces, 5 all-gathers incl. the LL packet
+    protocol, 2 reduce-scatters; NVLS emulated by reading / writing every rank's copy) and primitives_selftest.cu (every
+    NVSHMEM-style primitive of csrc/device/symm.cuh), on top of the REAL symm.cuh and common.cuh;
+  * the tutorial-size kernels (csrc/tutorials/*.cu — the queue of tutorial 1 and the two overlap protocols of tutorials
+    7 / 8, which the production tcgen05 GEMM kernels follow).
+Only csrc/device/ptx.cuh (inline PTX) and <cuda_runtime.h> are replaced by host stand-ins.
 
 What a pass means: for every payload access of every rank there is a release / acquire chain through the flags (no data
 race), nobody waits for a flag that never comes (no 60 s wait bound), and the results equal a host computation — over
@@ -21,11 +26,13 @@ SIM = ROOT / "csrc" / "sim"
 
 
 def _stage(dst: Path) -> None:
-    """Copy the kernel sources next to the host shim. Two mechanical edits: cut the file before its launch wrappers (they use
-    <<< >>>), and turn `__shared__ T a[..], b[..];` into references to per-CTA buffers."""
-    (dst / "kernels").mkdir(parents=True)
-    (dst / "tutorials").mkdir()
-    shutil.copy(SIM / "shim" / "kernels" / "common.cuh", dst / "kernels" / "common.cuh")
+    """Lay the sources out as in the repository, with the host ptx.cuh in place of the device one. The kernel files are
+    copied with two mechanical edits: cut before their launch wrappers (they use <<< >>>), and `__shared__ T a[..], b[..];`
+    becomes references to per-CTA buffers. csrc/kernels/common.cuh and csrc/device/symm.cuh are the REAL ones."""
+    for d in ("include", "csrc/device", "csrc/kernels", "csrc/tutorials"):
+        (dst / d).mkdir(parents=True)
+    shutil.copy(ROOT / "include" / "tdist.h", dst / "include" / "tdist.h")
+    shutil.copy(SIM / "shim" / "device" / "ptx.cuh", dst / "csrc" / "device" / "ptx.cuh")
 
     def shared(m):
         out = []
@@ -35,15 +42,23 @@ def _stage(dst: Path) -> None:
             out.append(f"typedef {m.group(1)} {name}_sim_t{decl[len(name):]}; SIM_SHARED({name}_sim_t, {name});")
         return " ".join(out)
 
-    for name in ("notify_wait_tutorial.cu", "overlap_tutorial.cu"):
-        src = (ROOT / "csrc" / "tutorials" / name).read_text()
-        src = src[:src.index("using namespace tdist;")]
-        (dst / "tutorials" / name).write_text(re.sub(r"__shared__\s+(\w+)\s+([^;]+);", shared, src))
+    def copy(rel, cut):
+        src = (ROOT / "csrc" / rel).read_text()
+        if cut:
+            src = src[:min(i for i in (src.find("\nusing namespace tdist;"), src.find('\nextern "C"')) if i >= 0)]
+        (dst / "csrc" / rel).write_text(re.sub(r"__shared__\s+(\w+)\s+([^;]+);", shared, src))
+
+    copy("device/symm.cuh", False)
+    copy("kernels/common.cuh", False)
+    for rel in ("tutorials/notify_wait_tutorial.cu", "tutorials/overlap_tutorial.cu", "kernels/collectives.cu",
+                "kernels/primitives_selftest.cu"):
+        copy(rel, True)
 
 
 def _build(stage_dir: Path, out: Path, *defines: str) -> None:
     cmd = ["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "--param=tsan-instrument-func-entry-exit=0", *defines,
-           f"-I{stage_dir}", f"-I{SIM}", "-x", "c++", str(SIM / "protocol_sim.cc"), "-o", str(out), "-pthread"]
+           f"-I{stage_dir / 'csrc'}", f"-I{SIM / 'stub'}", f"-I{SIM}", "-x", "c++", str(SIM / "protocol_sim.cc"), "-o", str(out),
+           "-pthread"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
 
@@ -82,6 +97,16 @@ CLEAN = [
 ]
 
 
+# production collectives: op, ranks, 16-byte vectors, CTAs, calls, alternate (1 / 2: odd / even calls use a third of the size)
+COLLECTIVES = [("coll", op, 3, 96, 3, 4) for op in ("barrier", "ar1", "ar2", "ar1mc", "ar2mc", "ar1mc_inplace", "ar2mc_inplace",
+                                                     "ag_pull", "ag_push", "ag_mc", "ag_ll", "ag_llmc", "rs", "rsmc", "selftest")]
+COLLECTIVES += [("coll", op, 4, 120, 3, 6, alt) for op in ("ar1", "ar2", "ar1mc", "ar2mc", "ag_ll", "ag_llmc", "rs", "rsmc")
+                for alt in (1, 2)]
+COLLECTIVES += [("coll", "ar2mc", 8, 64, 2, 3, 1), ("coll", "selftest", 8, 64, 1, 3), ("coll", "ar1", 1, 40, 2, 2),
+                ("coll", "rs", 2, 8, 4, 3)]
+CLEAN += COLLECTIVES
+
+
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
 def test_protocols_are_race_free(sims, case):
     rc, out = _run(sims[0], case)
@@ -97,12 +122,17 @@ def test_straggler_with_changing_sizes(sims):
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     rc, out = _run(sims[0], ("ag_gemm", 4, 192, 40, 16, 1, 3, 3, 1, 3), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "10"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
+    for op in ("ar2", "rsmc", "ag_llmc"):  # production collectives, 8 ranks, alternating sizes, one rank 5 ms late per flag
+        rc, out = _run(sims[0], ("coll", op, 8, 64, 2, 3, 1), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
+        assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
 
 
-@pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2)],
-                         ids=lambda c: c[0])
+@pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
+                                  ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2)],
+                         ids=lambda c: "-".join(map(str, c[:2])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
     rc, out = _run(sims[1], case)
     assert "ThreadSanitizer: data race" in out, out[-2000:]
-    assert re.search(r"(notify_wait|overlap)_tutorial\.cu:\d+", out), "the report should point into the kernel source"
+    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest)\.cu:\d+|symm\.cuh:\d+|ptx\.cuh:\d+", out), \
+        "the report should point into the device sources"

@@ -15,6 +15,10 @@
 //   protocol_sim ag_gemm <ranks> <rows> <N> <K> <push_ctas> <ctas> <calls> [alternate: 1 = odd calls use rows / div, 2 = even calls] [div = 2]
 //   protocol_sim coll <op> <ranks> <vecs> <ctas> <calls> [alternate]   op: ar1 ar2 ar1mc ar2mc ar1mc_inplace ag_pull ag_push
 //                                                                    ag_mc ag_ll ag_llmc rs rsmc barrier selftest
+//   protocol_sim moe_utils <tokens> <topk> <experts> <ranks> <row_vecs>      (one simulated GPU: functional check)
+//   protocol_sim moe_rs <ranks> <tokens> <topk> <row_vecs> <ctas> <calls> [alternate]
+//   protocol_sim a2a <ranks> <max rows per peer> <row_vecs> <experts per rank> <ctas per peer> <calls>
+//   protocol_sim ep <ranks> <tokens> <hidden> <experts> <ctas> <calls> [fp8]
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -22,6 +26,8 @@
 #include "tutorials/overlap_tutorial.cu"      // tdist::tut::tut_ag_gemm_kernel, tut_gemm_rs_kernel
 #include "kernels/collectives.cu"             // PRODUCTION: barrier, all-reduce x4, all-gather x5, reduce-scatter x2
 #include "kernels/primitives_selftest.cu"     // PRODUCTION: every NVSHMEM-style device primitive of symm.cuh in one kernel
+#include "kernels/moe.cu"                     // PRODUCTION: MoE align / sort, tile swizzle, gathers, top-k reduce (+ reduce-scatter)
+#include "kernels/ep_a2a.cu"                  // PRODUCTION: low-latency all-to-all, EP counts / dispatch (bf16, fp8) / combine
 
 #include <atomic>
 #include <string>
@@ -320,13 +326,19 @@ int run_collective(const std::string& op, int world, int max_vecs, int ctas, int
 
 }  // namespace
 
+#include "moe_ep_scenarios.h"
+
 int main(int argc, char** argv) {
   auto arg = [&](int i, int dflt) { return argc > i ? atoi(argv[i]) : dflt; };
   const std::string what = argc > 1 ? argv[1] : "queue";
   if (what == "queue") return run_queue(arg(2, 3), arg(3, 11), arg(4, 300), arg(5, 3), arg(6, 3));
   if (what == "ag_gemm") return run_ag_gemm(arg(2, 3), arg(3, 96), arg(4, 72), arg(5, 32), arg(6, 2), arg(7, 5), arg(8, 3), arg(9, 0), arg(10, 2));
   if (what == "coll") return run_collective(argc > 2 ? argv[2] : "ar1", arg(3, 3), arg(4, 96), arg(5, 3), arg(6, 3), arg(7, 0));
+  if (what == "moe_utils") return run_moe_utils(arg(2, 96), arg(3, 2), arg(4, 5), arg(5, 3), arg(6, 2));
+  if (what == "moe_rs") return run_moe_rs(arg(2, 3), arg(3, 48), arg(4, 2), arg(5, 3), arg(6, 3), arg(7, 4), arg(8, 0));
+  if (what == "a2a") return run_a2a(arg(2, 3), arg(3, 24), arg(4, 3), arg(5, 2), arg(6, 2), arg(7, 4));
+  if (what == "ep") return run_ep(arg(2, 3), arg(3, 12), arg(4, 256), arg(5, 6), arg(6, 2), arg(7, 3), arg(8, 0));
   if (what == "gemm_rs") return run_gemm_rs(arg(2, 3), arg(3, 3 * 96), arg(4, 72), arg(5, 32), arg(6, 4), arg(7, 3), arg(8, 0), arg(9, 2));
-  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll [sizes...]\n");
+  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep [sizes...]\n");
   return 2;
 }

@@ -12,9 +12,11 @@
 #include <ucontext.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <functional>
 #include <memory>
+#include <mutex>
 #include <vector>
 
 #include "kernels/common.cuh"  // the REAL csrc/kernels/common.cuh (+ device/symm.cuh), staged next to the host ptx.cuh
@@ -43,9 +45,36 @@ struct CtaRun {
   SimCta state;
   ucontext_t sched;
   std::vector<Fiber> fibers;
+  std::vector<char> warp_scratch;  // 32 x 16 bytes per warp: shuffles
   int cur = 0;
 };
 inline thread_local CtaRun* tl_cta = nullptr;
+
+// TDIST_SIM_WATCHDOG_S=n: after n seconds print, for every CTA that is still running, how many of its threads have finished,
+// wait at the CTA barrier, wait at a warp barrier or are runnable (polling) — then abort. For debugging a scenario that hangs.
+inline std::mutex g_live_mu;
+inline std::vector<CtaRun*> g_live;
+inline void watchdog_start() {
+  static std::atomic<bool> started{false};
+  const char* e = getenv("TDIST_SIM_WATCHDOG_S");
+  if (e == nullptr || started.exchange(true)) return;
+  static int secs = atoi(e);
+  pthread_t t;
+  pthread_create(&t, nullptr, [](void*) -> void* {
+    timespec ts{secs, 0};
+    nanosleep(&ts, nullptr);
+    std::lock_guard<std::mutex> g(g_live_mu);
+    for (CtaRun* r : g_live) {
+      int done = 0, bar = 0, warp = 0, run = 0;
+      for (auto& f : r->fibers) (f.done ? done : f.at_barrier ? bar : f.at_warp ? warp : run)++;
+      fprintf(stderr, "sim watchdog: rank %d cta %d: %d done, %d at __syncthreads, %d at a warp barrier, %d runnable (current %d)\n",
+              r->rank, r->cta, done, bar, warp, run, r->cur);
+    }
+    abort();
+    return nullptr;
+  }, nullptr);
+  pthread_detach(t);
+}
 
 inline void fiber_main() {
   CtaRun* r = tl_cta;
@@ -59,10 +88,16 @@ inline void* cta_thread(void* p) {
   sim_cta = &r->state;
   sim_rank = r->rank;
   blockIdx.x = r->cta;
+  blockIdx.y = blockIdx.z = threadIdx.y = threadIdx.z = 0;  // 1-D launches (the dim3 default is 1, right for the extents only)
   blockDim.x = r->threads;
   gridDim.x = r->ctas;
   sim_rng = 2654435761u * unsigned(r->rank * 100003 + r->cta * 1009 + 1);
   r->fibers.resize(r->threads);
+  {
+    std::lock_guard<std::mutex> g(g_live_mu);
+    g_live.push_back(r);
+  }
+  r->warp_scratch.assign(size_t(r->threads + 31) / 32 * 512, 0);
   for (int t = 0; t < r->threads; ++t) {
     Fiber& f = r->fibers[t];
     f.stack.reset(new char[kFiberStack]);
@@ -89,7 +124,11 @@ inline void* cta_thread(void* p) {
       if (!f.done && f.at_barrier) ++waiting;
       if (f.done) --alive;
     }
-    if (alive == 0) break;
+    if (alive == 0) {
+      std::lock_guard<std::mutex> g(g_live_mu);
+      g_live.erase(std::find(g_live.begin(), g_live.end(), r));
+      break;
+    }
     if (waiting == alive)  // everybody has arrived: open the barrier
       for (auto& f : r->fibers) f.at_barrier = false;
     for (int w0 = 0; w0 < r->threads; w0 += 32) {  // warp barriers: all live lanes of a warp have arrived
@@ -122,6 +161,10 @@ void sim_syncwarp() {
   f.at_warp = true;
   swapcontext(&f.ctx, &r->sched);
 }
+void* sim_warp_scratch() {
+  sim::CtaRun* r = sim::tl_cta;
+  return r->warp_scratch.data() + size_t(r->cur / 32) * 512;
+}
 void sim_yield() {  // a polling thread lets its siblings run: on the GPU they run in parallel
   sim::CtaRun* r = sim::tl_cta;
   if (r == nullptr) return;
@@ -132,6 +175,7 @@ namespace sim {
 
 // One kernel launch of one rank: returns when every CTA has finished (launches of a rank are sequential, like a stream).
 inline void launch(int rank, int ctas, int threads, const std::function<void()>& kernel) {
+  watchdog_start();
   std::vector<std::unique_ptr<CtaRun>> runs(ctas);
   std::vector<pthread_t> th(ctas);
   for (int c = 0; c < ctas; ++c) {

@@ -55,6 +55,8 @@ extern thread_local sim_dim3 threadIdx, blockIdx, blockDim, gridDim;
 extern thread_local SimCta* sim_cta;
 extern thread_local unsigned sim_rng;
 #define SIM_SHARED(type_t, name) type_t& name = *static_cast<type_t*>(sim_cta->shared_buf(sizeof(type_t), #name))
+// `extern __shared__ T name[];` (dynamic shared memory): a fixed 96 KB per CTA
+#define SIM_DYN_SHARED(type_t, name) type_t* name = static_cast<type_t*>(sim_cta->shared_buf(96 << 10, "dynamic"))
 
 // scheduler hooks (csrc/sim/sim_runtime.h)
 void sim_syncthreads();  // yield until every CUDA thread of the CTA has arrived
@@ -62,6 +64,21 @@ void sim_syncwarp();     // ... every lane of this thread's warp
 void sim_yield();        // let the sibling threads of the CTA run (called from every flag poll)
 inline void __syncthreads() { sim_syncthreads(); }
 inline void __syncwarp(unsigned = 0xffffffffu) { sim_syncwarp(); }
+void* sim_warp_scratch();  // 32 x 16 bytes shared by the lanes of the calling thread's warp
+// warp shuffles: every lane publishes its value, the warp meets, every lane reads the source lane's value
+template <typename T>
+inline T __shfl_sync(unsigned, T v, int src_lane) {
+  static_assert(sizeof(T) <= 16, "shuffle payload");
+  char* w = static_cast<char*>(sim_warp_scratch());
+  memcpy(w + (threadIdx.x & 31u) * 16, &v, sizeof(T));
+  sim_syncwarp();
+  T r;
+  memcpy(&r, w + (unsigned(src_lane) & 31u) * 16, sizeof(T));
+  sim_syncwarp();
+  return r;
+}
+template <typename T>
+inline T __shfl_xor_sync(unsigned m, T v, int lane_mask) { return __shfl_sync(m, v, int(threadIdx.x & 31u) ^ lane_mask); }
 inline void __threadfence() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }  // ordering is carried by the atomics around it
 inline void __threadfence_system() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void __trap() { abort(); }

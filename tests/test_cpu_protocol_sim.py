@@ -1,8 +1,10 @@
 """Flag-protocol checker: device code of this library is compiled for the CPU and run with 1-8 simulated ranks in one process
 under ThreadSanitizer (csrc/sim/):
   * the PRODUCTION collectives of csrc/kernels/collectives.cu (barrier, 4 all-reduces, 5 all-gathers incl. the LL packet
-    protocol, 2 reduce-scatters; NVLS emulated by reading / writing every rank's copy) and primitives_selftest.cu (every
-    NVSHMEM-style primitive of csrc/device/symm.cuh), on top of the REAL symm.cuh and common.cuh;
+    protocol, 2 reduce-scatters; NVLS emulated by reading / writing every rank's copy), primitives_selftest.cu (every
+    NVSHMEM-style primitive of csrc/device/symm.cuh), the MoE kernels of moe.cu (align / sort, tile swizzle, gathers, top-k
+    reduce, fused top-k reduce + reduce-scatter) and the expert-parallel kernels of ep_a2a.cu (low-latency all-to-all,
+    counts exchange, dispatch with bf16 and fp8 payload, combine), on top of the REAL symm.cuh and common.cuh;
   * the tutorial-size kernels (csrc/tutorials/*.cu — the queue of tutorial 1 and the two overlap protocols of tutorials
     7 / 8, which the production tcgen05 GEMM kernels follow).
 Only csrc/device/ptx.cuh (inline PTX) and <cuda_runtime.h> are replaced by host stand-ins.
@@ -45,13 +47,14 @@ def _stage(dst: Path) -> None:
     def copy(rel, cut):
         src = (ROOT / "csrc" / rel).read_text()
         if cut:
-            src = src[:min(i for i in (src.find("\nusing namespace tdist;"), src.find('\nextern "C"')) if i >= 0)]
+            src = src[:src.index('\nextern "C"')]
+        src = re.sub(r"extern\s+__shared__\s+(\w+)\s+(\w+)\[\];", r"SIM_DYN_SHARED(\1, \2);", src)  # dynamic shared memory
         (dst / "csrc" / rel).write_text(re.sub(r"__shared__\s+(\w+)\s+([^;]+);", shared, src))
 
     copy("device/symm.cuh", False)
     copy("kernels/common.cuh", False)
     for rel in ("tutorials/notify_wait_tutorial.cu", "tutorials/overlap_tutorial.cu", "kernels/collectives.cu",
-                "kernels/primitives_selftest.cu"):
+                "kernels/primitives_selftest.cu", "kernels/moe.cu", "kernels/ep_a2a.cu"):
         copy(rel, True)
 
 
@@ -105,12 +108,16 @@ COLLECTIVES += [("coll", op, 4, 120, 3, 6, alt) for op in ("ar1", "ar2", "ar1mc"
 COLLECTIVES += [("coll", "ar2mc", 8, 64, 2, 3, 1), ("coll", "selftest", 8, 64, 1, 3), ("coll", "ar1", 1, 40, 2, 2),
                 ("coll", "rs", 2, 8, 4, 3)]
 CLEAN += COLLECTIVES
+# production MoE / EP kernels (argument lists: csrc/sim/protocol_sim.cc)
+CLEAN += [("moe_utils", 96, 2, 5, 3, 2), ("moe_utils", 256, 4, 16, 4, 1), ("moe_rs", 3, 48, 2, 3, 3, 4), ("moe_rs", 4, 64, 2, 2, 3, 6, 2),
+          ("moe_rs", 8, 64, 2, 2, 2, 4, 1), ("a2a", 3, 24, 3, 2, 2, 4), ("a2a", 8, 8, 2, 2, 1, 3), ("ep", 3, 12, 256, 6, 2, 3),
+          ("ep", 4, 8, 256, 8, 3, 3), ("ep", 8, 8, 256, 16, 2, 2), ("ep", 2, 8, 256, 4, 2, 2, 1), ("ep", 4, 8, 512, 8, 2, 2, 1)]
 
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
 def test_protocols_are_race_free(sims, case):
     rc, out = _run(sims[0], case)
-    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
+    assert rc == 0 and ("data ok" in out or ": ok" in out) and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
 
 
 def test_straggler_with_changing_sizes(sims):
@@ -128,11 +135,12 @@ def test_straggler_with_changing_sizes(sims):
 
 
 @pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
-                                  ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2)],
+                                  ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
+                                  ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2)],
                          ids=lambda c: "-".join(map(str, c[:2])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
     rc, out = _run(sims[1], case)
     assert "ThreadSanitizer: data race" in out, out[-2000:]
-    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest)\.cu:\d+|symm\.cuh:\d+|ptx\.cuh:\d+", out), \
+    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a)\.cu:\d+|symm\.cuh:\d+|ptx\.cuh:\d+", out), \
         "the report should point into the device sources"

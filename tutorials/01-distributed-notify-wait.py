@@ -54,7 +54,9 @@ STEP 4 — sequence numbers. ``base`` grows by ceil(n_items / slots) with every 
 boolean flag would need "everybody has seen it, now clear it, now everybody has seen the clear" — two more barriers per
 call. With monotone values a rank that is already in call n+1 cannot be mistaken for call n, so calls follow each other
 with no barrier in between and the launch can be captured in a CUDA graph. Every fused op of this library uses the same
-trick (``PhaseState`` in symm.cuh keeps the counter on the device).
+trick (``PhaseState`` in symm.cuh keeps the counter on the device). This kernel, unmodified, also runs on the CPU with
+1-5 simulated ranks under ThreadSanitizer (csrc/sim, tests/test_cpu_protocol_sim.py): no payload access without a
+release / acquire chain through the flags, no lost wake-up, with more and with fewer items than slots.
 
 STEP 5 — the host side of the same protocol: ``set_signal`` / ``wait_eq`` enqueue a flag write / a flag wait on the
 current stream (one-thread kernels by default, so that they can be captured in CUDA graphs; ``use_memops=True`` selects

@@ -821,6 +821,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       if (warp == 3) {
         // ====================================================== warp 3: publishes this CTA's finished tiles
         if (lane == 0) {
+          // [sim:rs_publish begin] (csrc/sim runs the text between these markers against rs_pull_body on the CPU)
           const int bps = blocks_per_shard(p);
           uint32_t k = 0;
           for (int t = gemm_cta; t < tiles; t += num_gemm, ++k) {
@@ -840,6 +841,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               ptx::st_release_sys(flag, epoch);
             }
           }
+          // [sim:rs_publish end]
         }
       } else {
         // ====================================================== warp 2: NVLS reducer of my own segment
@@ -853,6 +855,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       if (warp == 3) {
         // ====================================================== warp 3: publishes this CTA's finished tiles
         if (lane == 0) {
+          // [sim:ar_publish begin]
           uint32_t k = 0;
           const int W = p.ctx.world;
           for (int t = gemm_cta; t < tiles; t += num_gemm, ++k) {
@@ -869,6 +872,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               for (int s2 = 0; s2 < W; ++s2) ptx::st_relaxed_sys(symm_at(p.ctx, flag, (p.ctx.rank + s2) % W), epoch);
             }
           }
+          // [sim:ar_publish end]
         }
       } else {
         // ====================================================== warp 2: cross-rank reducer

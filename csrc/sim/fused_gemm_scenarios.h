@@ -1,0 +1,136 @@
+// fused_gemm_scenarios.h — the communication side of the PRODUCTION fused GEMM kernel (csrc/kernels/gemm_sm100.cuh) on the
+// simulator. The tensor-core main loop (TMA, mbarrier, tcgen05) cannot run on a CPU; what runs here, per GEMM CTA, is
+//   warp 2  the real reducer                 rs_pull_body / ar_reduce_body (called exactly as the kernel calls them)
+//   warp 3  the real publisher               the text between the [sim:..._publish] markers of the kernel, pasted in by
+//                                            the staging step (its spin on the shared tile counter gets a yield)
+//   warp 4  a stand-in for the epilogue      walks the kernel's own tile order (tile_coord), stores each "partial tile" —
+//                                            small integers instead of a product — where the epilogue stores it, then
+//                                            counts it in shared memory as the epilogue does
+// with the kernel's prologue arithmetic (tiles_m, tiles_n, epoch, parity) restated around them. So the flag positions, the
+// epochs, the parity halves, the owner-interleaved order and the reduction units are the production ones.
+#pragma once
+
+namespace {
+
+float fused_val(int rank, int row, int col) { return float((rank * 5 + row * 3 + col) % 8); }
+
+template <int BLOCK_N>
+void fused_cta(const tdist::GemmParams& p) {
+  using namespace tdist;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int tiles_m = (p.mode == GEMM_AG || p.mode == GEMM_RS) ? blocks_per_shard(p) * p.ctx.world : (p.M + kBlockM - 1) / kBlockM;
+  const int tiles = tiles_m * tiles_n;
+  const int num_gemm = gridDim.x - p.num_comm_ctas;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+  const uint32_t phase_base = phase_begin(p.ps);
+  const uint32_t epoch = phase_base + 2;
+  const int parity = (epoch >> 1) & 1;
+  typedef uint32_t stored_count_sim_t;
+  SIM_SHARED(stored_count_sim_t, stored_count_word);
+  uint32_t* stored_count = &stored_count_word;
+  if (threadIdx.x == 0) *stored_count = 0;
+  __syncthreads();
+  if (warp == 4) {
+    if (lane == 0) {  // epilogue stand-in
+      for (int t = gemm_cta; t < tiles; t += num_gemm) {
+        const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(p.c) + size_t(parity) * p.ws_parity_bytes);
+        const long long ld = p.mode == GEMM_RS ? p.N : p.ldc;
+        const int col0 = tc.n_blk * BLOCK_N;
+        for (int r = tc.row0; r < min(tc.row0 + kBlockM, tc.row_end); ++r)
+          for (int c = col0; c < min(col0 + BLOCK_N, p.N); ++c) dst[size_t(r) * ld + c] = __float2bfloat16(fused_val(p.ctx.rank, r, c));
+        atomicAdd(stored_count, 1u);
+        sim_yield();
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+      if (p.mode == GEMM_RS) {
+#include "kernels/gemm_rs_publish.inc"
+      } else {
+#include "kernels/gemm_ar_publish.inc"
+      }
+    }
+  } else if (warp == 2) {
+    if (p.mode == GEMM_RS)
+      rs_pull_body<BF16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_n, false);
+    else
+      ar_reduce_body<BF16, BLOCK_N>(p, epoch, gemm_cta, num_gemm, tiles_m, tiles_n);
+  }
+  __syncthreads();
+  phase_end(p.ps, phase_base, 2);
+}
+
+// mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
+// AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
+// smaller) or 2 (even calls smaller).
+int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate) {
+  using namespace tdist;
+  using bf16 = __nv_bfloat16;
+  constexpr int BLOCK_N = 64;
+  const bool rs = mode == "rs", one_shot = mode == "ar1";
+  const size_t W = world;
+  const size_t parity_bytes = size_t(max_M) * N * 2;
+  const size_t out_bytes = size_t(max_M) * N * 2;  // AR two-shot: the output is symmetric (peers store into it)
+  const size_t flag_words = W * size_t((max_M + 127) / 128 + W) * ((N + BLOCK_N - 1) / BLOCK_N) + 64;
+  const size_t off_out = 2 * parity_bytes, off_flags = off_out + out_bytes, off_flags2 = off_flags + flag_words * 4;
+  sim::Node node(world, off_flags2 + (TDIST_MAX_RANKS + 64) * 4, mc != 0);
+  auto M_of = [=](int call) { return alternate && (call & 1) == (alternate & 1) ? max_M / 2 : max_M; };
+  sim::run_ranks(world, [&](int rank) {
+    uint32_t state[2] = {0, 0};
+    uint32_t counters[4] = {0, 0, 0, 0};
+    std::vector<bf16> out_local(size_t(max_M) * N);
+    for (int call = 0; call < calls; ++call) {
+      const int M = M_of(call);
+      GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.ctx = node.ctx(rank);
+      p.c = node.base(rank);
+      p.ws_parity_bytes = parity_bytes;
+      p.M = M;
+      p.N = N;
+      p.K = 64;
+      p.ldc = N;
+      p.mode = rs ? GEMM_RS : GEMM_AR;
+      p.variant = VARIANT_NVLS;
+      p.is_bf16 = 1;
+      p.group_m = 8;
+      p.rows_per_rank = rs ? M / world : M;
+      p.flags = reinterpret_cast<uint32_t*>(node.base(rank) + off_flags);
+      p.flags2 = reinterpret_cast<uint32_t*>(node.base(rank) + off_flags2);
+      p.counters = counters;
+      p.ps = PhaseState{state, state + 1};
+      p.ar_one_shot = one_shot;
+      p.use_mc = mc;
+      p.rs_unit_rows = 16;
+      // RS and one-shot AR write a local result; two-shot AR writes the symmetric output of every rank
+      p.out = (rs || one_shot) ? static_cast<void*>(out_local.data()) : static_cast<void*>(node.base(rank) + off_out);
+      const GemmParams* pp = &p;
+      sim::launch(rank, ctas, 256, [=] { fused_cta<BLOCK_N>(*pp); });
+      const bf16* got = static_cast<const bf16*>(p.out);
+      const int rows = rs ? M / world : M, row_base = rs ? rank * (M / world) : 0;
+      for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < N; ++c) {
+          float want = 0.f;
+          for (size_t q = 0; q < W; ++q) want += fused_val(int(q), row_base + r, c);
+          const float g = __bfloat162float(got[size_t(r) * N + c]);
+          if (g != want) mismatch(("fused " + mode).c_str(), rank, call, long(r) * N + c, g, want);
+        }
+      if (!rs && !one_shot) {
+        // the caller of the two-shot op reads `out` and the next call overwrites it on every rank: keep the ranks together,
+        // as the layer above does by consuming the result before it launches again
+        uint32_t* bflags = p.flags2 + 32;
+        const SymmCtx cx = p.ctx;
+        const PhaseState ps = p.ps;
+        sim::launch(rank, 1, 32, [=] { barrier_all_kernel(cx, bflags, ps); });
+      }
+    }
+  });
+  printf("protocol_sim fused %s: %d ranks x %d calls, M %d%s N %d, %d GEMM CTAs, %s: %s\n", mode.c_str(), world, calls, max_M,
+         alternate ? " (alternating with half)" : "", N, ctas, mc ? "in-switch reduction" : "peer loads",
+         g_errors ? "DATA MISMATCH" : "data ok");
+  return g_errors ? 1 : 0;
+}
+
+}  // namespace

@@ -80,6 +80,7 @@ inline T __shfl_sync(unsigned, T v, int src_lane) {
 template <typename T>
 inline T __shfl_xor_sync(unsigned m, T v, int lane_mask) { return __shfl_sync(m, v, int(threadIdx.x & 31u) ^ lane_mask); }
 inline void __threadfence() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }  // ordering is carried by the atomics around it
+inline void __threadfence_block() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void __threadfence_system() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void __trap() { abort(); }
 

@@ -4,7 +4,9 @@ under ThreadSanitizer (csrc/sim/):
     protocol, 2 reduce-scatters; NVLS emulated by reading / writing every rank's copy), primitives_selftest.cu (every
     NVSHMEM-style primitive of csrc/device/symm.cuh), the MoE kernels of moe.cu (align / sort, tile swizzle, gathers, top-k
     reduce, fused top-k reduce + reduce-scatter) and the expert-parallel kernels of ep_a2a.cu (low-latency all-to-all,
-    counts exchange, dispatch with bf16 and fp8 payload, combine), on top of the REAL symm.cuh and common.cuh;
+    counts exchange, dispatch with bf16 and fp8 payload, combine), and the communication side of the fused tcgen05 GEMM
+    (gemm_sm100.cuh: the real reducer bodies rs_pull_body / ar_reduce_body, the real publisher loops and the real tile
+    order around a stand-in for the tensor-core epilogue), on top of the REAL symm.cuh and common.cuh;
   * the tutorial-size kernels (csrc/tutorials/*.cu — the queue of tutorial 1 and the two overlap protocols of tutorials
     7 / 8, which the production tcgen05 GEMM kernels follow).
 Only csrc/device/ptx.cuh (inline PTX) and <cuda_runtime.h> are replaced by host stand-ins.
@@ -56,10 +58,23 @@ def _stage(dst: Path) -> None:
     for rel in ("tutorials/notify_wait_tutorial.cu", "tutorials/overlap_tutorial.cu", "kernels/collectives.cu",
                 "kernels/primitives_selftest.cu", "kernels/moe.cu", "kernels/ep_a2a.cu"):
         copy(rel, True)
+    # the fused tcgen05 GEMM: parameter block, tile order and communication bodies (everything before the kernel template),
+    # plus the publisher loops of the kernel, i.e. the text between its [sim:...] markers, with a yield in their spin on the
+    # shared tile counter (csrc/sim/fused_gemm_scenarios.h wraps them)
+    gemm = (ROOT / "csrc" / "kernels" / "gemm_sm100.cuh").read_text()
+    cut = gemm.index("\ntemplate <int BLOCK_N, int STAGES>\n__global__")
+    (dst / "csrc" / "kernels" / "gemm_sm100.cuh").write_text(gemm[:cut] + "\n}  // namespace tdist\n")
+    spin = re.compile(r"(while \(\*reinterpret_cast<volatile uint32_t\*>\(stored_count\) <= k\) \{)\s*\}")
+    for name in ("rs_publish", "ar_publish"):
+        a = gemm.index("\n", gemm.index(f"[sim:{name} begin]")) + 1
+        snippet = gemm[a:gemm.index(f"// [sim:{name} end]")]
+        assert spin.search(snippet), name
+        (dst / "csrc" / "kernels" / f"gemm_{name}.inc").write_text(spin.sub(r"\1 sim_yield(); }", snippet))
 
 
 def _build(stage_dir: Path, out: Path, *defines: str) -> None:
-    cmd = ["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "--param=tsan-instrument-func-entry-exit=0", *defines,
+    # (the device wait bound of symm.cuh is compiled in: 15 s here instead of 60)
+    cmd = ["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "--param=tsan-instrument-func-entry-exit=0", "-DTDIST_SPIN_TIMEOUT_S=15", *defines,
            f"-I{stage_dir / 'csrc'}", f"-I{SIM / 'stub'}", f"-I{SIM}", "-x", "c++", str(SIM / "protocol_sim.cc"), "-o", str(out),
            "-pthread"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
@@ -112,6 +127,10 @@ CLEAN += COLLECTIVES
 CLEAN += [("moe_utils", 96, 2, 5, 3, 2), ("moe_utils", 256, 4, 16, 4, 1), ("moe_rs", 3, 48, 2, 3, 3, 4), ("moe_rs", 4, 64, 2, 2, 3, 6, 2),
           ("moe_rs", 8, 64, 2, 2, 2, 4, 1), ("a2a", 3, 24, 3, 2, 2, 4), ("a2a", 8, 8, 2, 2, 1, 3), ("ep", 3, 12, 256, 6, 2, 3),
           ("ep", 4, 8, 256, 8, 3, 3), ("ep", 8, 8, 256, 16, 2, 2), ("ep", 2, 8, 256, 4, 2, 2, 1), ("ep", 4, 8, 512, 8, 2, 2, 1)]
+# communication side of the production fused GEMM: mode, ranks, M, N, GEMM CTAs, calls, in-switch reduction, alternate
+CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3, 3, 0), ("fused", "rs", 4, 1024, 64, 2, 4, 1, 2),
+          ("fused", "rs", 8, 2048, 64, 2, 3, 1), ("fused", "ar1", 3, 256, 128, 2, 3, 1), ("fused", "ar1", 4, 256, 128, 2, 4, 1, 1),
+          ("fused", "ar2", 3, 256, 128, 2, 3, 1), ("fused", "ar2", 2, 256, 128, 2, 2, 0), ("fused", "ar2", 8, 256, 64, 2, 2, 1)]
 
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
@@ -134,13 +153,25 @@ def test_straggler_with_changing_sizes(sims):
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
 
 
+@pytest.mark.xfail(strict=False, reason="known formal gap of gemm_sm100.cuh (profiles/protocol_sim.md): flag positions follow the call's M")
+def test_fused_gemm_rs_changing_sizes_with_a_straggler(sims):
+    """The production GEMM + RS communication code with calls alternating between M and M / 2 on one context while one rank's
+    flag writes are 100 ms late: a rank that is a whole call ahead writes the flag word under which a slower owner waits for
+    another rank's tile (the flag layout is computed from the call's M) — the owner reduces a tile that has not been written.
+    Needs a skew of a whole kernel inside one wave, which the hardware does not produce; fix = flag positions as constants of
+    the context (docs/roadmap.md). Passes once that is done."""
+    rc, out = _run(sims[0], ("fused", "rs", 4, 1024, 64, 1, 2, 1, 1), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "100"})
+    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out, out[-1500:]
+
+
 @pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
                                   ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
-                                  ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2)],
+                                  ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2),
+                                  ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1)],
                          ids=lambda c: "-".join(map(str, c[:2])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
     rc, out = _run(sims[1], case)
     assert "ThreadSanitizer: data race" in out, out[-2000:]
-    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a)\.cu:\d+|symm\.cuh:\d+|ptx\.cuh:\d+", out), \
+    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a)\.cu:\d+|(symm|ptx|gemm_sm100)\.cuh:\d+|fused_gemm_scenarios\.h:\d+", out), \
         "the report should point into the device sources"

@@ -468,6 +468,9 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     }
     if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
     tiles_m = ((p.rows_per_rank + kBlockM - 1) / kBlockM) * W;
+    // opt-in: one flag row per source rank whose length is a constant of the context (see GemmParams::flag_row); the size
+    // checks below still apply to the call's own layout, which fits in such a row whenever it fits in the area
+    if (env_int("TDIST_FIXED_FLAG_LAYOUT", 0) && f->flags_words >= size_t(W)) p.flag_row = int(f->flags_words / W);
   } else if (f->mode == TDIST_GEMM_AR) {
     // a->a = [M, K/W]; f->ws = symmetric tile buffer [2][M][ldc]; f->out = [M, ldc]
     p.rows_per_rank = a->M;
@@ -490,6 +493,7 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
       return -1;
     }
     p.counters = f->flags2 + 32;  // a local word behind the W closing flags
+    if (env_int("TDIST_FIXED_FLAG_LAYOUT", 0) && f->flags_words >= size_t(W)) p.flag_row = int(f->flags_words / W);
     if (make_tmap(&p.tma_a[0], a->a, a->M, a->K, a->lda, kBlockM) != 0) return -1;
     tiles_m = (a->M + kBlockM - 1) / kBlockM;
   } else {

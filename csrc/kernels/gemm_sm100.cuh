@@ -86,6 +86,10 @@ struct GemmParams {
   long long a_lda;         // AG: row stride of a_local in elements
   size_t ws_parity_bytes;  // distance between the two parity halves of the workspace: a constant of the CONTEXT, so that
                            // calls of different sizes on one context never overlap the other parity's live data
+  int flag_row;            // RS (NVLS) / AR: flag words per SOURCE RANK. 0 = the row follows the call (bps * tiles_n, or tiles):
+                           // the measured default. > 0 (TDIST_FIXED_FLAG_LAYOUT=1: flags_words / W, a constant of the
+                           // context): every flag word has ONE writer rank over all calls, so calls of different M on one
+                           // context cannot meet in a word under two meanings (profiles/protocol_sim.md)
   // grouped (MoE) GEMM: block_expert[m_blk] selects the expert whose [N, K] weight slab (rows
   // expert*N .. of B) multiplies the 128-row block; negative = padding block, skipped by all roles
   const int* block_expert;
@@ -345,7 +349,8 @@ __device__ __forceinline__ void rs_pull_body(const GemmParams& p, uint32_t epoch
     const int r0 = blk * kBlockM + sc * unit_rows;
     if (blk >= bps || r0 >= p.rows_per_rank) continue;
     // flags layout (RS, NVLS): [W src][bps][tiles_n], written by src when its partial tile is stored
-    if (lane < W && !(p.debug & 4)) wait_ge_sys_poll_relaxed(p.flags + (size_t(lane) * bps + blk) * tiles_n + n_blk, epoch);
+    if (lane < W && !(p.debug & 4))
+      wait_ge_sys_poll_relaxed(p.flags + size_t(lane) * (p.flag_row > 0 ? p.flag_row : bps * tiles_n) + blk * tiles_n + n_blk, epoch);
     __syncwarp();
     const int rows = min(unit_rows, p.rows_per_rank - r0);
     const int col0 = n_blk * BLOCK_N;
@@ -464,7 +469,7 @@ __device__ __forceinline__ void ar_reduce_body(const GemmParams& p, uint32_t epo
     const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
     const int r0 = tc.row0 + sc * unit_rows;
     if (r0 >= p.M) continue;
-    if (lane < W) wait_ge_sys_poll_relaxed(p.flags + size_t(lane) * tiles + t, epoch);
+    if (lane < W) wait_ge_sys_poll_relaxed(p.flags + size_t(lane) * (p.flag_row > 0 ? p.flag_row : tiles) + t, epoch);
     __syncwarp();
     const int rows = min(unit_rows, p.M - r0);
     const int col0 = tc.n_blk * BLOCK_N;
@@ -829,7 +834,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             while (*reinterpret_cast<volatile uint32_t*>(stored_count) <= k) {
             }
             __threadfence_block();
-            uint32_t* flag = symm_at(p.ctx, p.flags + (size_t(p.ctx.rank) * bps + tc.blk) * tiles_n + tc.n_blk, tc.shard);
+            uint32_t* flag = symm_at(
+                p.ctx, p.flags + size_t(p.ctx.rank) * (p.flag_row > 0 ? p.flag_row : bps * tiles_n) + tc.blk * tiles_n + tc.n_blk, tc.shard);
             if (!(p.debug & 8)) {
               // The partial tile is in THIS GPU's memory and the owner's switch reads are served from this GPU's L2,
               // so a GPU-scope fence orders the tile before the flag; the flag itself is a plain system-scope store.
@@ -863,7 +869,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             }
             __threadfence_block();
             ptx::fence_acq_rel_gpu();  // the tile is in this GPU's memory: see the RS publisher
-            uint32_t* flag = p.flags + size_t(p.ctx.rank) * tiles + t;
+            uint32_t* flag = p.flags + size_t(p.ctx.rank) * (p.flag_row > 0 ? p.flag_row : tiles) + t;
             if (!p.ar_one_shot) {
               ptx::st_relaxed_sys(symm_at(p.ctx, flag, t % W), epoch);
             } else if (p.use_mc) {

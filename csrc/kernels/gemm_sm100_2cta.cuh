@@ -370,7 +370,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
             __threadfence_block();
             const int blk128 = tc.pblk * 2 + int(cta_rank);
             if (blk128 >= bps128) continue;
-            uint32_t* flag = symm_at(p.ctx, p.flags + (size_t(p.ctx.rank) * bps128 + blk128) * tiles_n + tc.n_blk, tc.shard);
+            uint32_t* flag = symm_at(
+                p.ctx, p.flags + size_t(p.ctx.rank) * (p.flag_row > 0 ? p.flag_row : bps128 * tiles_n) + blk128 * tiles_n + tc.n_blk, tc.shard);
             if (!(p.debug & 8)) {
               // The partial tile is in THIS GPU's memory and the owner's switch reads are served from this GPU's L2,
               // so a GPU-scope fence orders the tile before the flag; the flag itself is a plain system-scope store.

@@ -64,8 +64,8 @@ void fused_cta(const tdist::GemmParams& p) {
 
 // mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
 // AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
-// smaller) or 2 (even calls smaller).
-int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate) {
+// smaller) or 2 (even calls smaller). `fixed_rows`: one flag row per source rank of constant length (GemmParams::flag_row).
+int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate, int fixed_rows) {
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
@@ -104,6 +104,7 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       p.ar_one_shot = one_shot;
       p.use_mc = mc;
       p.rs_unit_rows = 16;
+      p.flag_row = fixed_rows ? int(flag_words / W) : 0;  // TDIST_FIXED_FLAG_LAYOUT=1 of csrc/kernels/gemm.cu
       // RS and one-shot AR write a local result; two-shot AR writes the symmetric output of every rank
       p.out = (rs || one_shot) ? static_cast<void*>(out_local.data()) : static_cast<void*>(node.base(rank) + off_out);
       const GemmParams* pp = &p;
@@ -127,8 +128,8 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       }
     }
   });
-  printf("protocol_sim fused %s: %d ranks x %d calls, M %d%s N %d, %d GEMM CTAs, %s: %s\n", mode.c_str(), world, calls, max_M,
-         alternate ? " (alternating with half)" : "", N, ctas, mc ? "in-switch reduction" : "peer loads",
+  printf("protocol_sim fused %s: %d ranks x %d calls, M %d%s N %d, %d GEMM CTAs, %s, flag rows %s: %s\n", mode.c_str(), world, calls, max_M,
+         alternate ? " (alternating with half)" : "", N, ctas, mc ? "in-switch reduction" : "peer loads", fixed_rows ? "fixed" : "per call",
          g_errors ? "DATA MISMATCH" : "data ok");
   return g_errors ? 1 : 0;
 }

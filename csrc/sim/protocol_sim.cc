@@ -19,7 +19,7 @@
 //   protocol_sim moe_rs <ranks> <tokens> <topk> <row_vecs> <ctas> <calls> [alternate]
 //   protocol_sim a2a <ranks> <max rows per peer> <row_vecs> <experts per rank> <ctas per peer> <calls>
 //   protocol_sim ep <ranks> <tokens> <hidden> <experts> <ctas> <calls> [fp8]
-//   protocol_sim fused rs|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate]   (production GEMM comm side)
+//   protocol_sim fused rs|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -341,7 +341,7 @@ int main(int argc, char** argv) {
   if (what == "moe_rs") return run_moe_rs(arg(2, 3), arg(3, 48), arg(4, 2), arg(5, 3), arg(6, 3), arg(7, 4), arg(8, 0));
   if (what == "a2a") return run_a2a(arg(2, 3), arg(3, 24), arg(4, 3), arg(5, 2), arg(6, 2), arg(7, 4));
   if (what == "ep") return run_ep(arg(2, 3), arg(3, 12), arg(4, 256), arg(5, 6), arg(6, 2), arg(7, 3), arg(8, 0));
-  if (what == "fused") return run_fused(argc > 2 ? argv[2] : "rs", arg(3, 3), arg(4, 3 * 256), arg(5, 128), arg(6, 3), arg(7, 3), arg(8, 1), arg(9, 0));
+  if (what == "fused") return run_fused(argc > 2 ? argv[2] : "rs", arg(3, 3), arg(4, 3 * 256), arg(5, 128), arg(6, 3), arg(7, 3), arg(8, 1), arg(9, 0), arg(10, 0));
   if (what == "gemm_rs") return run_gemm_rs(arg(2, 3), arg(3, 3 * 96), arg(4, 72), arg(5, 32), arg(6, 4), arg(7, 3), arg(8, 0), arg(9, 2));
   fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep|fused [sizes...]\n");
   return 2;

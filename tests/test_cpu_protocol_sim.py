@@ -127,10 +127,13 @@ CLEAN += COLLECTIVES
 CLEAN += [("moe_utils", 96, 2, 5, 3, 2), ("moe_utils", 256, 4, 16, 4, 1), ("moe_rs", 3, 48, 2, 3, 3, 4), ("moe_rs", 4, 64, 2, 2, 3, 6, 2),
           ("moe_rs", 8, 64, 2, 2, 2, 4, 1), ("a2a", 3, 24, 3, 2, 2, 4), ("a2a", 8, 8, 2, 2, 1, 3), ("ep", 3, 12, 256, 6, 2, 3),
           ("ep", 4, 8, 256, 8, 3, 3), ("ep", 8, 8, 256, 16, 2, 2), ("ep", 2, 8, 256, 4, 2, 2, 1), ("ep", 4, 8, 512, 8, 2, 2, 1)]
-# communication side of the production fused GEMM: mode, ranks, M, N, GEMM CTAs, calls, in-switch reduction, alternate
+# communication side of the production fused GEMM: mode, ranks, M, N, GEMM CTAs, calls, in-switch reduction, alternate,
+# fixed flag rows (GemmParams::flag_row, TDIST_FIXED_FLAG_LAYOUT=1)
 CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3, 3, 0), ("fused", "rs", 4, 1024, 64, 2, 4, 1, 2),
           ("fused", "rs", 8, 2048, 64, 2, 3, 1), ("fused", "ar1", 3, 256, 128, 2, 3, 1), ("fused", "ar1", 4, 256, 128, 2, 4, 1, 1),
-          ("fused", "ar2", 3, 256, 128, 2, 3, 1), ("fused", "ar2", 2, 256, 128, 2, 2, 0), ("fused", "ar2", 8, 256, 64, 2, 2, 1)]
+          ("fused", "ar2", 3, 256, 128, 2, 3, 1), ("fused", "ar2", 2, 256, 128, 2, 2, 0), ("fused", "ar2", 8, 256, 64, 2, 2, 1),
+          ("fused", "rs", 3, 768, 128, 3, 4, 1, 2, 1), ("fused", "rs", 8, 2048, 64, 2, 3, 1, 1, 1), ("fused", "rs", 3, 768, 128, 3, 3, 0, 0, 1),
+          ("fused", "ar1", 4, 256, 128, 2, 4, 1, 1, 1), ("fused", "ar2", 4, 256, 128, 2, 4, 1, 2, 1)]
 
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
@@ -153,15 +156,22 @@ def test_straggler_with_changing_sizes(sims):
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
 
 
-@pytest.mark.xfail(strict=False, reason="known formal gap of gemm_sm100.cuh (profiles/protocol_sim.md): flag positions follow the call's M")
+@pytest.mark.xfail(strict=False, reason="known formal gap of the default flag layout of gemm_sm100.cuh (profiles/protocol_sim.md); TDIST_FIXED_FLAG_LAYOUT=1 closes it")
 def test_fused_gemm_rs_changing_sizes_with_a_straggler(sims):
     """The production GEMM + RS communication code with calls alternating between M and M / 2 on one context while one rank's
     flag writes are 100 ms late: a rank that is a whole call ahead writes the flag word under which a slower owner waits for
-    another rank's tile (the flag layout is computed from the call's M) — the owner reduces a tile that has not been written.
-    Needs a skew of a whole kernel inside one wave, which the hardware does not produce; fix = flag positions as constants of
-    the context (docs/roadmap.md). Passes once that is done."""
+    another rank's tile (the DEFAULT flag layout is computed from the call's M) — the owner reduces a tile that has not been
+    written. Needs a skew of a whole kernel inside one wave, which the hardware does not produce; the fix (next test) is
+    opt-in until it has run on GPUs. Passes once it is the default."""
     rc, out = _run(sims[0], ("fused", "rs", 4, 1024, 64, 1, 2, 1, 1), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "100"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out, out[-1500:]
+
+
+def test_fused_gemm_rs_fixed_flag_rows_survive_the_straggler(sims):
+    """The same scenario with one flag row per source rank whose length is a constant of the context (GemmParams::flag_row,
+    enabled by TDIST_FIXED_FLAG_LAYOUT=1): every flag word has one writer over all calls — clean."""
+    rc, out = _run(sims[0], ("fused", "rs", 4, 1024, 64, 1, 2, 1, 1, 1), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "100"})
+    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-1500:]
 
 
 @pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),

@@ -362,6 +362,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
       if (warp == 3) {
         // ====================================================== warp 3: publishes this CTA's finished half tiles
         if (lane == 0) {
+          // [sim:rs_publish_pair begin] (run on the CPU against rs_pull_body by csrc/sim, see gemm_sm100.cuh)
           uint32_t k = 0;
           for (int t = pair; t < tiles; t += num_pairs, ++k) {
             const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
@@ -383,6 +384,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
               ptx::st_release_sys(flag, epoch);
             }
           }
+          // [sim:rs_publish_pair end]
         }
       } else {
         // ====================================================== warp 2: NVLS reducer of my own segment

@@ -62,14 +62,60 @@ void fused_cta(const tdist::GemmParams& p) {
   phase_end(p.ps, phase_base, 2);
 }
 
-// mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
+// The CTA-pair kernel (gemm_sm100_2cta.cuh, the default of the flagship): two consecutive CTAs share a 256-row tile, CTA
+// `cta_rank` of the pair owns its 128-row half; both run a reducer and a publisher of their own.
+template <int BLOCK_N>
+void fused_pair_cta(const tdist::GemmParams& p) {
+  using namespace tdist;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = blockIdx.x & 1u;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int bps128 = blocks_per_shard(p);
+  const int ptiles_m = ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * p.ctx.world;
+  const int tiles = ptiles_m * tiles_n;
+  const int num_pairs = (gridDim.x - p.num_comm_ctas) / 2;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+  const int pair = gemm_cta >> 1;
+  const uint32_t phase_base = phase_begin(p.ps);
+  const uint32_t epoch = phase_base + 2;
+  const int parity = (epoch >> 1) & 1;
+  typedef uint32_t stored_count_sim_t;
+  SIM_SHARED(stored_count_sim_t, stored_count_word);
+  uint32_t* stored_count = &stored_count_word;
+  if (threadIdx.x == 0) *stored_count = 0;
+  __syncthreads();
+  if (warp == 4) {
+    if (lane == 0) {  // epilogue stand-in: my 128-row half of every pair tile, masked by the end of the shard as the stores are
+      for (int t = pair; t < tiles; t += num_pairs) {
+        const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(p.c) + size_t(parity) * p.ws_parity_bytes);
+        const int row0 = tc.row0 + int(cta_rank) * kBlockM, col0 = tc.n_blk * BLOCK_N;
+        for (int r = row0; r < min(row0 + kBlockM, tc.row_end); ++r)
+          for (int c = col0; c < min(col0 + BLOCK_N, p.N); ++c) dst[size_t(r) * p.N + c] = __float2bfloat16(fused_val(p.ctx.rank, r, c));
+        atomicAdd(stored_count, 1u);
+        sim_yield();
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0) {
+#include "kernels/gemm_rs_publish_pair.inc"
+    }
+  } else if (warp == 2) {
+    const int ncw = static_cast<int>(gridDim.x) - p.num_comm_ctas;
+    rs_pull_body<BF16, BLOCK_N>(p, epoch, gemm_cta, ncw, tiles_n, true);
+  }
+  __syncthreads();
+  phase_end(p.ps, phase_base, 2);
+}
+
+// mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; "rs2": the CTA-pair kernel's form, `ctas` must be even; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
 // AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
 // smaller) or 2 (even calls smaller). `fixed_rows`: one flag row per source rank of constant length (GemmParams::flag_row).
 int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate, int fixed_rows) {
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
-  const bool rs = mode == "rs", one_shot = mode == "ar1";
+  const bool pair = mode == "rs2", rs = mode == "rs" || pair, one_shot = mode == "ar1";
   const size_t W = world;
   const size_t parity_bytes = size_t(max_M) * N * 2;
   const size_t out_bytes = size_t(max_M) * N * 2;  // AR two-shot: the output is symmetric (peers store into it)
@@ -108,7 +154,10 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       // RS and one-shot AR write a local result; two-shot AR writes the symmetric output of every rank
       p.out = (rs || one_shot) ? static_cast<void*>(out_local.data()) : static_cast<void*>(node.base(rank) + off_out);
       const GemmParams* pp = &p;
-      sim::launch(rank, ctas, 256, [=] { fused_cta<BLOCK_N>(*pp); });
+      if (pair)
+        sim::launch(rank, ctas, 256, [=] { fused_pair_cta<BLOCK_N>(*pp); });
+      else
+        sim::launch(rank, ctas, 256, [=] { fused_cta<BLOCK_N>(*pp); });
       const bf16* got = static_cast<const bf16*>(p.out);
       const int rows = rs ? M / world : M, row_base = rs ? rank * (M / world) : 0;
       for (int r = 0; r < rows; ++r)

@@ -19,7 +19,7 @@
 //   protocol_sim moe_rs <ranks> <tokens> <topk> <row_vecs> <ctas> <calls> [alternate]
 //   protocol_sim a2a <ranks> <max rows per peer> <row_vecs> <experts per rank> <ctas per peer> <calls>
 //   protocol_sim ep <ranks> <tokens> <hidden> <experts> <ctas> <calls> [fp8]
-//   protocol_sim fused rs|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
+//   protocol_sim fused rs|rs2|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -30,6 +30,7 @@
 #include "kernels/moe.cu"                     // PRODUCTION: MoE align / sort, tile swizzle, gathers, top-k reduce (+ reduce-scatter)
 #include "kernels/ep_a2a.cu"                  // PRODUCTION: low-latency all-to-all, EP counts / dispatch (bf16, fp8) / combine
 #include "kernels/gemm_sm100.cuh"             // PRODUCTION: parameter block, tile order and communication bodies of the fused GEMM
+#include "kernels/gemm_sm100_2cta.cuh"        // PRODUCTION: tile order of the CTA-pair kernel
 
 #include <atomic>
 #include <string>

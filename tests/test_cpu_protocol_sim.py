@@ -92,8 +92,8 @@ def sims(tmp_path_factory):
     _stage(d / "stage")
     probe = subprocess.run(["g++", "-fsanitize=thread", "-x", "c++", "-", "-o", str(d / "probe")], input="int main(){}",
                            capture_output=True, text=True)
-    if probe.returncode != 0:
-        pytest.skip("ThreadSanitizer runtime not available")
+    if probe.returncode != 0 or subprocess.run([str(d / "probe")], capture_output=True).returncode != 0:
+        pytest.skip("ThreadSanitizer runtime not available (or it cannot run on this kernel's address-space layout)")
     _build(d / "stage", d / "sim")
     _build(d / "stage", d / "sim_broken", "-DTDIST_SIM_BREAK_RELEASE")
     return d / "sim", d / "sim_broken"

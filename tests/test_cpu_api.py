@@ -42,3 +42,56 @@ def test_public_api_checklist():
         if not hasattr(DenseLLM, meth): missing.append(f"DenseLLM.{meth}")
     assert not missing, missing
 
+
+
+def test_ctypes_prototypes_match_the_c_header():
+    """Every prototype declared in triton_dist/_lib.py has the argument count and the argument KINDS (pointer, 32-bit integer,
+    size_t, 64-bit integer, float) of its declaration in include/tdist.h, and every function of the header that Python calls
+    through the library has a prototype (an undeclared function would get 32-bit integer arguments for its pointers)."""
+    import ctypes
+    import re
+    from pathlib import Path
+
+    from triton_dist import _lib
+
+    root = Path(__file__).resolve().parent.parent
+    header = re.sub(r"/\*.*?\*/", " ", (root / "include" / "tdist.h").read_text(), flags=re.S)
+    header = re.sub(r"//[^\n]*", " ", header)
+    protos = {}
+    for m in re.finditer(r"\b(?:int|void\s*\*|size_t|const\s+char\s*\*)\s+(tdist_\w+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        params = [q.strip() for q in m.group(2).replace("\n", " ").split(",") if q.strip() and q.strip() != "void"]
+        protos[m.group(1)] = params
+    assert len(protos) > 60, len(protos)
+
+    def kind_c(param):
+        if "*" in param or "[" in param:
+            return "ptr"
+        t = param.rsplit(" ", 1)[0].strip() if " " in param else param
+        t = t.replace("const ", "").strip()
+        return {"int": "i32", "uint32_t": "i32", "unsigned": "i32", "unsigned int": "i32", "size_t": "i64", "long long": "i64",
+                "unsigned long long": "i64", "uint64_t": "i64", "float": "f32"}[t]
+
+    def kind_py(t):
+        if t in (ctypes.c_void_p, ctypes.c_char_p) or hasattr(t, "_type_") and not isinstance(t._type_, str):
+            return "ptr"  # c_void_p or POINTER(struct)
+        return {ctypes.c_int: "i32", ctypes.c_uint32: "i32", ctypes.c_size_t: "i64", ctypes.c_longlong: "i64",
+                ctypes.c_ulonglong: "i64", ctypes.c_float: "f32"}[t]
+
+    lib = _lib.load(required=True)
+    checked = 0
+    for name, params in protos.items():
+        fn = getattr(lib, name)
+        if fn.argtypes is None:
+            continue  # declared where it is used (tutorial and probe entry points); see below
+        got = [kind_py(t) for t in fn.argtypes]
+        want = [kind_c(q) for q in params]
+        assert got == want, f"{name}: ctypes {got} vs header {want}"
+        checked += 1
+    assert checked > 55, checked
+    # functions the package calls: every `lib().tdist_xxx(` / `lib.tdist_xxx(` in the Python sources is declared
+    used = set()
+    for py in (root / "triton_dist").rglob("*.py"):
+        used |= set(re.findall(r"\.(tdist_\w+)\(", py.read_text()))
+    undeclared = sorted(n for n in used if n in protos and getattr(lib, n).argtypes is None)
+    local_decl = {"tdist_link_probe"}  # declared next to its only caller
+    assert set(undeclared) <= local_decl, undeclared

@@ -156,6 +156,7 @@ def _declare(lib: ctypes.CDLL) -> None:
     sig("tdist_primitives_selftest", [P(SymmCtx), vp, vp, u32, vp])
     sig("tdist_moe_tile_swizzle", [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp])
     sig("tdist_moe_gather_rows", [vp, vp, vp, vp, i32, i32, i32, i32, vp])
+    sig("tdist_moe_gather_rows_stage", [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp])
     sig("tdist_moe_topk_reduce", [i32, vp, vp, vp, vp, i32, i32, i32, vp])
     sig("tdist_moe_reduce_rs", [P(SymmCtx), i32, vp, vp, sz, vp, vp, vp, i32, i32, i32, vp, vp, vp, i32, vp])
     sig("tdist_a2a", [P(SymmCtx), vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp])

@@ -95,3 +95,50 @@ def test_ctypes_prototypes_match_the_c_header():
     undeclared = sorted(n for n in used if n in protos and getattr(lib, n).argtypes is None)
     local_decl = {"tdist_link_probe"}  # declared next to its only caller
     assert set(undeclared) <= local_decl, undeclared
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """The ctypes mirrors of the C ABI structs (context, GEMM / fused arguments, megakernel op) have the size and the field
+    offsets a C compiler gives include/tdist.h: same field order, types and padding."""
+    import ctypes
+    import re
+    import shutil
+    import subprocess
+    from pathlib import Path
+
+    import pytest
+
+    from triton_dist import _lib
+
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    root = Path(__file__).resolve().parent.parent
+    header = (root / "include" / "tdist.h").read_text()
+    pairs = {"tdist_symm_ctx": _lib.SymmCtx, "tdist_gemm_args": _lib.GemmArgs, "tdist_fused_args": _lib.FusedArgs,
+             "tdist_mega_op": _lib.MegaOp}
+    rename = {("tdist_mega_op", "inp"): "in"}  # `in` is a Python keyword
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "tdist.h"', 'int main(void) {']
+    for cname, cls in pairs.items():
+        body = re.search(r"typedef struct " + cname + r"\s*\{(.*?)\}\s*" + cname + r"\s*;", header, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", " ", body, flags=re.S)
+        c_fields = []
+        for decl in (d for d in body.split(";") if d.strip()):  # "int M, N, K" declares three fields
+            for part in decl.split(","):
+                c_fields.append(re.sub(r"\[.*", "", part.split()[-1].lstrip("*")))
+        py_fields = [rename.get((cname, n), n) for n, _ in cls._fields_]
+        assert c_fields == py_fields, f"{cname}: header fields {c_fields} vs ctypes {py_fields}"
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for f in c_fields:
+            lines.append(f'  printf("{cname} {f} %zu\\n", offsetof({cname}, {f}));')
+    lines += ["  return 0;", "}"]
+    (tmp_path / "abi.c").write_text("\n".join(lines))
+    subprocess.run(["gcc", f"-I{root / 'include'}", str(tmp_path / "abi.c"), "-o", str(tmp_path / "abi")], check=True)
+    out = subprocess.run([str(tmp_path / "abi")], capture_output=True, text=True, check=True).stdout
+    for line in out.splitlines():
+        cname, field, value = line.split()
+        cls = pairs[cname]
+        if field == "size":
+            assert ctypes.sizeof(cls) == int(value), f"{cname}: sizeof {ctypes.sizeof(cls)} vs {value}"
+        else:
+            py_name = {v: k[1] for k, v in rename.items() if k[0] == cname}.get(field, field)
+            assert getattr(cls, py_name).offset == int(value), f"{cname}.{field}: offset {getattr(cls, py_name).offset} vs {value}"

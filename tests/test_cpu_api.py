@@ -142,3 +142,35 @@ def test_ctypes_structs_match_the_c_header(tmp_path):
         else:
             py_name = {v: k[1] for k, v in rename.items() if k[0] == cname}.get(field, field)
             assert getattr(cls, py_name).offset == int(value), f"{cname}.{field}: offset {getattr(cls, py_name).offset} vs {value}"
+
+
+def test_native_call_sites_pass_the_declared_number_of_arguments():
+    """Every call of a native entry point in the Python sources (``lib.tdist_xxx(...)``) passes as many positional arguments as
+    the ctypes prototype declares: most of these calls sit on GPU-only paths, where a miscount would only show on a GPU."""
+    import ast
+    from pathlib import Path
+
+    from triton_dist import _lib
+
+    root = Path(__file__).resolve().parent.parent
+    lib = _lib.load(required=True)
+    checked, problems = 0, []
+    files = list((root / "triton_dist").rglob("*.py")) + [root / "bench.py", root / "__graft_entry__.py"]
+    for py in files:
+        tree = ast.parse(py.read_text())
+        for node in ast.walk(tree):
+            if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and node.func.attr.startswith("tdist_")):
+                continue
+            name = node.func.attr
+            fn = getattr(lib, name, None)
+            if fn is None:
+                problems.append(f"{py.name}:{node.lineno}: {name} is not exported by the library")
+                continue
+            if fn.argtypes is None or any(isinstance(a, ast.Starred) for a in node.args) or node.keywords:
+                continue
+            checked += 1
+            if len(node.args) != len(fn.argtypes):
+                problems.append(f"{py.relative_to(root)}:{node.lineno}: {name} called with {len(node.args)} arguments, prototype has "
+                                f"{len(fn.argtypes)}")
+    assert not problems, "\n".join(problems)
+    assert checked > 60, checked

@@ -174,3 +174,39 @@ def test_native_call_sites_pass_the_declared_number_of_arguments():
                                 f"{len(fn.argtypes)}")
     assert not problems, "\n".join(problems)
     assert checked > 60, checked
+
+
+def test_no_undefined_names_in_the_python_sources():
+    """A name that is read but bound nowhere (module, enclosing function, builtins) in code that only runs on a GPU would first
+    fail on a GPU: scan every source file with the compiler's own symbol tables."""
+    import builtins
+    import symtable
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    files = (list((root / "triton_dist").rglob("*.py")) + [root / "bench.py", root / "__graft_entry__.py", root / "build.py"] +
+             list((root / "tutorials").glob("*.py")) + list((root / "scripts").glob("*.py")) + list((root / "tests").glob("*.py")))
+    known = set(dir(builtins)) | {"__file__", "__name__", "__doc__", "__builtins__", "__spec__", "__package__", "__path__"}
+    problems = []
+    for f in files:
+        src = f.read_text()
+        if "import *" in src:
+            continue
+        top = symtable.symtable(src, str(f), "exec")
+        module_names = {s.get_name() for s in top.get_symbols() if s.is_assigned() or s.is_imported() or s.is_namespace()}
+
+        def walk(table):
+            for s in table.get_symbols():
+                name = s.get_name()
+                if not s.is_referenced() or name in known:
+                    continue
+                if table.get_type() == "module":
+                    if not (s.is_assigned() or s.is_imported() or s.is_namespace()):
+                        problems.append(f"{f.relative_to(root)}: {name}")
+                elif s.is_global() and not s.is_declared_global() and name not in module_names:
+                    problems.append(f"{f.relative_to(root)}: {table.get_name()}(): {name}")
+            for child in table.get_children():
+                walk(child)
+
+        walk(top)
+    assert len(files) > 150 and not problems, problems

@@ -169,6 +169,21 @@ inline float2 unpack_bf16x2(uint32_t u) {
 inline uint32_t pack_f16x2(float lo, float hi) { return uint32_t(f32_to_f16(lo)) | (uint32_t(f32_to_f16(hi)) << 16); }
 inline float2 unpack_f16x2(uint32_t u) { return make_float2(f16_to_f32(uint16_t(u & 0xffffu)), f16_to_f32(uint16_t(u >> 16))); }
 
+// ---- warp reductions (shuffle trees, as the device versions) and programmatic dependent launch (no-ops: launches of a
+// simulated rank are already sequential)
+template <typename T>
+inline T warp_reduce_sum(T v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <typename T>
+inline T warp_reduce_max(T v) {
+  for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+inline void gdc_wait() {}
+inline void gdc_launch_dependents() {}
+
 // ---- NVLS emulation: `mc` is an address inside the node's multicast window
 inline char* mc_copy(const void* mc, int rank) {
   return sim_mc.heap + size_t(rank) * sim_mc.bytes + (static_cast<const char*>(mc) - sim_mc.mc_base);
@@ -217,3 +232,5 @@ inline int4 multimem_ld_reduce_f32x4(const void* mc) {
 
 }  // namespace ptx
 }  // namespace tdist
+inline uint16_t sim_f32_to_f16(float f) { return tdist::ptx::f32_to_f16(f); }
+inline float sim_f16_to_f32(uint16_t h) { return tdist::ptx::f16_to_f32(h); }

@@ -42,6 +42,7 @@ struct Fiber {
 struct CtaRun {
   const std::function<void()>* kernel;
   int rank, cta, ctas, threads;
+  int gx = 0, gy = 1, gz = 1;  // 3-D grid extents (gx == 0: 1-D launch of `ctas` CTAs)
   SimCta state;
   ucontext_t sched;
   std::vector<Fiber> fibers;
@@ -87,10 +88,21 @@ inline void* cta_thread(void* p) {
   tl_cta = r;
   sim_cta = &r->state;
   sim_rank = r->rank;
-  blockIdx.x = r->cta;
-  blockIdx.y = blockIdx.z = threadIdx.y = threadIdx.z = 0;  // 1-D launches (the dim3 default is 1, right for the extents only)
+  threadIdx.y = threadIdx.z = 0;  // (the dim3 default is 1, right for the extents only)
   blockDim.x = r->threads;
-  gridDim.x = r->ctas;
+  if (r->gx > 0) {  // 3-D grid: x fastest
+    blockIdx.x = r->cta % r->gx;
+    blockIdx.y = (r->cta / r->gx) % r->gy;
+    blockIdx.z = r->cta / (r->gx * r->gy);
+    gridDim.x = r->gx;
+    gridDim.y = r->gy;
+    gridDim.z = r->gz;
+  } else {
+    blockIdx.x = r->cta;
+    blockIdx.y = blockIdx.z = 0;
+    gridDim.x = r->ctas;
+    gridDim.y = gridDim.z = 1;
+  }
   sim_rng = 2654435761u * unsigned(r->rank * 100003 + r->cta * 1009 + 1);
   r->fibers.resize(r->threads);
   {
@@ -174,7 +186,7 @@ void sim_yield() {  // a polling thread lets its siblings run: on the GPU they r
 namespace sim {
 
 // One kernel launch of one rank: returns when every CTA has finished (launches of a rank are sequential, like a stream).
-inline void launch(int rank, int ctas, int threads, const std::function<void()>& kernel) {
+inline void launch(int rank, int ctas, int threads, const std::function<void()>& kernel, int gx = 0, int gy = 1, int gz = 1) {
   watchdog_start();
   std::vector<std::unique_ptr<CtaRun>> runs(ctas);
   std::vector<pthread_t> th(ctas);
@@ -185,6 +197,9 @@ inline void launch(int rank, int ctas, int threads, const std::function<void()>&
     runs[c]->cta = c;
     runs[c]->ctas = ctas;
     runs[c]->threads = threads;
+    runs[c]->gx = gx;
+    runs[c]->gy = gy;
+    runs[c]->gz = gz;
     if (pthread_create(&th[c], nullptr, cta_thread, runs[c].get()) != 0) {
       perror("pthread_create");
       abort();
@@ -222,6 +237,11 @@ struct Node {
     return c;
   }
 };
+
+// 3-D grid of gx x gy x gz CTAs (single-GPU kernels such as the split-KV decode attention)
+inline void launch3(int gx, int gy, int gz, int threads, const std::function<void()>& kernel) {
+  launch(0, gx * gy * gz, threads, kernel, gx, gy, gz);
+}
 
 // Every rank runs `driver(rank)` on its own OS thread: ranks issue their launches independently of each other.
 inline void run_ranks(int world, const std::function<void(int)>& driver) {

@@ -138,6 +138,18 @@ inline float __bfloat162float(__nv_bfloat16 b) {
   return f;
 }
 
+// fp16 storage type (conversions: csrc/sim/shim/device/ptx.cuh has the bit-exact routines)
+struct __half {
+  uint16_t v;
+};
+uint16_t sim_f32_to_f16(float f);
+float sim_f16_to_f32(uint16_t h);
+inline __half __float2half(float f) { return __half{sim_f32_to_f16(f)}; }
+inline float __half2float(__half h) { return sim_f16_to_f32(h.v); }
+inline float __expf(float x) { return expf(x); }
+inline float __logf(float x) { return logf(x); }
+#define CUDART_INF_F (__builtin_inff())
+
 // runtime API surface the launch helpers of common.cuh touch (never reached: the simulator calls the kernels directly)
 typedef int cudaError_t;
 typedef void* cudaStream_t;

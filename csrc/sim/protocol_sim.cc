@@ -20,6 +20,8 @@
 //   protocol_sim a2a <ranks> <max rows per peer> <row_vecs> <experts per rank> <ctas per peer> <calls>
 //   protocol_sim ep <ranks> <tokens> <hidden> <experts> <ctas> <calls> [fp8]
 //   protocol_sim fused rs|rs2|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
+//   protocol_sim decode <batch> <Hq> <Hkv> <max cached tokens> <kv splits> <page size, 0 = dense> <hidden> <intermediate> <vocab> [fp16]
+//                                                                    (one simulated GPU: one decode step, every kernel against a host oracle)
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -29,6 +31,7 @@
 #include "kernels/primitives_selftest.cu"     // PRODUCTION: every NVSHMEM-style device primitive of symm.cuh in one kernel
 #include "kernels/moe.cu"                     // PRODUCTION: MoE align / sort, tile swizzle, gathers, top-k reduce (+ reduce-scatter)
 #include "kernels/ep_a2a.cu"                  // PRODUCTION: low-latency all-to-all, EP counts / dispatch (bf16, fp8) / combine
+#include "kernels/decode.cu"                  // PRODUCTION: decode path (GEMV, norms, rotary + KV append, split-KV attention, sampling)
 #include "kernels/gemm_sm100.cuh"             // PRODUCTION: parameter block, tile order and communication bodies of the fused GEMM
 #include "kernels/gemm_sm100_2cta.cuh"        // PRODUCTION: tile order of the CTA-pair kernel
 
@@ -331,6 +334,7 @@ int run_collective(const std::string& op, int world, int max_vecs, int ctas, int
 
 #include "moe_ep_scenarios.h"
 #include "fused_gemm_scenarios.h"
+#include "decode_scenarios.h"
 
 int main(int argc, char** argv) {
   auto arg = [&](int i, int dflt) { return argc > i ? atoi(argv[i]) : dflt; };
@@ -343,7 +347,8 @@ int main(int argc, char** argv) {
   if (what == "a2a") return run_a2a(arg(2, 3), arg(3, 24), arg(4, 3), arg(5, 2), arg(6, 2), arg(7, 4));
   if (what == "ep") return run_ep(arg(2, 3), arg(3, 12), arg(4, 256), arg(5, 6), arg(6, 2), arg(7, 3), arg(8, 0));
   if (what == "fused") return run_fused(argc > 2 ? argv[2] : "rs", arg(3, 3), arg(4, 3 * 256), arg(5, 128), arg(6, 3), arg(7, 3), arg(8, 1), arg(9, 0), arg(10, 0));
+  if (what == "decode") return run_decode(arg(2, 3), arg(3, 14), arg(4, 2), arg(5, 70), arg(6, 5), arg(7, 0), arg(8, 128), arg(9, 64), arg(10, 300), arg(11, 0));
   if (what == "gemm_rs") return run_gemm_rs(arg(2, 3), arg(3, 3 * 96), arg(4, 72), arg(5, 32), arg(6, 4), arg(7, 3), arg(8, 0), arg(9, 2));
-  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep|fused [sizes...]\n");
+  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep|fused|decode [sizes...]\n");
   return 2;
 }

@@ -38,6 +38,7 @@ struct Fiber {
   ucontext_t ctx;
   std::unique_ptr<char[]> stack;
   bool done = false, at_barrier = false, at_warp = false;
+  unsigned warp_mask = 0xffffffffu;  // lanes named by the pending __syncwarp / shuffle
 };
 struct CtaRun {
   const std::function<void()>* kernel;
@@ -143,16 +144,24 @@ inline void* cta_thread(void* p) {
     }
     if (waiting == alive)  // everybody has arrived: open the barrier
       for (auto& f : r->fibers) f.at_barrier = false;
-    for (int w0 = 0; w0 < r->threads; w0 += 32) {  // warp barriers: all live lanes of a warp have arrived
-      bool open = true, any = false;
-      for (int t = w0; t < std::min(w0 + 32, r->threads); ++t) {
+    // warp barriers: a waiting lane is released when every live lane its mask names waits with the same mask (two
+    // half-warps that shuffle with 0x0000ffff / 0xffff0000 meet independently of each other, as on the device)
+    for (int w0 = 0; w0 < r->threads; w0 += 32) {
+      const int w1 = std::min(w0 + 32, r->threads);
+      for (int t = w0; t < w1; ++t) {
         const Fiber& f = r->fibers[t];
-        if (f.done) continue;
-        any = true;
-        open = open && f.at_warp;
+        if (f.done || !f.at_warp) continue;
+        const unsigned m = f.warp_mask;
+        bool open = true;
+        for (int u = w0; u < w1 && open; ++u) {
+          const Fiber& g = r->fibers[u];
+          if (!((m >> (u - w0)) & 1u) || g.done) continue;
+          open = g.at_warp && g.warp_mask == m;
+        }
+        if (open)
+          for (int u = w0; u < w1; ++u)
+            if ((m >> (u - w0)) & 1u) r->fibers[u].at_warp = false;
       }
-      if (any && open)
-        for (int t = w0; t < std::min(w0 + 32, r->threads); ++t) r->fibers[t].at_warp = false;
     }
   }
   return nullptr;
@@ -167,9 +176,10 @@ void sim_syncthreads() {
   f.at_barrier = true;
   swapcontext(&f.ctx, &r->sched);
 }
-void sim_syncwarp() {
+void sim_syncwarp(unsigned mask) {
   sim::CtaRun* r = sim::tl_cta;
   sim::Fiber& f = r->fibers[r->cur];
+  f.warp_mask = mask;
   f.at_warp = true;
   swapcontext(&f.ctx, &r->sched);
 }

@@ -32,6 +32,9 @@ struct uint2 {
 struct float2 {
   float x, y;
 };
+struct alignas(16) float4 {
+  float x, y, z, w;
+};
 inline int4 make_int4(int x, int y, int z, int w) { return int4{x, y, z, w}; }
 inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 inline float2 make_float2(float x, float y) { return float2{x, y}; }
@@ -60,21 +63,21 @@ extern thread_local unsigned sim_rng;
 
 // scheduler hooks (csrc/sim/sim_runtime.h)
 void sim_syncthreads();  // yield until every CUDA thread of the CTA has arrived
-void sim_syncwarp();     // ... every lane of this thread's warp
+void sim_syncwarp(unsigned mask = 0xffffffffu);  // ... every lane of this thread's warp that `mask` names
 void sim_yield();        // let the sibling threads of the CTA run (called from every flag poll)
 inline void __syncthreads() { sim_syncthreads(); }
-inline void __syncwarp(unsigned = 0xffffffffu) { sim_syncwarp(); }
+inline void __syncwarp(unsigned mask = 0xffffffffu) { sim_syncwarp(mask); }
 void* sim_warp_scratch();  // 32 x 16 bytes shared by the lanes of the calling thread's warp
 // warp shuffles: every lane publishes its value, the warp meets, every lane reads the source lane's value
 template <typename T>
-inline T __shfl_sync(unsigned, T v, int src_lane) {
+inline T __shfl_sync(unsigned mask, T v, int src_lane) {
   static_assert(sizeof(T) <= 16, "shuffle payload");
   char* w = static_cast<char*>(sim_warp_scratch());
   memcpy(w + (threadIdx.x & 31u) * 16, &v, sizeof(T));
-  sim_syncwarp();
+  sim_syncwarp(mask);
   T r;
   memcpy(&r, w + (unsigned(src_lane) & 31u) * 16, sizeof(T));
-  sim_syncwarp();
+  sim_syncwarp(mask);
   return r;
 }
 template <typename T>
@@ -146,6 +149,7 @@ uint16_t sim_f32_to_f16(float f);
 float sim_f16_to_f32(uint16_t h);
 inline __half __float2half(float f) { return __half{sim_f32_to_f16(f)}; }
 inline float __half2float(__half h) { return sim_f16_to_f32(h.v); }
+inline float rsqrtf(float x) { return 1.f / sqrtf(x); }
 inline float __expf(float x) { return expf(x); }
 inline float __logf(float x) { return logf(x); }
 #define CUDART_INF_F (__builtin_inff())

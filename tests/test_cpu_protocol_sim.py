@@ -49,7 +49,7 @@ def _stage(dst: Path) -> None:
     def copy(rel, cut):
         src = (ROOT / "csrc" / rel).read_text()
         if cut:
-            src = src[:src.index('\nextern "C"')]
+            src = src[:src.index(cut if isinstance(cut, str) else '\nextern "C"')] + (cut if isinstance(cut, str) else "")
         src = re.sub(r"extern\s+__shared__\s+(\w+)\s+(\w+)\[\];", r"SIM_DYN_SHARED(\1, \2);", src)  # dynamic shared memory
         (dst / "csrc" / rel).write_text(re.sub(r"__shared__\s+(\w+)\s+([^;]+);", shared, src))
 
@@ -58,6 +58,7 @@ def _stage(dst: Path) -> None:
     for rel in ("tutorials/notify_wait_tutorial.cu", "tutorials/overlap_tutorial.cu", "kernels/collectives.cu",
                 "kernels/primitives_selftest.cu", "kernels/moe.cu", "kernels/ep_a2a.cu"):
         copy(rel, True)
+    copy("kernels/decode.cu", "\n}  // namespace tdist\n")  # the kernels only: the launch helpers that follow use the runtime API
     # the fused tcgen05 GEMM: parameter block, tile order and communication bodies (everything before the kernel template),
     # plus the publisher loops of the kernel, i.e. the text between its [sim:...] markers, with a yield in their spin on the
     # shared tile counter (csrc/sim/fused_gemm_scenarios.h wraps them)
@@ -141,6 +142,13 @@ CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3,
           ("fused", "rs2", 2, 1024, 128, 2, 2, 1), ("fused", "rs2", 3, 1536, 128, 4, 3, 1), ("fused", "rs2", 4, 1536, 64, 2, 4, 1, 2),
           ("fused", "rs2", 4, 1536, 64, 4, 4, 1, 1, 1), ("fused", "rs2", 8, 2048, 64, 2, 2, 1), ("fused", "rs2", 3, 1152, 128, 2, 3, 0, 0, 1)]
 
+# one decode step through the production decode-path kernels on one simulated GPU: batch, query heads, KV heads, cached tokens,
+# KV splits, page size (0 = dense cache), hidden, intermediate, vocabulary, fp16. The head groups 14 / 2 = 7 and 16 / 2 = 8
+# and 1 cover the 4 + 2 + 1, 8 and 1-head passes; sequence 1 is always shorter than the number of splits (empty splits)
+CLEAN += [("decode", 3, 14, 2, 70, 5, 0, 128, 64, 300, 0), ("decode", 3, 14, 2, 70, 5, 16, 128, 64, 300, 1),
+          ("decode", 2, 16, 2, 45, 3, 8, 64, 40, 130, 0), ("decode", 5, 3, 3, 33, 9, 0, 64, 24, 77, 1),
+          ("decode", 16, 4, 1, 20, 2, 4, 64, 24, 50, 0), ("decode", 1, 6, 2, 200, 4, 32, 128, 64, 1100, 0)]
+
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
 def test_protocols_are_race_free(sims, case):
@@ -194,3 +202,23 @@ def test_negative_control_is_reported(sims, case):
     assert "ThreadSanitizer: data race" in out, out[-2000:]
     assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a)\.cu:\d+|(symm|ptx|gemm_sm100)\.cuh:\d+|fused_gemm_scenarios\.h:\d+", out), \
         "the report should point into the device sources"
+
+
+@pytest.mark.parametrize("name,good,bad,expect", [
+    ("rope_sign", "lane < 16 ? f[i] * cc[i] - other * sn[i]", "lane < 16 ? f[i] * cc[i] + other * sn[i]", "rope q"),
+    ("gqa_pass_offset", "const int h0 = kvh * g_total + g_offset;", "const int h0 = kvh * g_total;", "flash decode"),
+    ("page_slot", "size_t(pos % page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return", "size_t(pos / page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return", "flash decode"),
+    ("argmax_tie", "(ov == best && oi < bi)", "(ov == best && oi > bi)", "argmax"),
+])
+def test_decode_oracles_catch_a_mutated_kernel(sims, tmp_path, name, good, bad, expect):
+    """Mutation control for the decode scenario: one token of csrc/kernels/decode.cu changed in the staged copy (rotation
+    sign, head offset of the second GQA pass, slot inside a KV page, tie rule of the sampler) — the host oracle of that
+    kernel must report it."""
+    _stage(tmp_path / "stage")
+    f = tmp_path / "stage" / "csrc" / "kernels" / "decode.cu"
+    src = f.read_text()
+    assert good in src, "the mutated expression is no longer in decode.cu: update this test"
+    f.write_text(src.replace(good, bad))
+    _build(tmp_path / "stage", tmp_path / "sim_mut")
+    rc, out = _run(tmp_path / "sim_mut", ("decode", 3, 14, 2, 70, 5, 16, 128, 64, 300, 0))
+    assert rc == 1 and "DATA MISMATCH" in out and expect in out, out[-2000:]

@@ -6,12 +6,14 @@
 // Reference dispatcher: mega_triton_kernel/core/code_generator.py:31-89; task bodies:
 // mega_triton_kernel/kernels/{linear,mlp_fc1,norm,activation,elementwise,flash_attn,allreduce,barrier,prefetch}.py.
 //
-// B200 specifics: all decode linears are weight-streaming GEMVs on CUDA cores (M = batch <= 8 rows; the tensor
-// core would idle at this arithmetic intensity) with 16-byte loads, 8 in flight per lane, and the FIRST batch of
-// weight loads is issued BEFORE the dependency wait — weights do not depend on activations, so the HBM latency of
-// every task start hides behind the scoreboard wait. RMSNorm is folded into the consumer linear's prologue, SiLU*up
-// into fc1's epilogue and the residual add into the all-reduce, which removes three scoreboard hops per layer.
-// The all-reduce is NVLS multimem.ld_reduce with a per-tile cross-rank flag exchange.
+// B200 specifics: the decode linears are weight-streaming skinny GEMMs (M = batch <= 8 rows): the weights of all linear
+// tasks of a CTA form ONE stream of TMA stages (3-D tiled loads, 128 B swizzle) into per-warp stage buffers that runs
+// ahead across task boundaries — weights do not depend on activations, so the HBM latency of every task start hides
+// behind the scoreboard wait — and a stage is consumed with ldmatrix + mma.sync.m16n8k16 (weights as the M operand, the
+// batch as N; see LINEAR below). RMSNorm is folded into the consumer linear's prologue, SiLU*up into fc1's epilogue and
+// the residual add into the all-reduce, which removes three scoreboard hops per layer. The all-reduce is NVLS
+// multimem.ld_reduce with a per-tile cross-rank flag exchange.
+// The whole kernel also runs on the CPU under ThreadSanitizer with simulated ranks (csrc/sim/mega_scenarios.h).
 #include <cuda_bf16.h>
 #include <math_constants.h>
 

@@ -22,6 +22,8 @@
 //   protocol_sim fused rs|rs2|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
 //   protocol_sim decode <batch> <Hq> <Hkv> <max cached tokens> <kv splits> <page size, 0 = dense> <hidden> <intermediate> <vocab> [fp16]
 //                                                                    (one simulated GPU: one decode step, every kernel against a host oracle)
+//   protocol_sim mega <ranks> <CTAs> <layers> <batch> <steps> <graph: 0 fused, 1 op by op, 2 fused + one-task attention> <in-switch all-reduce 0/1>
+//                     <KV heads per rank> <query heads per KV head> <MLP columns per rank> <KV splits>     (the decode megakernel + its native builder)
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -34,6 +36,7 @@
 #include "kernels/decode.cu"                  // PRODUCTION: decode path (GEMV, norms, rotary + KV append, split-KV attention, sampling)
 #include "kernels/gemm_sm100.cuh"             // PRODUCTION: parameter block, tile order and communication bodies of the fused GEMM
 #include "kernels/gemm_sm100_2cta.cuh"        // PRODUCTION: tile order of the CTA-pair kernel
+#include "mega/megakernel.cu"                 // PRODUCTION: the decode megakernel (interpreter + every task body)
 
 #include <atomic>
 #include <string>
@@ -335,6 +338,7 @@ int run_collective(const std::string& op, int world, int max_vecs, int ctas, int
 #include "moe_ep_scenarios.h"
 #include "fused_gemm_scenarios.h"
 #include "decode_scenarios.h"
+#include "mega_scenarios.h"
 
 int main(int argc, char** argv) {
   auto arg = [&](int i, int dflt) { return argc > i ? atoi(argv[i]) : dflt; };
@@ -348,7 +352,12 @@ int main(int argc, char** argv) {
   if (what == "ep") return run_ep(arg(2, 3), arg(3, 12), arg(4, 256), arg(5, 6), arg(6, 2), arg(7, 3), arg(8, 0));
   if (what == "fused") return run_fused(argc > 2 ? argv[2] : "rs", arg(3, 3), arg(4, 3 * 256), arg(5, 128), arg(6, 3), arg(7, 3), arg(8, 1), arg(9, 0), arg(10, 0));
   if (what == "decode") return run_decode(arg(2, 3), arg(3, 14), arg(4, 2), arg(5, 70), arg(6, 5), arg(7, 0), arg(8, 128), arg(9, 64), arg(10, 300), arg(11, 0));
+  if (what == "mega") return run_mega(arg(2, 2), arg(3, 4), arg(4, 2), arg(5, 2), arg(6, 3), arg(7, 0), arg(8, 1), arg(9, 1), arg(10, 2), arg(11, 128), arg(12, 3));
   if (what == "gemm_rs") return run_gemm_rs(arg(2, 3), arg(3, 3 * 96), arg(4, 72), arg(5, 32), arg(6, 4), arg(7, 3), arg(8, 0), arg(9, 2));
-  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep|fused|decode [sizes...]\n");
+  fprintf(stderr, "usage: protocol_sim queue|ag_gemm|gemm_rs|coll|moe_utils|moe_rs|a2a|ep|fused|decode|mega [sizes...]\n");
   return 2;
 }
+
+// the native task-graph builder and scheduler of the megakernel, as it is (host code; its "device" memory is host memory here
+// and its launch goes to tdist_mega_launch in mega_scenarios.h). Last: it ends with file-scope using-directives.
+#include "mega/builder.cc"

@@ -10,6 +10,7 @@
 //   NVLS:     multimem_st_* writes every rank's copy, multimem_ld_reduce_* reads every rank's copy and adds in fp32
 // Every flag poll yields to the sibling CUDA threads of the CTA (they are fibers of one OS thread).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 struct SimMc {  // the simulated node's multicast window (set by sim::Node when multicast is enabled)
@@ -61,6 +62,11 @@ inline void red_add_release_sys(uint32_t* p, uint32_t v) {
   sim_straggle(sim_rank);
   __atomic_fetch_add(p, v, kRelease);
 }
+// "fence.acq_rel.gpu; red.relaxed.gpu" in the sources (the scoreboard signal of the megakernel): one release RMW, as above
+inline void red_add_relaxed_gpu(uint32_t* p, uint32_t v) {
+  sim_jitter();
+  __atomic_fetch_add(p, v, kRelease);
+}
 inline uint32_t atom_add_acq_rel_gpu(uint32_t* p, uint32_t v) { return __atomic_fetch_add(p, v, __ATOMIC_ACQ_REL); }
 inline uint32_t ld_acquire_sys(const uint32_t* p) {
   sim_yield();
@@ -78,8 +84,7 @@ inline void fence_acq_rel_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void fence_acq_rel_gpu() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void fence_sc_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 
-// ---- asynchronous-copy / mbarrier / tensor-memory instructions: not modelled. Code paths that need them (the TMA ring of the
-// point-to-point AG push, the GEMM main loop) are not simulated; the stubs only let their callers compile.
+// ---- 1-D bulk copies (the TMA ring of the point-to-point AG push): not modelled; the stubs only let their callers compile.
 #define TDIST_SIM_UNMODELLED(name)                  \
   template <typename... A>                          \
   inline void name(A&&...) {                        \
@@ -89,15 +94,98 @@ inline void fence_sc_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 TDIST_SIM_UNMODELLED(bulk_g2s)
 TDIST_SIM_UNMODELLED(bulk_s2g)
 TDIST_SIM_UNMODELLED(bulk_commit)
-TDIST_SIM_UNMODELLED(mbar_init)
-TDIST_SIM_UNMODELLED(mbar_wait)
-TDIST_SIM_UNMODELLED(mbar_arrive_expect_tx)
-TDIST_SIM_UNMODELLED(fence_barrier_init)
-TDIST_SIM_UNMODELLED(fence_proxy_async)
 template <int N>
 inline void bulk_wait() { abort(); }
 template <int N>
 inline void bulk_wait_read() { abort(); }
+
+// ---- mbarrier + tiled TMA loads, as far as the decode megakernel uses them: one arrival per phase, the transaction bytes
+// of the phase delivered by ONE tensor load. The load is performed at issue (the copy engine of the simulator is infinitely
+// fast), which completes the phase; the barrier word counts completed phases. All parties are fibers of one CTA.
+inline uint32_t smem_u32(const void* p) { return uint32_t(reinterpret_cast<uintptr_t>(p)); }
+inline void mbar_init(uint64_t* bar, uint32_t) { *bar = 0; }
+inline void fence_barrier_init() {}
+inline void fence_proxy_async() {}
+inline void fence_proxy_async_shared() {}
+inline void mbar_arrive_expect_tx(uint64_t*, uint32_t) {}
+inline void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while ((*bar & 1u) == parity) sim_yield();  // the phase with this parity has not completed yet
+}
+inline void prefetch_tensormap(const void*) {}
+inline void tma_prefetch_3d(const void*, int, int, int) {}
+inline void prefetch_l2_bulk(const void*, uint32_t) {}
+// box {box[0], box[1], box[2]} at element coordinates (c0, c1, c2); lands densely as [z][y][x]; elements outside the tensor
+// are zero; with the 128 B swizzle the 16-byte chunks of every 128 B line are XORed with bits 7-9 of the line's address
+inline void tma_load_3d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2) {
+  SimTmap t;
+  memcpy(&t, tmap, sizeof(t));
+  char* dst = static_cast<char*>(smem_dst);
+  const uint32_t row_bytes = t.box[0] * t.elt_bytes;
+  if (t.swizzle == uint32_t(CU_TENSOR_MAP_SWIZZLE_128B) && (row_bytes != 128 || (reinterpret_cast<uintptr_t>(dst) & 127u) != 0)) {
+    fprintf(stderr, "sim: tma_load_3d: a 128 B-swizzled box needs 128-byte rows and a 128-byte aligned destination\n");
+    abort();
+  }
+  for (uint32_t z = 0; z < t.box[2]; ++z)
+    for (uint32_t y = 0; y < t.box[1]; ++y) {
+      char* line = dst + (size_t(z) * t.box[1] + y) * row_bytes;
+      const uint32_t phase = t.swizzle == uint32_t(CU_TENSOR_MAP_SWIZZLE_128B) ? uint32_t(reinterpret_cast<uintptr_t>(line) >> 7) & 7u : 0u;
+      const uint64_t gy = uint64_t(c1) + y, gz = uint64_t(c2) + z;
+      const bool row_ok = c1 >= 0 && c2 >= 0 && gy < t.dims[1] && gz < t.dims[2];
+      for (uint32_t x = 0; x < t.box[0]; ++x) {
+        const uint64_t gx = uint64_t(c0) + x;
+        uint32_t byte = x * t.elt_bytes;
+        byte = (((byte >> 4) ^ phase) << 4) | (byte & 15u);
+        if (row_ok && c0 >= 0 && gx < t.dims[0])
+          memcpy(line + byte, t.base + gz * t.strides[1] + gy * t.strides[0] + gx * t.elt_bytes, t.elt_bytes);
+        else
+          memset(line + byte, 0, t.elt_bytes);
+      }
+    }
+  ++*bar;
+}
+
+// ---- warp-level matrix instructions of the megakernel's linear task (the staging step replaces the two inline-asm
+// statements of csrc/mega/megakernel.cu by calls to these): lanes exchange their operands through the warp scratch
+// ldmatrix.sync.aligned.m8n8.x4.b16: lane l supplies the address of row l % 8 of matrix l / 8; register j of lane l receives
+// elements 2 (l % 4), 2 (l % 4) + 1 of row l / 4 of matrix j
+inline void sim_ldmatrix_x4(uint32_t (&a)[4], const void* smem_ptr) {
+  char* w = static_cast<char*>(sim_warp_scratch()) + 512;
+  const unsigned lane = threadIdx.x & 31u;
+  memcpy(w + lane * 8, &smem_ptr, sizeof(void*));
+  sim_syncwarp();
+  for (unsigned j = 0; j < 4; ++j) {
+    const char* row;
+    memcpy(&row, w + (j * 8 + lane / 4) * 8, sizeof(void*));
+    memcpy(&a[j], row + (lane % 4) * 4, 4);
+  }
+  sim_syncwarp();
+}
+// mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32: D[16 x 8] += A[16 x 16] B[16 x 8]. With g = lane / 4, t = lane % 4:
+// a0 = A[g][2t, 2t+1], a1 = A[g+8][2t, 2t+1], a2 = A[g][2t+8, 2t+9], a3 = A[g+8][2t+8, 2t+9]; b0 = B[2t, 2t+1][g],
+// b1 = B[2t+8, 2t+9][g]; d0, d1 = D[g][2t, 2t+1], d2, d3 = D[g+8][2t, 2t+1]
+inline void sim_mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  char* w = static_cast<char*>(sim_warp_scratch()) + 512;
+  const unsigned lane = threadIdx.x & 31u, g = lane / 4, t = lane % 4;
+  uint32_t mine[6] = {a[0], a[1], a[2], a[3], b0, b1};
+  memcpy(w + lane * 32, mine, sizeof(mine));
+  sim_syncwarp();
+  auto elem = [&](unsigned src_lane, unsigned reg, unsigned e) {
+    uint32_t v;
+    memcpy(&v, w + src_lane * 32 + reg * 4, 4);
+    return __bfloat162float(__nv_bfloat16{uint16_t(e ? v >> 16 : v & 0xffffu)});
+  };
+  for (unsigned r = 0; r < 2; ++r)      // rows g, g + 8
+    for (unsigned c = 0; c < 2; ++c) {  // columns 2t, 2t + 1
+      float acc = d[r * 2 + c];
+      const unsigned n = 2 * t + c;
+      for (unsigned k = 0; k < 16; ++k) {
+        const unsigned tk = (k % 8) / 2, e = k % 2, hi = k / 8;
+        acc += elem(g * 4 + tk, r + 2 * hi, e) * elem(n * 4 + tk, 4 + hi, e);
+      }
+      d[r * 2 + c] = acc;
+    }
+  sim_syncwarp();
+}
 
 // ---- LL packets: a 16-byte packet is {d0, flag, d1, flag}; each 8-byte half carries its own flag
 inline void st_relaxed_sys_v4(void* p, const int4& v) {

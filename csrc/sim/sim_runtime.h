@@ -47,7 +47,7 @@ struct CtaRun {
   SimCta state;
   ucontext_t sched;
   std::vector<Fiber> fibers;
-  std::vector<char> warp_scratch;  // 32 x 16 bytes per warp: shuffles
+  std::vector<char> warp_scratch;  // per warp: 32 x 16 bytes for shuffles, 32 x 32 bytes for the matrix instructions
   int cur = 0;
 };
 inline thread_local CtaRun* tl_cta = nullptr;
@@ -110,7 +110,7 @@ inline void* cta_thread(void* p) {
     std::lock_guard<std::mutex> g(g_live_mu);
     g_live.push_back(r);
   }
-  r->warp_scratch.assign(size_t(r->threads + 31) / 32 * 512, 0);
+  r->warp_scratch.assign(size_t(r->threads + 31) / 32 * 2048, 0);
   for (int t = 0; t < r->threads; ++t) {
     Fiber& f = r->fibers[t];
     f.stack.reset(new char[kFiberStack]);
@@ -185,7 +185,7 @@ void sim_syncwarp(unsigned mask) {
 }
 void* sim_warp_scratch() {
   sim::CtaRun* r = sim::tl_cta;
-  return r->warp_scratch.data() + size_t(r->cur / 32) * 512;
+  return r->warp_scratch.data() + size_t(r->cur / 32) * 2048;
 }
 void sim_yield() {  // a polling thread lets its siblings run: on the GPU they run in parallel
   sim::CtaRun* r = sim::tl_cta;

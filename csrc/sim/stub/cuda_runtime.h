@@ -22,6 +22,7 @@
 #define __restrict__
 #define __launch_bounds__(...)
 #define __align__(n) alignas(n)
+#define __grid_constant__
 
 struct int4 {
   int x, y, z, w;
@@ -38,6 +39,7 @@ struct alignas(16) float4 {
 inline int4 make_int4(int x, int y, int z, int w) { return int4{x, y, z, w}; }
 inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 inline float2 make_float2(float x, float y) { return float2{x, y}; }
+inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
 
 struct sim_dim3 {
   unsigned x = 1, y = 1, z = 1;
@@ -58,8 +60,10 @@ extern thread_local sim_dim3 threadIdx, blockIdx, blockDim, gridDim;
 extern thread_local SimCta* sim_cta;
 extern thread_local unsigned sim_rng;
 #define SIM_SHARED(type_t, name) type_t& name = *static_cast<type_t*>(sim_cta->shared_buf(sizeof(type_t), #name))
-// `extern __shared__ T name[];` (dynamic shared memory): a fixed 96 KB per CTA
-#define SIM_DYN_SHARED(type_t, name) type_t* name = static_cast<type_t*>(sim_cta->shared_buf(96 << 10, "dynamic"))
+// `extern __shared__ T name[];` (dynamic shared memory): the 227 KB a CTA can opt into, 1024-byte aligned (TMA swizzle
+// patterns are functions of the shared-memory address)
+#define SIM_DYN_SHARED(type_t, name) \
+  type_t* name = reinterpret_cast<type_t*>((reinterpret_cast<uintptr_t>(sim_cta->shared_buf(232448 + 1024, "dynamic")) + 1023) & ~uintptr_t(1023))
 
 // scheduler hooks (csrc/sim/sim_runtime.h)
 void sim_syncthreads();  // yield until every CUDA thread of the CTA has arrived
@@ -151,6 +155,10 @@ inline __half __float2half(float f) { return __half{sim_f32_to_f16(f)}; }
 inline float __half2float(__half h) { return sim_f16_to_f32(h.v); }
 inline float rsqrtf(float x) { return 1.f / sqrtf(x); }
 inline float __expf(float x) { return expf(x); }
+inline float __frcp_rn(float x) { return 1.f / x; }
+template <typename T>
+inline T __ldcg(const T* p) { return *p; }
+inline long long clock64() { return 0; }
 inline float __logf(float x) { return logf(x); }
 #define CUDART_INF_F (__builtin_inff())
 
@@ -159,4 +167,33 @@ typedef int cudaError_t;
 typedef void* cudaStream_t;
 constexpr cudaError_t cudaSuccess = 0;
 inline cudaError_t cudaGetLastError() { return cudaSuccess; }
+// "device" memory of host code that is compiled into the simulator as it is (csrc/mega/builder.cc): host memory
+enum cudaMemcpyKind { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2 };
+enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount = 16 };
+template <typename T>
+inline cudaError_t cudaMalloc(T** p, size_t n) {
+  *p = static_cast<T*>(aligned_alloc(256, (n + 255) / 256 * 256));
+  return *p != nullptr ? cudaSuccess : 2;
+}
+inline cudaError_t cudaFree(void* p) {
+  free(p);
+  return cudaSuccess;
+}
+inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) {
+  memcpy(d, s, n);
+  return cudaSuccess;
+}
+inline cudaError_t cudaMemset(void* d, int v, size_t n) {
+  memset(d, v, n);
+  return cudaSuccess;
+}
+inline cudaError_t cudaGetDevice(int* d) {
+  *d = 0;
+  return cudaSuccess;
+}
+inline cudaError_t cudaDeviceGetAttribute(int* v, cudaDeviceAttr, int) {
+  *v = 148;
+  return cudaSuccess;
+}
+inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 inline const char* cudaGetErrorString(cudaError_t) { return "simulated"; }

@@ -33,7 +33,7 @@ def _stage(dst: Path) -> None:
     """Lay the sources out as in the repository, with the host ptx.cuh in place of the device one. The kernel files are
     copied with two mechanical edits: cut before their launch wrappers (they use <<< >>>), and `__shared__ T a[..], b[..];`
     becomes references to per-CTA buffers. csrc/kernels/common.cuh and csrc/device/symm.cuh are the REAL ones."""
-    for d in ("include", "csrc/device", "csrc/kernels", "csrc/tutorials"):
+    for d in ("include", "csrc/device", "csrc/kernels", "csrc/tutorials", "csrc/mega", "csrc/runtime"):
         (dst / d).mkdir(parents=True)
     shutil.copy(ROOT / "include" / "tdist.h", dst / "include" / "tdist.h")
     shutil.copy(SIM / "shim" / "device" / "ptx.cuh", dst / "csrc" / "device" / "ptx.cuh")
@@ -46,11 +46,15 @@ def _stage(dst: Path) -> None:
             out.append(f"typedef {m.group(1)} {name}_sim_t{decl[len(name):]}; SIM_SHARED({name}_sim_t, {name});")
         return " ".join(out)
 
-    def copy(rel, cut):
+    def copy(rel, cut, asm=()):
         src = (ROOT / "csrc" / rel).read_text()
         if cut:
             src = src[:src.index(cut if isinstance(cut, str) else '\nextern "C"')] + (cut if isinstance(cut, str) else "")
-        src = re.sub(r"extern\s+__shared__\s+(\w+)\s+(\w+)\[\];", r"SIM_DYN_SHARED(\1, \2);", src)  # dynamic shared memory
+        src = re.sub(r"extern\s+__shared__\s+(?:__align__\(\d+\)\s+)?(\w+)\s+(\w+)\[\];", r"SIM_DYN_SHARED(\1, \2);", src)  # dynamic shared memory
+        for name in asm:  # a function whose body is one inline-asm statement: call the host emulation of that instruction instead
+            a = src.index("asm volatile(", src.index(f" void {name}("))
+            args = re.findall(r"[&\s(]\(?&?(\w+)\)?(?:\[\d+\])?\s*[,)]", src[src.index(f" void {name}("):a])
+            src = src[:a] + f"ptx::sim_{name}({', '.join(args)});" + src[src.index("\n}", a):]
         (dst / "csrc" / rel).write_text(re.sub(r"__shared__\s+(\w+)\s+([^;]+);", shared, src))
 
     copy("device/symm.cuh", False)
@@ -59,6 +63,12 @@ def _stage(dst: Path) -> None:
                 "kernels/primitives_selftest.cu", "kernels/moe.cu", "kernels/ep_a2a.cu"):
         copy(rel, True)
     copy("kernels/decode.cu", "\n}  // namespace tdist\n")  # the kernels only: the launch helpers that follow use the runtime API
+    # the decode megakernel with its native builder: the interpreter kernel up to its launch wrapper, ldmatrix / mma.sync
+    # through the host emulations of csrc/sim/shim/device/ptx.cuh; builder.cc and mega.h as they are, on a stand-in driver.h
+    copy("mega/megakernel.cu", True, asm=("ldmatrix_x4", "mma_bf16_16816"))
+    for rel in ("mega/mega.h", "mega/builder.cc"):
+        shutil.copy(ROOT / "csrc" / rel, dst / "csrc" / rel)
+    shutil.copy(SIM / "shim" / "runtime" / "driver.h", dst / "csrc" / "runtime" / "driver.h")
     # the fused tcgen05 GEMM: parameter block, tile order and communication bodies (everything before the kernel template),
     # plus the publisher loops of the kernel, i.e. the text between its [sim:...] markers, with a yield in their spin on the
     # shared tile counter (csrc/sim/fused_gemm_scenarios.h wraps them)
@@ -149,6 +159,12 @@ CLEAN += [("decode", 3, 14, 2, 70, 5, 0, 128, 64, 300, 0), ("decode", 3, 14, 2, 
           ("decode", 2, 16, 2, 45, 3, 8, 64, 40, 130, 0), ("decode", 5, 3, 3, 33, 9, 0, 64, 24, 77, 1),
           ("decode", 16, 4, 1, 20, 2, 4, 64, 24, 50, 0), ("decode", 1, 6, 2, 200, 4, 32, 128, 64, 1100, 0)]
 
+# the decode megakernel + its native builder: ranks, CTAs, layers, batch, steps, graph (0 fused, 1 op by op + barrier op,
+# 2 fused + one-task attention), in-switch all-reduce, KV heads per rank, query heads per KV head, MLP columns per rank, KV splits
+CLEAN += [("mega", 2, 4, 2, 2, 3, 0, 1, 1, 2, 128, 3), ("mega", 3, 5, 2, 3, 3, 1, 0, 2, 3, 128, 4), ("mega", 4, 3, 1, 8, 2, 2, 1, 1, 8, 64, 5),
+          ("mega", 8, 2, 1, 1, 2, 0, 1, 1, 1, 64, 2), ("mega", 1, 1, 2, 3, 2, 1, 0, 2, 4, 128, 3), ("mega", 2, 7, 1, 4, 4, 2, 0, 2, 4, 64, 4),
+          ("mega", 3, 4, 2, 2, 3, 0, 1, 1, 2, 128, 16), ("mega", 1, 2, 1, 2, 1, 0, 0, 1, 12, 64, 3)]
+
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
 def test_protocols_are_race_free(sims, case):
@@ -164,6 +180,9 @@ def test_straggler_with_changing_sizes(sims):
     rc, out = _run(sims[0], ("gemm_rs", 4, 768, 64, 16, 1, 2, 1, 3), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "30"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     rc, out = _run(sims[0], ("ag_gemm", 4, 192, 40, 16, 1, 3, 3, 1, 3), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "10"})
+    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
+    # the megakernel with one rank 5 ms late at every cross-rank flag: 3 steps back to back on double-buffered partials
+    rc, out = _run(sims[0], ("mega", 3, 3, 1, 2, 3, 0, 1, 1, 2, 64, 2), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     for op in ("ar2", "rsmc", "ag_llmc"):  # production collectives, 8 ranks, alternating sizes, one rank 5 ms late per flag
         rc, out = _run(sims[0], ("coll", op, 8, 64, 2, 3, 1), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
@@ -191,7 +210,8 @@ def test_fused_gemm_rs_fixed_flag_rows_survive_the_straggler(sims):
 @pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
                                   ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
                                   ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2),
-                                  ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1)],
+                                  ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1),
+                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2)],
                          ids=lambda c: "-".join(map(str, c[:2])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
@@ -200,7 +220,7 @@ def test_negative_control_is_reported(sims, case):
         if "ThreadSanitizer: data race" in out:
             break
     assert "ThreadSanitizer: data race" in out, out[-2000:]
-    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a)\.cu:\d+|(symm|ptx|gemm_sm100)\.cuh:\d+|fused_gemm_scenarios\.h:\d+", out), \
+    assert re.search(r"(notify_wait_tutorial|overlap_tutorial|collectives|primitives_selftest|moe|ep_a2a|megakernel)\.cu:\d+|(symm|ptx|gemm_sm100)\.cuh:\d+|fused_gemm_scenarios\.h:\d+", out), \
         "the report should point into the device sources"
 
 
@@ -222,3 +242,24 @@ def test_decode_oracles_catch_a_mutated_kernel(sims, tmp_path, name, good, bad, 
     _build(tmp_path / "stage", tmp_path / "sim_mut")
     rc, out = _run(tmp_path / "sim_mut", ("decode", 3, 14, 2, 70, 5, 16, 128, 64, 300, 0))
     assert rc == 1 and "DATA MISMATCH" in out and expect in out, out[-2000:]
+
+
+@pytest.mark.parametrize("name,good,bad,expect", [
+    # the ldmatrix address ignores the 128 B swizzle the TMA applied to the stage buffer: wrong weights
+    ("swizzle", "const uint8_t* ap = lp + ((uint32_t(s4 * 2) + a_hi) ^ ph) * 16u;", "const uint8_t* ap = lp + (uint32_t(s4 * 2) + a_hi) * 16u;", "DATA MISMATCH"),
+    # tasks wait for the scoreboard value of the PREVIOUS step: consumers run before their producers
+    ("scoreboard_target", "const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1", "const uint32_t tgt0 = (step - 1) * uint32_t(t.dep0_cnt), tgt1",
+     "ThreadSanitizer: data race"),
+    # the "up" half of a gate | up weight tile is fetched from the gate rows
+    ("pair_rows", "c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);", "c1 = int(e.row0 + blk * e.R);", "DATA MISMATCH"),
+])
+def test_megakernel_mutations_are_caught(sims, tmp_path, name, good, bad, expect):
+    """Mutation control for the megakernel scenario: one expression of csrc/mega/megakernel.cu changed in the staged copy."""
+    _stage(tmp_path / "stage")
+    f = tmp_path / "stage" / "csrc" / "mega" / "megakernel.cu"
+    src = f.read_text()
+    assert good in src, "the mutated expression is no longer in megakernel.cu: update this test"
+    f.write_text(src.replace(good, bad))
+    _build(tmp_path / "stage", tmp_path / "sim_mut")
+    rc, out = _run(tmp_path / "sim_mut", ("mega", 2, 3, 1, 2, 2, 0, 0, 1, 2, 64, 2), {"TDIST_SIM_WATCHDOG_S": "240"})
+    assert rc != 0 and expect in out, out[-2000:]

@@ -157,6 +157,13 @@ int tdist_gemm_tile_order(int mode, int M, int N, int world, int rank, int block
  * `epoch` on success, -1 otherwise. Call on every rank. */
 int tdist_primitives_selftest(const tdist_symm_ctx* ctx, void* buf, uint32_t* flags, uint32_t epoch, void* stream);
 
+/* Bandwidth probes of the data paths the fused kernels are built from (csrc/kernels/link_probe.cu; pure data movers, no
+ * cross-rank waits). mode: 0 local copy, 1 NVLS broadcast push, 2 unicast push to the peers, 3 pull from the peers, 4 NVLS
+ * pull-reduce, 5 bulk-copy ring to the multicast address, 6 bulk-copy ring pulling from a peer. `src` / `out`: local
+ * buffers of `bytes` (x world for the pull modes, see the source); `symm`: symmetric [world][bytes]. bytes % 16 == 0. */
+int tdist_link_probe(const tdist_symm_ctx* ctx, int mode, const void* src, void* symm, void* out, size_t bytes, int grid,
+                     int threads, int unroll, void* stream);
+
 /* ---- MoE helpers (csrc/kernels/moe.cu; reference csrc/lib/moe_utils.cu, kernels/nvidia/moe_utils.py) ---- */
 /* sort (token,k) pairs by expert, pad every expert to block_m rows. meta[0] = padded rows, meta[1] = blocks. */
 int tdist_moe_align_sort(const int* topk_ids, int num_pairs, int num_experts, int block_m, int* sorted_pair_ids,

@@ -97,6 +97,52 @@ def test_ctypes_prototypes_match_the_c_header():
     assert set(undeclared) <= local_decl, undeclared
 
 
+def test_locally_declared_ctypes_prototypes_match_the_c_header():
+    """Entry points whose ctypes prototype is written next to the only caller (tutorials 01 / 07 / 08, the link probe, the
+    no-alloc test) instead of triton_dist/_lib.py: the `argtypes` expression there, evaluated, has the argument count and
+    kinds of the declaration in include/tdist.h."""
+    import ctypes
+    import re
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    header = re.sub(r"/\*.*?\*/", " ", (root / "include" / "tdist.h").read_text(), flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(?:int|void\s*\*|size_t|const\s+char\s*\*)\s+(tdist_\w+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        protos[m.group(1)] = [q.strip() for q in m.group(2).replace("\n", " ").split(",") if q.strip() and q.strip() != "void"]
+
+    def kind_c(param):
+        if "*" in param or "[" in param:
+            return "ptr"
+        t = param.rsplit(" ", 1)[0].replace("const ", "").strip()
+        return {"int": "i32", "uint32_t": "i32", "unsigned": "i32", "size_t": "i64", "long long": "i64", "float": "f32"}[t]
+
+    kind_py = {ctypes.c_void_p: "ptr", ctypes.c_int: "i32", ctypes.c_uint32: "i32", ctypes.c_size_t: "i64", ctypes.c_longlong: "i64",
+               ctypes.c_float: "f32"}
+    env = {"ctypes": ctypes, "vp": ctypes.c_void_p, "i32": ctypes.c_int, "f32": ctypes.c_float, "ll": ctypes.c_longlong}
+    files = list((root / "tutorials").glob("*.py")) + [root / "tests" / "test_zz_no_alloc.py",
+                                                       root / "triton_dist" / "benchmark" / "bench_link_probe.py"]
+    checked = set()
+    for py in files:
+        text = py.read_text()
+        for m in re.finditer(r"\.(tdist_\w+)\.argtypes\s*=\s*", text):
+            # the expression runs to the end of the line on which its brackets are balanced
+            end, depth = m.end(), 0
+            while True:
+                ch = text[end]
+                depth += ch in "([" 
+                depth -= ch in ")]"
+                if ch == "\n" and depth == 0:
+                    break
+                end += 1
+            got = [kind_py[t] for t in eval(text[m.end():end], dict(env))]
+            want = [kind_c(q) for q in protos[m.group(1)]]
+            assert got == want, f"{py.name}: {m.group(1)}: ctypes {got} vs header {want}"
+            checked.add(m.group(1))
+    assert {"tdist_tutorial_queue", "tdist_tutorial_ag_gemm", "tdist_tutorial_gemm_rs", "tdist_link_probe", "tdist_flash_decode_noalloc",
+            "tdist_flash_decode"} <= checked, checked
+
+
 def test_ctypes_structs_match_the_c_header(tmp_path):
     """The ctypes mirrors of the C ABI structs (context, GEMM / fused arguments, megakernel op) have the size and the field
     offsets a C compiler gives include/tdist.h: same field order, types and padding."""

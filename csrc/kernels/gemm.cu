@@ -356,6 +356,11 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
     }
     return tdist_gemm(&g, stream);
   }
+  if (W == 1 && f->mode == TDIST_GEMM_AR) {  // nothing to reduce: the plain GEMM, written to the caller's output
+    tdist_gemm_args g = *a;
+    g.c = f->out;
+    return tdist_gemm(&g, stream);
+  }
   if (f->mode == TDIST_GEMM_AG) {
     // a->a = own shard [M/W, K]; f->ws = symmetric workspace [2][M][K]; a->M = full M
     if (a->M % W != 0) {

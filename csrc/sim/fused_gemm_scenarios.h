@@ -112,6 +112,10 @@ void fused_pair_cta(const tdist::GemmParams& p) {
 // AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
 // smaller) or 2 (even calls smaller). `fixed_rows`: one flag row per source rank of constant length (GemmParams::flag_row).
 int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate, int fixed_rows) {
+  if (mode == "rs2" && (ctas < 2 || ctas % 2 != 0)) {
+    fprintf(stderr, "fused rs2: the CTA-pair form needs an even number of CTAs\n");
+    return 2;
+  }
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
@@ -148,7 +152,7 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       p.counters = counters;
       p.ps = PhaseState{state, state + 1};
       p.ar_one_shot = one_shot;
-      p.use_mc = mc;
+      p.use_mc = mc != 0 && node.mc_window != nullptr;  // the host code's rule (a single rank has no multicast mapping)
       p.rs_unit_rows = 16;
       p.flag_row = fixed_rows ? int(flag_words / W) : 0;  // TDIST_FIXED_FLAG_LAYOUT=1 of csrc/kernels/gemm.cu
       // RS and one-shot AR write a local result; two-shot AR writes the symmetric output of every rank

@@ -22,8 +22,23 @@ OPS = ["ar1", "ar2", "ar1mc", "ar2mc", "ar1mc_inplace", "ar2mc_inplace", "ag_pul
 
 def random_case(rng):
     W = rng.choice([1, 2, 2, 3, 4, 5, 8])
-    kind = rng.choice(["coll"] * 6 + ["moe_rs", "a2a", "ep", "queue", "ag_gemm", "gemm_rs"])
+    kind = rng.choice(["coll"] * 6 + ["moe_rs", "a2a", "ep", "queue", "ag_gemm", "gemm_rs", "fused", "decode", "mega", "mega"])
     c = rng.choice
+    if kind == "decode":  # one simulated GPU
+        hkv = c([1, 2, 3])
+        page = c([0, 0, 4, 16])
+        return ["decode", c([1, 2, 5, 16]), hkv * c([1, 2, 3, 4, 7, 8, 12]), hkv, c([1, 9, 40, 90]), c([1, 2, 5, 11]), page,
+                c([64, 128, 200]), c([8, 40, 64]), c([3, 50, 333]), c([0, 1])], 1
+    if kind == "mega":
+        W = c([1, 2, 2, 3, 4])
+        graph = c([0, 0, 1, 2])
+        return ["mega", W, c([1, 2, 3, 5, 9]), c([1, 1, 2]), c([1, 2, 3, 8]), c([1, 2, 3]), graph, c([0, 1]), c([1, 2]),
+                c([1, 2, 4, 8] if graph == 2 else [1, 2, 4, 8, 9]), c([64, 128, 192]), c([1, 2, 3, 7, 16])], W
+    if kind == "fused":
+        mode = c(["rs", "rs2", "ar1", "ar2"])
+        M = W * c([128, 256, 384]) if mode != "rs2" else W * c([256, 384, 512])
+        ctas = c([2, 4, 6]) if mode == "rs2" else c([1, 2, 3, 5])  # the CTA-pair form needs whole pairs
+        return ["fused", mode, W, M, c([64, 128, 192]), ctas, c([1, 2, 4]), c([0, 1]), c([0, 0, 1, 2]), 1], W
     if kind == "coll":
         return ["coll", c(OPS), W, c([1, 2, 3, 7, 16, 33, 96, 200]), c([1, 2, 3, 5]), c([1, 2, 3, 5]), c([0, 0, 1, 2])], W
     if kind == "moe_rs":

@@ -607,6 +607,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
             if (e < 0) continue;
             b_row += e * p.N;
           }
+          // [sim:ag_wait begin] (csrc/sim runs the text between these markers against ag_push_mc_body on the CPU)
           const CUtensorMap* ta = &p.tma_a[0];
           int a_row = tc.row0;
           const uint32_t* slab_flags = nullptr;
@@ -633,6 +634,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               __syncwarp();
               ptx::fence_proxy_async();
             }
+            // [sim:ag_wait end]
             if (lane == 0) {
               ptx::mbar_wait(empty_bar + stage, ph ^ 1);
               ptx::mbar_arrive_expect_tx(full_bar + stage, L::kStageBytes);

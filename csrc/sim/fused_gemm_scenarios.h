@@ -108,6 +108,119 @@ void fused_pair_cta(const tdist::GemmParams& p) {
   phase_end(p.ps, phase_base, 2);
 }
 
+// AG + GEMM, the in-switch broadcast form (the flagship's first half at 3+ ranks): comm CTAs run the real ag_push_mc_body;
+// warp 0 of every GEMM CTA walks the kernel's tile order and runs the producer warp's arrival wait — the text between the
+// [sim:ag_wait] markers — in front of a stand-in for the TMA loads of a k block: plain reads of the 128 x 64 A elements the
+// loads would fetch (the rows of the tile that belong to its shard), summed per tile for the comparison with the host.
+template <int BLOCK_N>
+void fused_ag_cta(const tdist::GemmParams& p, unsigned long long* sums) {
+  using namespace tdist;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int tiles_m = blocks_per_shard(p) * p.ctx.world;
+  const int tiles = tiles_m * tiles_n;
+  const int num_k = (p.K + kBlockK - 1) / kBlockK;
+  const int num_gemm = gridDim.x - p.num_comm_ctas;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+  const uint32_t phase_base = phase_begin(p.ps);
+  const uint32_t epoch = phase_base + 2;
+  const int parity = (epoch >> 1) & 1;
+  if (gemm_cta < 0) {
+    ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+  } else if (warp == 0) {
+    const int bps = blocks_per_shard(p);
+    for (int t = gemm_cta; t < tiles; t += num_gemm) {
+      const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+      unsigned long long sum = 0;
+#include "kernels/gemm_ag_wait.inc"
+        if (lane == 0) {  // stand-in for the loads of k block kb
+          const bool local = ta == &p.tma_a_local;
+          const uint16_t* src = local ? static_cast<const uint16_t*>(p.a_local)
+                                      : reinterpret_cast<const uint16_t*>(static_cast<const char*>(p.a_ws) + size_t(parity) * p.ws_parity_bytes);
+          const long long ld = local ? p.a_lda : p.K;
+          const int rows = min(kBlockM, tc.row_end - tc.row0);
+          for (int r = 0; r < rows; ++r)
+            for (int k = kb * kBlockK; k < min((kb + 1) * kBlockK, p.K); ++k) sum += src[size_t(a_row + r) * ld + k];
+        }
+      }  // k blocks
+      __syncwarp();
+      if (lane == 0) sums[t] = sum;
+    }
+  }
+  __syncthreads();
+  phase_end(p.ps, phase_base, 2);
+}
+
+// rows: rows per rank (a multiple of 8 is not required; blocks of 128), `alternate` as below (the smaller calls use half the rows)
+int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas, int calls, int alternate, int slices, int slabs) {
+  using namespace tdist;
+  using bf16 = __nv_bfloat16;
+  constexpr int BLOCK_N = 64;
+  if (world < 2 || K % 8 != 0 || slices < 1 || (slices & (slices - 1)) || slices > 32 || push_ctas < 1 || ctas <= push_ctas) {
+    fprintf(stderr, "fused ag: needs 2+ ranks (one rank runs the plain GEMM), K %% 8 == 0, a power-of-two slice count <= 32, push CTAs < CTAs\n");
+    return 2;
+  }
+  const size_t W = world;
+  const size_t parity_bytes = W * max_rows * size_t(K) * 2;
+  const int bps_max = (max_rows + kBlockM - 1) / kBlockM;
+  const size_t flag_words = W * bps_max * kAgSlots;
+  sim::Node node(world, 2 * parity_bytes + flag_words * 4, true);
+  auto rows_of = [=](int call) { return alternate && (call & 1) == (alternate & 1) ? max_rows / 2 : max_rows; };
+  std::vector<std::vector<bf16>> A(size_t(calls) * world);  // one input per (call, rank): never rewritten
+  for (int c = 0; c < calls; ++c)
+    for (int r = 0; r < world; ++r) A[size_t(c) * world + r] = random_bf16(size_t(rows_of(c)) * K, 4000 * c + 17 * r + 3, 1.f);
+  sim::run_ranks(world, [&](int rank) {
+    uint32_t state[2] = {0, 0};
+    for (int call = 0; call < calls; ++call) {
+      const int rows = rows_of(call);
+      GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.ctx = node.ctx(rank);
+      p.mode = GEMM_AG;
+      p.variant = VARIANT_NVLS;
+      p.is_bf16 = 1;
+      p.group_m = 8;
+      p.M = rows * world;
+      p.N = N;
+      p.K = K;
+      p.rows_per_rank = rows;
+      p.a_local = A[size_t(call) * world + rank].data();
+      p.a_lda = K;
+      p.a_ws = node.base(rank);
+      p.ws_parity_bytes = parity_bytes;
+      p.flags = reinterpret_cast<uint32_t*>(node.base(rank) + 2 * parity_bytes);
+      p.ps = PhaseState{state, state + 1};
+      p.num_comm_ctas = push_ctas;
+      // the host code's split of a block into K slabs (csrc/kernels/gemm.cu)
+      const int num_kb = (K + kBlockK - 1) / kBlockK;
+      int sl = slabs;
+      if (sl > kAgSlots / slices) sl = kAgSlots / slices;
+      if (sl > num_kb) sl = num_kb;
+      if (sl < 1) sl = 1;
+      p.ag_slices = slices;
+      p.ag_slab_kblocks = (num_kb + sl - 1) / sl;
+      p.ag_kslabs = (num_kb + p.ag_slab_kblocks - 1) / p.ag_slab_kblocks;
+      const int tiles_n = (N + BLOCK_N - 1) / BLOCK_N, tiles_m = blocks_per_shard(p) * world, tiles = tiles_m * tiles_n;
+      std::vector<unsigned long long> sums(tiles, ~0ull);
+      unsigned long long* sp = sums.data();
+      const GemmParams* pp = &p;
+      sim::launch(rank, ctas, 64, [=] { fused_ag_cta<BLOCK_N>(*pp, sp); });
+      for (int t = 0; t < tiles; ++t) {
+        const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+        const uint16_t* src = reinterpret_cast<const uint16_t*>(A[size_t(call) * world + tc.shard].data());
+        unsigned long long want = 0;
+        for (int r = tc.blk * kBlockM; r < std::min((tc.blk + 1) * kBlockM, rows); ++r)
+          for (int k = 0; k < K; ++k) want += src[size_t(r) * K + k];
+        if (sums[t] != want) mismatch("fused ag", rank, call, t, float(sums[t] % 100000), float(want % 100000));
+      }
+    }
+  });
+  printf("protocol_sim fused ag: %d ranks x %d calls, %d rows per rank%s, N %d, K %d, %d push + %d GEMM CTAs, %d row slices x %d K slabs per block: %s\n",
+         world, calls, max_rows, alternate ? " (alternating with half)" : "", N, K, push_ctas, ctas - push_ctas, slices, slabs,
+         g_errors ? "DATA MISMATCH" : "data ok");
+  return g_errors ? 1 : 0;
+}
+
 // mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; "rs2": the CTA-pair kernel's form, `ctas` must be even; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
 // AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
 // smaller) or 2 (even calls smaller). `fixed_rows`: one flag row per source rank of constant length (GemmParams::flag_row).

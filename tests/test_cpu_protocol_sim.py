@@ -70,8 +70,9 @@ def _stage(dst: Path) -> None:
         shutil.copy(ROOT / "csrc" / rel, dst / "csrc" / rel)
     shutil.copy(SIM / "shim" / "runtime" / "driver.h", dst / "csrc" / "runtime" / "driver.h")
     # the fused tcgen05 GEMM: parameter block, tile order and communication bodies (everything before the kernel template),
-    # plus the publisher loops of the kernel, i.e. the text between its [sim:...] markers, with a yield in their spin on the
-    # shared tile counter (csrc/sim/fused_gemm_scenarios.h wraps them)
+    # plus the publisher loops of the kernel and the arrival wait of its TMA producer warp in AG mode, i.e. the text between
+    # its [sim:...] markers, with a yield in the publishers' spin on the shared tile counter (csrc/sim/fused_gemm_scenarios.h
+    # wraps them)
     gemm = (ROOT / "csrc" / "kernels" / "gemm_sm100.cuh").read_text()
     cut = gemm.index("\ntemplate <int BLOCK_N, int STAGES>\n__global__")
     (dst / "csrc" / "kernels" / "gemm_sm100.cuh").write_text(gemm[:cut] + "\n}  // namespace tdist\n")
@@ -79,10 +80,10 @@ def _stage(dst: Path) -> None:
     pair = (ROOT / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").read_text()  # the CTA-pair kernel: tile order + publisher
     cut = pair.index("\ntemplate <int BLOCK_N, int STAGES>\n__global__")
     (dst / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").write_text(pair[:cut] + "\n}  // namespace tdist\n")
-    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair)):
+    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair), ("ag_wait", gemm)):
         a = text.index("\n", text.index(f"[sim:{name} begin]")) + 1
         snippet = text[a:text.index(f"// [sim:{name} end]")]
-        assert spin.search(snippet), name
+        assert spin.search(snippet) or name == "ag_wait", name  # (the AG wait polls flags, which yield by themselves)
         (dst / "csrc" / "kernels" / f"gemm_{name}.inc").write_text(spin.sub(r"\1 sim_yield(); }", snippet))
 
 
@@ -152,6 +153,11 @@ CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3,
           ("fused", "rs2", 2, 1024, 128, 2, 2, 1), ("fused", "rs2", 3, 1536, 128, 4, 3, 1), ("fused", "rs2", 4, 1536, 64, 2, 4, 1, 2),
           ("fused", "rs2", 4, 1536, 64, 4, 4, 1, 1, 1), ("fused", "rs2", 8, 2048, 64, 2, 2, 1), ("fused", "rs2", 3, 1152, 128, 2, 3, 0, 0, 1)]
 
+# the production AG + GEMM in its in-switch broadcast form (real ag_push_mc_body, real arrival wait of the TMA producer warp, real
+# tile order): "ag", ranks, rows per rank, N, K, push CTAs, CTAs, calls, alternate, row slices, K slabs
+CLEAN += [("fused", "ag", 3, 192, 128, 192, 2, 5, 3, 0, 2, 2), ("fused", "ag", 8, 128, 64, 128, 8, 11, 2, 0, 8, 1),
+          ("fused", "ag", 2, 300, 128, 64, 1, 2, 4, 1, 4, 3), ("fused", "ag", 4, 256, 192, 256, 3, 6, 4, 2, 2, 4),
+          ("fused", "ag", 4, 200, 64, 512, 5, 9, 3, 1, 1, 8)]
 # one decode step through the production decode-path kernels on one simulated GPU: batch, query heads, KV heads, cached tokens,
 # KV splits, page size (0 = dense cache), hidden, intermediate, vocabulary, fp16. The head groups 14 / 2 = 7 and 16 / 2 = 8
 # and 1 cover the 4 + 2 + 1, 8 and 1-head passes; sequence 1 is always shorter than the number of splits (empty splits)
@@ -184,6 +190,9 @@ def test_straggler_with_changing_sizes(sims):
     # the megakernel with one rank 5 ms late at every cross-rank flag: 3 steps back to back on double-buffered partials
     rc, out = _run(sims[0], ("mega", 3, 3, 1, 2, 3, 0, 1, 1, 2, 64, 2), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
+    # production AG + GEMM, calls alternating between 256 and 128 rows per rank, one rank 50 ms late at every flag
+    rc, out = _run(sims[0], ("fused", "ag", 4, 256, 64, 128, 2, 4, 4, 1, 2, 2), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "50"})
+    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     for op in ("ar2", "rsmc", "ag_llmc"):  # production collectives, 8 ranks, alternating sizes, one rank 5 ms late per flag
         rc, out = _run(sims[0], ("coll", op, 8, 64, 2, 3, 1), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
@@ -211,8 +220,8 @@ def test_fused_gemm_rs_fixed_flag_rows_survive_the_straggler(sims):
                                   ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
                                   ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2),
                                   ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1),
-                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2)],
-                         ids=lambda c: "-".join(map(str, c[:2])))
+                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2), ("fused", "ag", 2, 256, 64, 128, 2, 4, 2, 0, 2, 2)],
+                         ids=lambda c: "-".join(map(str, c[:3])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
     for attempt in range(4):  # whether the unordered accesses actually meet depends on the schedule of that run

@@ -168,6 +168,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
         uint32_t ph = 0;
         for (int t = pair; t < tiles; t += num_pairs) {
           const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
+          // [sim:ag_wait_pair begin] (csrc/sim runs the text between these markers against ag_push_mc_body on the CPU)
           const CUtensorMap* ta = &p.tma_a[0];
           int a_row = tc.row0 + int(cta_rank) * kBlockM;  // my 128 rows of the 256-row tile
           const int blk128 = tc.pblk * 2 + int(cta_rank);
@@ -197,6 +198,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
               __syncwarp();
               ptx::fence_proxy_async();
             }
+            // [sim:ag_wait_pair end]
             if (lane == 0) {
               ptx::mbar_wait(empty_bar + stage, ph ^ 1);
               const uint32_t leader_full = ptx::smem_u32(full_bar + stage) & kPeerBitMask;

@@ -151,13 +151,61 @@ void fused_ag_cta(const tdist::GemmParams& p, unsigned long long* sums) {
   phase_end(p.ps, phase_base, 2);
 }
 
+// the same for the CTA-pair kernel (gemm_sm100_2cta.cuh): both CTAs of a pair walk the 256-row pair tiles, each waits for and
+// reads its own 128-row half
+template <int BLOCK_N>
+void fused_ag_pair_cta(const tdist::GemmParams& p, unsigned long long* sums) {
+  using namespace tdist;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = blockIdx.x & 1u;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int bps128 = blocks_per_shard(p);
+  const int ptiles_m = ((p.rows_per_rank + 2 * kBlockM - 1) / (2 * kBlockM)) * p.ctx.world;
+  const int tiles = ptiles_m * tiles_n;
+  const int num_k = (p.K + kBlockK - 1) / kBlockK;
+  const int num_pairs = (gridDim.x - p.num_comm_ctas) / 2;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+  const int pair = gemm_cta >> 1;
+  const uint32_t phase_base = phase_begin(p.ps);
+  const uint32_t epoch = phase_base + 2;
+  const int parity = (epoch >> 1) & 1;
+  if (gemm_cta < 0) {
+    ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+  } else if (warp == 0) {
+    for (int t = pair; t < tiles; t += num_pairs) {
+      const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
+      unsigned long long sum = 0;
+#include "kernels/gemm_ag_wait_pair.inc"
+        (void)b_row;
+        if (lane == 0) {  // stand-in for the loads of k block kb: my half of the pair tile, up to the end of the shard
+          const bool local = ta == &p.tma_a_local;
+          const uint16_t* src = local ? static_cast<const uint16_t*>(p.a_local)
+                                      : reinterpret_cast<const uint16_t*>(static_cast<const char*>(p.a_ws) + size_t(parity) * p.ws_parity_bytes);
+          const long long ld = local ? p.a_lda : p.K;
+          const int rows = min(kBlockM, tc.row_end - (tc.row0 + int(cta_rank) * kBlockM));
+          for (int r = 0; r < rows; ++r)
+            for (int k = kb * kBlockK; k < min((kb + 1) * kBlockK, p.K); ++k) sum += src[size_t(a_row + r) * ld + k];
+        }
+      }  // k blocks
+      __syncwarp();
+      if (lane == 0) sums[size_t(t) * 2 + cta_rank] = sum;
+    }
+  }
+  __syncthreads();
+  phase_end(p.ps, phase_base, 2);
+}
+
 // rows: rows per rank (a multiple of 8 is not required; blocks of 128), `alternate` as below (the smaller calls use half the rows)
-int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas, int calls, int alternate, int slices, int slabs) {
+int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas, int calls, int alternate, int slices, int slabs, bool pair) {
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
   if (world < 2 || K % 8 != 0 || slices < 1 || (slices & (slices - 1)) || slices > 32 || push_ctas < 1 || ctas <= push_ctas) {
     fprintf(stderr, "fused ag: needs 2+ ranks (one rank runs the plain GEMM), K %% 8 == 0, a power-of-two slice count <= 32, push CTAs < CTAs\n");
+    return 2;
+  }
+  if (pair && (push_ctas % 2 != 0 || (ctas - push_ctas) % 2 != 0)) {
+    fprintf(stderr, "fused ag2: the CTA-pair form needs even numbers of push and GEMM CTAs\n");
     return 2;
   }
   const size_t W = world;
@@ -200,23 +248,38 @@ int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas,
       p.ag_slices = slices;
       p.ag_slab_kblocks = (num_kb + sl - 1) / sl;
       p.ag_kslabs = (num_kb + p.ag_slab_kblocks - 1) / p.ag_slab_kblocks;
-      const int tiles_n = (N + BLOCK_N - 1) / BLOCK_N, tiles_m = blocks_per_shard(p) * world, tiles = tiles_m * tiles_n;
-      std::vector<unsigned long long> sums(tiles, ~0ull);
+      const int tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
+      const int tiles_m = pair ? ((rows + 2 * kBlockM - 1) / (2 * kBlockM)) * world : blocks_per_shard(p) * world, tiles = tiles_m * tiles_n;
+      std::vector<unsigned long long> sums(size_t(tiles) * (pair ? 2 : 1), ~0ull);
       unsigned long long* sp = sums.data();
       const GemmParams* pp = &p;
-      sim::launch(rank, ctas, 64, [=] { fused_ag_cta<BLOCK_N>(*pp, sp); });
-      for (int t = 0; t < tiles; ++t) {
-        const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
-        const uint16_t* src = reinterpret_cast<const uint16_t*>(A[size_t(call) * world + tc.shard].data());
-        unsigned long long want = 0;
-        for (int r = tc.blk * kBlockM; r < std::min((tc.blk + 1) * kBlockM, rows); ++r)
-          for (int k = 0; k < K; ++k) want += src[size_t(r) * K + k];
-        if (sums[t] != want) mismatch("fused ag", rank, call, t, float(sums[t] % 100000), float(want % 100000));
-      }
+      if (pair)
+        sim::launch(rank, ctas, 64, [=] { fused_ag_pair_cta<BLOCK_N>(*pp, sp); });
+      else
+        sim::launch(rank, ctas, 64, [=] { fused_ag_cta<BLOCK_N>(*pp, sp); });
+      for (int t = 0; t < tiles; ++t)
+        for (int half = 0; half < (pair ? 2 : 1); ++half) {
+          int shard, first;
+          if (pair) {
+            const PairCoord tc = pair_coord(p, t, tiles_m, tiles_n);
+            shard = tc.shard;
+            first = tc.pblk * 2 * kBlockM + half * kBlockM;
+          } else {
+            const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+            shard = tc.shard;
+            first = tc.blk * kBlockM;
+          }
+          const uint16_t* src = reinterpret_cast<const uint16_t*>(A[size_t(call) * world + shard].data());
+          unsigned long long want = 0;
+          for (int r = first; r < std::min(first + kBlockM, rows); ++r)
+            for (int k = 0; k < K; ++k) want += src[size_t(r) * K + k];
+          const unsigned long long got = sums[pair ? size_t(t) * 2 + half : size_t(t)];
+          if (got != want) mismatch(pair ? "fused ag2" : "fused ag", rank, call, t, float(got % 100000), float(want % 100000));
+        }
     }
   });
-  printf("protocol_sim fused ag: %d ranks x %d calls, %d rows per rank%s, N %d, K %d, %d push + %d GEMM CTAs, %d row slices x %d K slabs per block: %s\n",
-         world, calls, max_rows, alternate ? " (alternating with half)" : "", N, K, push_ctas, ctas - push_ctas, slices, slabs,
+  printf("protocol_sim fused %s: %d ranks x %d calls, %d rows per rank%s, N %d, K %d, %d push + %d GEMM CTAs, %d row slices x %d K slabs per block: %s\n",
+         pair ? "ag2" : "ag", world, calls, max_rows, alternate ? " (alternating with half)" : "", N, K, push_ctas, ctas - push_ctas, slices, slabs,
          g_errors ? "DATA MISMATCH" : "data ok");
   return g_errors ? 1 : 0;
 }

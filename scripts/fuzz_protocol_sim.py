@@ -35,8 +35,10 @@ def random_case(rng):
         return ["mega", W, c([1, 2, 3, 5, 9]), c([1, 1, 2]), c([1, 2, 3, 8]), c([1, 2, 3]), graph, c([0, 1]), c([1, 2]),
                 c([1, 2, 4, 8] if graph == 2 else [1, 2, 4, 8, 9]), c([64, 128, 192]), c([1, 2, 3, 7, 16])], W
     if kind == "fused" and W > 1 and rng.random() < 0.3:
-        push = c([1, 2, 3, 8])
-        return ["fused", "ag", W, c([64, 128, 200, 256, 384]), c([64, 128, 192]), c([64, 128, 320, 512]), push, push + c([1, 2, 4]),
+        pair = rng.random() < 0.5  # the CTA-pair kernel: even CTA counts
+        push = c([2, 4, 8]) if pair else c([1, 2, 3, 8])
+        return ["fused", "ag2" if pair else "ag", W, c([64, 128, 200, 256, 384]), c([64, 128, 192]), c([64, 128, 320, 512]), push,
+                push + (c([2, 4]) if pair else c([1, 2, 4])),
                 c([1, 2, 4]), c([0, 0, 1, 2]), c([1, 2, 4, 8]), c([1, 2, 4, 8])], W
     if kind == "fused":
         mode = c(["rs", "rs2", "ar1", "ar2"])

@@ -80,10 +80,10 @@ def _stage(dst: Path) -> None:
     pair = (ROOT / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").read_text()  # the CTA-pair kernel: tile order + publisher
     cut = pair.index("\ntemplate <int BLOCK_N, int STAGES>\n__global__")
     (dst / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").write_text(pair[:cut] + "\n}  // namespace tdist\n")
-    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair), ("ag_wait", gemm)):
+    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair), ("ag_wait", gemm), ("ag_wait_pair", pair)):
         a = text.index("\n", text.index(f"[sim:{name} begin]")) + 1
         snippet = text[a:text.index(f"// [sim:{name} end]")]
-        assert spin.search(snippet) or name == "ag_wait", name  # (the AG wait polls flags, which yield by themselves)
+        assert spin.search(snippet) or name.startswith("ag_wait"), name  # (the AG wait polls flags, which yield by themselves)
         (dst / "csrc" / "kernels" / f"gemm_{name}.inc").write_text(spin.sub(r"\1 sim_yield(); }", snippet))
 
 
@@ -157,7 +157,11 @@ CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3,
 # tile order): "ag", ranks, rows per rank, N, K, push CTAs, CTAs, calls, alternate, row slices, K slabs
 CLEAN += [("fused", "ag", 3, 192, 128, 192, 2, 5, 3, 0, 2, 2), ("fused", "ag", 8, 128, 64, 128, 8, 11, 2, 0, 8, 1),
           ("fused", "ag", 2, 300, 128, 64, 1, 2, 4, 1, 4, 3), ("fused", "ag", 4, 256, 192, 256, 3, 6, 4, 2, 2, 4),
-          ("fused", "ag", 4, 200, 64, 512, 5, 9, 3, 1, 1, 8)]
+          ("fused", "ag", 4, 200, 64, 512, 5, 9, 3, 1, 1, 8),
+          # "ag2": the CTA-pair kernel's producer wait and tile order (each CTA of a pair waits for its 128-row half)
+          ("fused", "ag2", 3, 384, 128, 192, 2, 6, 3, 0, 2, 2), ("fused", "ag2", 8, 256, 64, 128, 8, 12, 2, 0, 8, 1),
+          ("fused", "ag2", 2, 300, 128, 64, 2, 4, 4, 1, 4, 3), ("fused", "ag2", 4, 512, 192, 256, 4, 8, 4, 2, 2, 4),
+          ("fused", "ag2", 3, 200, 64, 128, 2, 4, 3, 1, 1, 1)]
 # one decode step through the production decode-path kernels on one simulated GPU: batch, query heads, KV heads, cached tokens,
 # KV splits, page size (0 = dense cache), hidden, intermediate, vocabulary, fp16. The head groups 14 / 2 = 7 and 16 / 2 = 8
 # and 1 cover the 4 + 2 + 1, 8 and 1-head passes; sequence 1 is always shorter than the number of splits (empty splits)
@@ -191,8 +195,9 @@ def test_straggler_with_changing_sizes(sims):
     rc, out = _run(sims[0], ("mega", 3, 3, 1, 2, 3, 0, 1, 1, 2, 64, 2), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
     assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     # production AG + GEMM, calls alternating between 256 and 128 rows per rank, one rank 50 ms late at every flag
-    rc, out = _run(sims[0], ("fused", "ag", 4, 256, 64, 128, 2, 4, 4, 1, 2, 2), {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "50"})
-    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
+    for case in (("fused", "ag", 4, 256, 64, 128, 2, 4, 4, 1, 2, 2), ("fused", "ag2", 4, 512, 64, 128, 2, 6, 4, 1, 2, 2)):
+        rc, out = _run(sims[0], case, {"TDIST_SIM_SLOW_RANK": "0", "TDIST_SIM_SLOW_MS": "50"})
+        assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]
     for op in ("ar2", "rsmc", "ag_llmc"):  # production collectives, 8 ranks, alternating sizes, one rank 5 ms late per flag
         rc, out = _run(sims[0], ("coll", op, 8, 64, 2, 3, 1), {"TDIST_SIM_SLOW_RANK": "1", "TDIST_SIM_SLOW_MS": "5"})
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-3000:]

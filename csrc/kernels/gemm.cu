@@ -441,6 +441,9 @@ int tdist_gemm_fused(const tdist_gemm_args* a, const tdist_fused_args* f, void* 
         }
       }
     }
+    // opt-in, as for RS / AR below: one flag row of constant length per source rank (the size checks above still apply: the
+    // call's own rows fit in such a row whenever they fit in the area)
+    if (env_int("TDIST_FIXED_FLAG_LAYOUT", 0) && f->flags_words >= size_t(W)) p.flag_row = int(f->flags_words / W);
     if (make_tmap(&p.tma_a_local, a->a, p.rows_per_rank, a->K, a->lda, kBlockM) != 0) return -1;
     if (make_tmap(&p.tma_a[0], f->ws, a->M, a->K, a->K, kBlockM) != 0) return -1;
     if (make_tmap(&p.tma_a[1], static_cast<char*>(f->ws) + p.ws_parity_bytes, a->M, a->K, a->K, kBlockM) != 0) return -1;

@@ -86,7 +86,7 @@ struct GemmParams {
   long long a_lda;         // AG: row stride of a_local in elements
   size_t ws_parity_bytes;  // distance between the two parity halves of the workspace: a constant of the CONTEXT, so that
                            // calls of different sizes on one context never overlap the other parity's live data
-  int flag_row;            // RS (NVLS) / AR: flag words per SOURCE RANK. 0 = the row follows the call (bps * tiles_n, or tiles):
+  int flag_row;            // AG / RS (NVLS) / AR: flag words per SOURCE RANK. 0 = the row follows the call (bps * slots, bps * tiles_n, or tiles):
                            // the measured default. > 0 (TDIST_FIXED_FLAG_LAYOUT=1: flags_words / W, a constant of the
                            // context): every flag word has ONE writer rank over all calls, so calls of different M on one
                            // context cannot meet in a word under two meanings (profiles/protocol_sim.md)
@@ -253,8 +253,8 @@ __device__ __forceinline__ void ag_push_body(const GemmParams& p, uint8_t* smem,
       ptx::fence_proxy_async();
       ptx::fence_acq_rel_sys();
     }
-    // flags layout (AG): [W src][blocks_per_shard][kAgParts]; empty parts are flagged too
-    notify(p.ctx, p.flags + (rank * bps + j) * kAgParts + q, peer, epoch);
+    // flags layout (AG): [W src][blocks_per_shard (or the fixed row, GemmParams::flag_row)][kAgParts]; empty parts are flagged too
+    notify(p.ctx, p.flags + size_t(rank) * (p.flag_row > 0 ? p.flag_row : bps * kAgParts) + j * kAgParts + q, peer, epoch);
   }
 }
 
@@ -307,7 +307,7 @@ __device__ __forceinline__ void ag_push_mc_body(const GemmParams& p, uint32_t ep
     // flags layout (AG, NVLS): [W src][blocks_per_shard][kAgSlots], slot = slab * slices + slice
     if (threadIdx.x == 0) {
       ptx::fence_acq_rel_sys();
-      ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + (size_t(rank) * bps + j) * kAgSlots + sb * slices + sl), epoch);
+      ptx::multimem_st_b32(mc_ptr(p.ctx, p.flags + size_t(rank) * (p.flag_row > 0 ? p.flag_row : bps * kAgSlots) + j * kAgSlots + sb * slices + sl), epoch);
     }
   }
 }
@@ -619,11 +619,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
               ta = &p.tma_a[parity];
               if (p.variant != VARIANT_NVLS) {
                 // wait until every part of block (src, blk) has landed in my workspace
-                if (lane < kAgParts) wait_ge_sys_poll_relaxed(p.flags + (tc.shard * bps + tc.blk) * kAgParts + lane, epoch);
+                if (lane < kAgParts)
+                  wait_ge_sys_poll_relaxed(p.flags + size_t(tc.shard) * (p.flag_row > 0 ? p.flag_row : bps * kAgParts) + tc.blk * kAgParts + lane, epoch);
                 __syncwarp();
                 ptx::fence_proxy_async();
               } else {
-                slab_flags = p.flags + (size_t(tc.shard) * bps + tc.blk) * kAgSlots;
+                slab_flags = p.flags + size_t(tc.shard) * (p.flag_row > 0 ? p.flag_row : bps * kAgSlots) + tc.blk * kAgSlots;
               }
             }
           }

@@ -181,11 +181,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_2cta_kernel(const 
               ta = &p.tma_a[parity];
               if (blk128 < bps128) {
                 if (p.variant != VARIANT_NVLS) {
-                  if (lane < kAgParts) wait_ge_sys_poll_relaxed(p.flags + (tc.shard * bps128 + blk128) * kAgParts + lane, epoch);
+                  if (lane < kAgParts)
+                    wait_ge_sys_poll_relaxed(p.flags + size_t(tc.shard) * (p.flag_row > 0 ? p.flag_row : bps128 * kAgParts) + blk128 * kAgParts + lane, epoch);
                   __syncwarp();
                   ptx::fence_proxy_async();
                 } else {
-                  slab_flags = p.flags + (size_t(tc.shard) * bps128 + blk128) * kAgSlots;
+                  slab_flags = p.flags + size_t(tc.shard) * (p.flag_row > 0 ? p.flag_row : bps128 * kAgSlots) + blk128 * kAgSlots;
                 }
               }
             }

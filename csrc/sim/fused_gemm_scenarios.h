@@ -126,7 +126,12 @@ void fused_ag_cta(const tdist::GemmParams& p, unsigned long long* sums) {
   const uint32_t epoch = phase_base + 2;
   const int parity = (epoch >> 1) & 1;
   if (gemm_cta < 0) {
-    ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+    if (p.variant == VARIANT_NVLS) {
+      ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+    } else {
+      SIM_DYN_SHARED(uint8_t, smem);
+      ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+    }
   } else if (warp == 0) {
     const int bps = blocks_per_shard(p);
     for (int t = gemm_cta; t < tiles; t += num_gemm) {
@@ -170,7 +175,12 @@ void fused_ag_pair_cta(const tdist::GemmParams& p, unsigned long long* sums) {
   const uint32_t epoch = phase_base + 2;
   const int parity = (epoch >> 1) & 1;
   if (gemm_cta < 0) {
-    ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+    if (p.variant == VARIANT_NVLS) {
+      ag_push_mc_body(p, epoch, blockIdx.x, p.num_comm_ctas);
+    } else {
+      SIM_DYN_SHARED(uint8_t, smem);
+      ag_push_body(p, smem, epoch, blockIdx.x, p.num_comm_ctas);
+    }
   } else if (warp == 0) {
     for (int t = pair; t < tiles; t += num_pairs) {
       const PairCoord tc = pair_coord(p, t, ptiles_m, tiles_n);
@@ -195,11 +205,14 @@ void fused_ag_pair_cta(const tdist::GemmParams& p, unsigned long long* sums) {
   phase_end(p.ps, phase_base, 2);
 }
 
-// rows: rows per rank (a multiple of 8 is not required; blocks of 128), `alternate` as below (the smaller calls use half the rows)
-int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas, int calls, int alternate, int slices, int slabs, bool pair) {
+// rows: rows per rank (a multiple of 8 is not required; blocks of 128), `alternate` as below (the smaller calls use half the rows);
+// slices == 0 selects the point-to-point form (ag_push_body: bulk-copy ring to every peer, 4 flagged 32-row parts per block)
+int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas, int calls, int alternate, int slices, int slabs, int fixed_rows, bool pair) {
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
+  const bool ring = slices == 0;  // the point-to-point form (default with one peer): bulk-copy ring, 4 flagged parts per block
+  if (ring) slices = 1;
   if (world < 2 || K % 8 != 0 || slices < 1 || (slices & (slices - 1)) || slices > 32 || push_ctas < 1 || ctas <= push_ctas) {
     fprintf(stderr, "fused ag: needs 2+ ranks (one rank runs the plain GEMM), K %% 8 == 0, a power-of-two slice count <= 32, push CTAs < CTAs\n");
     return 2;
@@ -225,7 +238,7 @@ int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas,
       memset(&p, 0, sizeof(p));
       p.ctx = node.ctx(rank);
       p.mode = GEMM_AG;
-      p.variant = VARIANT_NVLS;
+      p.variant = ring ? VARIANT_LEGACY : VARIANT_NVLS;
       p.is_bf16 = 1;
       p.group_m = 8;
       p.M = rows * world;
@@ -239,6 +252,7 @@ int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas,
       p.flags = reinterpret_cast<uint32_t*>(node.base(rank) + 2 * parity_bytes);
       p.ps = PhaseState{state, state + 1};
       p.num_comm_ctas = push_ctas;
+      p.flag_row = fixed_rows ? int(flag_words / W) : 0;  // TDIST_FIXED_FLAG_LAYOUT=1 of csrc/kernels/gemm.cu
       // the host code's split of a block into K slabs (csrc/kernels/gemm.cu)
       const int num_kb = (K + kBlockK - 1) / kBlockK;
       int sl = slabs;
@@ -278,9 +292,9 @@ int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas,
         }
     }
   });
-  printf("protocol_sim fused %s: %d ranks x %d calls, %d rows per rank%s, N %d, K %d, %d push + %d GEMM CTAs, %d row slices x %d K slabs per block: %s\n",
-         pair ? "ag2" : "ag", world, calls, max_rows, alternate ? " (alternating with half)" : "", N, K, push_ctas, ctas - push_ctas, slices, slabs,
-         g_errors ? "DATA MISMATCH" : "data ok");
+  printf("protocol_sim fused %s: %d ranks x %d calls, %d rows per rank%s, N %d, K %d, %d push + %d GEMM CTAs, %s (%d row slices x %d K slabs per block), flag rows %s: %s\n",
+         pair ? "ag2" : "ag", world, calls, max_rows, alternate ? " (alternating with half)" : "", N, K, push_ctas, ctas - push_ctas,
+         ring ? "point-to-point ring" : "in-switch broadcast", slices, slabs, fixed_rows ? "fixed" : "per call", g_errors ? "DATA MISMATCH" : "data ok");
   return g_errors ? 1 : 0;
 }
 

@@ -24,7 +24,8 @@
 //                                                                    (one simulated GPU: one decode step, every kernel against a host oracle)
 //   protocol_sim mega <ranks> <CTAs> <layers> <batch> <steps> <graph: 0 fused, 1 op by op, 2 fused + one-task attention> <in-switch all-reduce 0/1>
 //                     <KV heads per rank> <query heads per KV head> <MLP columns per rank> <KV splits>     (the decode megakernel + its native builder)
-//   protocol_sim fused ag|ag2 <ranks> <rows per rank> <N> <K> <push CTAs> <CTAs> <calls> [alternate] [row slices] [K slabs]   (production AG + GEMM, in-switch push; ag2: the CTA-pair kernel)
+//   protocol_sim fused ag|ag2 <ranks> <rows per rank> <N> <K> <push CTAs> <CTAs> <calls> [alternate] [row slices, 0 = point-to-point ring] [K slabs] [fixed flag rows 0/1]
+//                                                                    (production AG + GEMM; ag2: the CTA-pair kernel)
 //   protocol_sim gemm_rs <ranks> <M> <N> <Kl> <ctas> <calls> [alternate: 1 = odd calls use M / div, 2 = even calls] [div = 2]
 #include "sim_runtime.h"
 
@@ -352,7 +353,7 @@ int main(int argc, char** argv) {
   if (what == "a2a") return run_a2a(arg(2, 3), arg(3, 24), arg(4, 3), arg(5, 2), arg(6, 2), arg(7, 4));
   if (what == "ep") return run_ep(arg(2, 3), arg(3, 12), arg(4, 256), arg(5, 6), arg(6, 2), arg(7, 3), arg(8, 0));
   if (what == "fused" && argc > 2 && (std::string(argv[2]) == "ag" || std::string(argv[2]) == "ag2"))
-    return run_fused_ag(arg(3, 3), arg(4, 192), arg(5, 128), arg(6, 192), arg(7, 2), arg(8, 6), arg(9, 3), arg(10, 0), arg(11, 2), arg(12, 2),
+    return run_fused_ag(arg(3, 3), arg(4, 192), arg(5, 128), arg(6, 192), arg(7, 2), arg(8, 6), arg(9, 3), arg(10, 0), arg(11, 2), arg(12, 2), arg(13, 0),
                         std::string(argv[2]) == "ag2");
   if (what == "fused") return run_fused(argc > 2 ? argv[2] : "rs", arg(3, 3), arg(4, 3 * 256), arg(5, 128), arg(6, 3), arg(7, 3), arg(8, 1), arg(9, 0), arg(10, 0));
   if (what == "decode") return run_decode(arg(2, 3), arg(3, 14), arg(4, 2), arg(5, 70), arg(6, 5), arg(7, 0), arg(8, 128), arg(9, 64), arg(10, 300), arg(11, 0));

@@ -5,6 +5,7 @@
 //             ld_acquire_sys / ld_acquire_gpu               atomic, acquire         the negative control)
 //             ld_relaxed_sys / ld_volatile                  atomic, relaxed
 //   packets:  st_relaxed_sys_v4 / ld_volatile_v4            two relaxed 8-byte atomics {data, flag}: the LL protocol's unit
+//   copies:   bulk and tiled TMA copies are performed at issue (mbarrier = count of completed phases)
 //   fences:   compiler barriers — ThreadSanitizer does not model stand-alone fences; the order it checks is carried by the
 //             release store that follows a fence and the acquire load that precedes the data loads, as on the device
 //   NVLS:     multimem_st_* writes every rank's copy, multimem_ld_reduce_* reads every rank's copy and adds in fp32
@@ -84,20 +85,19 @@ inline void fence_acq_rel_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void fence_acq_rel_gpu() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 inline void fence_sc_sys() { __atomic_signal_fence(__ATOMIC_SEQ_CST); }
 
-// ---- 1-D bulk copies (the TMA ring of the point-to-point AG push): not modelled; the stubs only let their callers compile.
-#define TDIST_SIM_UNMODELLED(name)                  \
-  template <typename... A>                          \
-  inline void name(A&&...) {                        \
-    fprintf(stderr, "sim: " #name " is not modelled\n"); \
-    abort();                                        \
-  }
-TDIST_SIM_UNMODELLED(bulk_g2s)
-TDIST_SIM_UNMODELLED(bulk_s2g)
-TDIST_SIM_UNMODELLED(bulk_commit)
+// ---- 1-D bulk copies (the ring of the point-to-point AG push: global -> shared -> peer global, driven by one thread):
+// performed at issue, like the tiled loads below; the store to the peer is a plain write, which is what the sanitizer checks
+// against the consumer's reads
+inline void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  memcpy(smem_dst, gsrc, bytes);
+  ++*bar;
+}
+inline void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) { memcpy(gdst, smem_src, bytes); }
+inline void bulk_commit() {}
 template <int N>
-inline void bulk_wait() { abort(); }
+inline void bulk_wait() {}
 template <int N>
-inline void bulk_wait_read() { abort(); }
+inline void bulk_wait_read() {}
 
 // ---- mbarrier + tiled TMA loads, as far as the decode megakernel uses them: one arrival per phase, the transaction bytes
 // of the phase delivered by ONE tensor load. The load is performed at issue (the copy engine of the simulator is infinitely

@@ -256,3 +256,147 @@ def test_no_undefined_names_in_the_python_sources():
 
         walk(top)
     assert len(files) > 150 and not problems, problems
+
+
+def test_module_attribute_references_resolve():
+    """`from x import name` and `alias.name` on the package's own modules, anywhere in the sources (also in branches that only
+    run on a GPU): the module really has that attribute. Catches a function renamed or removed under a caller that no CPU
+    test reaches."""
+    import ast
+    import importlib
+    import types
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    files = (list((root / "triton_dist").rglob("*.py")) + [root / "bench.py", root / "__graft_entry__.py"] +
+             list((root / "tutorials").glob("*.py")) + list((root / "tests").glob("*.py")))
+    problems, resolved = [], 0
+
+    def has(mod, name):
+        if hasattr(mod, name):
+            return True
+        try:
+            importlib.import_module(mod.__name__ + "." + name)
+            return True
+        except Exception:
+            return False
+
+    for f in files:
+        tree = ast.parse(f.read_text())
+        rel = f.relative_to(root)
+        package = ".".join(rel.parts[:-1]) if rel.parts[0] == "triton_dist" else ""
+        alias = {}
+        for node in ast.walk(tree):
+            if isinstance(node, ast.ImportFrom):
+                if node.level:
+                    if not package:
+                        continue
+                    base = package.split(".")[:len(package.split(".")) - node.level + 1]
+                    modname = ".".join(base + ([node.module] if node.module else []))
+                elif node.module and node.module.startswith("triton_dist"):
+                    modname = node.module
+                else:
+                    continue
+                try:
+                    mod = importlib.import_module(modname)
+                except Exception as e:  # noqa: BLE001
+                    problems.append(f"{rel}:{node.lineno}: import {modname}: {e}")
+                    continue
+                for a in node.names:
+                    if a.name == "*":
+                        continue
+                    if not has(mod, a.name):
+                        problems.append(f"{rel}:{node.lineno}: {modname} has no attribute {a.name}")
+                        continue
+                    resolved += 1
+                    obj = getattr(mod, a.name, None)
+                    if obj is None:
+                        obj = importlib.import_module(modname + "." + a.name)
+                    if isinstance(obj, types.ModuleType):
+                        alias[a.asname or a.name] = obj
+            elif isinstance(node, ast.Import):
+                for a in node.names:
+                    if a.name.startswith("triton_dist") and a.asname:
+                        alias[a.asname] = importlib.import_module(a.name)
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Attribute) and isinstance(node.value, ast.Name) and node.value.id in alias:
+                resolved += 1
+                if not has(alias[node.value.id], node.attr):
+                    problems.append(f"{rel}:{node.lineno}: {node.value.id}.{node.attr}: {alias[node.value.id].__name__} has no such attribute")
+    assert resolved > 1000 and not problems, (resolved, problems)
+
+
+def test_calls_of_package_functions_bind_to_their_signatures():
+    """Every call of a function or class of this package through an imported name (`f(...)` after `from x import f`,
+    `mod.f(...)` after `from x import mod`), anywhere in the sources, binds to the callee's signature: number of positional
+    arguments and keyword names. Calls with * / ** arguments are skipped."""
+    import ast
+    import importlib
+    import inspect
+    import types
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    files = (list((root / "triton_dist").rglob("*.py")) + [root / "bench.py", root / "__graft_entry__.py"] +
+             list((root / "tutorials").glob("*.py")) + list((root / "tests").glob("*.py")))
+    problems, checked = [], 0
+    for f in files:
+        tree = ast.parse(f.read_text())
+        rel = f.relative_to(root)
+        package = ".".join(rel.parts[:-1]) if rel.parts[0] == "triton_dist" else ""
+        names, rebound = {}, set()
+        for node in ast.walk(tree):
+            if isinstance(node, ast.ImportFrom):
+                if node.level:
+                    if not package:
+                        continue
+                    parts = package.split(".")
+                    modname = ".".join(parts[:len(parts) - node.level + 1] + ([node.module] if node.module else []))
+                elif node.module and node.module.startswith("triton_dist"):
+                    modname = node.module
+                else:
+                    continue
+                try:
+                    mod = importlib.import_module(modname)
+                except Exception:  # noqa: BLE001  (reported by test_module_attribute_references_resolve)
+                    continue
+                for a in node.names:
+                    obj = getattr(mod, a.name, None)
+                    if obj is None and a.name != "*":
+                        try:
+                            obj = importlib.import_module(modname + "." + a.name)
+                        except Exception:  # noqa: BLE001
+                            continue
+                    names[a.asname or a.name] = obj
+            elif isinstance(node, (ast.FunctionDef, ast.ClassDef)):
+                rebound.add(node.name)  # a local definition of the same name shadows the import
+            elif isinstance(node, ast.Name) and isinstance(node.ctx, ast.Store):
+                rebound.add(node.id)
+            elif isinstance(node, ast.arg):
+                rebound.add(node.arg)
+        for node in ast.walk(tree):
+            if not isinstance(node, ast.Call):
+                continue
+            fn = node.func
+            target = None
+            if isinstance(fn, ast.Name) and fn.id in names and fn.id not in rebound:
+                target = names[fn.id]
+            elif (isinstance(fn, ast.Attribute) and isinstance(fn.value, ast.Name) and fn.value.id in names and fn.value.id not in rebound
+                  and isinstance(names[fn.value.id], types.ModuleType)):
+                target = getattr(names[fn.value.id], fn.attr, None)
+            if target is None or not (inspect.isfunction(target) or inspect.isclass(target)):
+                continue
+            if not getattr(target, "__module__", "").startswith("triton_dist"):
+                continue
+            if any(isinstance(a, ast.Starred) for a in node.args) or any(k.arg is None for k in node.keywords):
+                continue
+            try:
+                sig = inspect.signature(target)
+            except (TypeError, ValueError):
+                continue
+            try:
+                sig.bind(*[None] * len(node.args), **{k.arg: None for k in node.keywords})
+                checked += 1
+            except TypeError as e:
+                problems.append(f"{rel}:{node.lineno}: {getattr(target, '__qualname__', target)}{sig}: {e}")
+    assert checked > 600 and not problems, (checked, problems)

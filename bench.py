@@ -154,8 +154,9 @@ class ClockSampler:
         return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_clock, "reasons": sorted(self.reasons), "samples": len(s)}
 
 
-def decode_section(rank: int, world: int, steps: int):
-    """Qwen3-32B decode latency at TP=world: bs=1, ctx=512, megakernel (one launch per token)."""
+def decode_section(rank: int, world: int, steps: int, out: dict):
+    """Qwen3-32B decode latency at TP=world: bs=1, ctx=512, megakernel (one launch per token). Results are written into
+    `out` as they are measured, so that a time limit on the section keeps what was finished."""
     import torch
     import torch.distributed as dist
 
@@ -179,10 +180,10 @@ def decode_section(rank: int, world: int, steps: int):
     pk = measured_peaks()
     floor = wbytes / (pk["hbm_gbs"] * 1e6)
     info = builder.info()
-    out = {"model": "Qwen3-32B (random init)", "tp": world, "bsz": 1, "ctx": 512, "ms_per_token": round(ms, 4),
-           "weight_bytes_per_token_per_rank": wbytes, "hbm_floor_ms_of_" + pk["source"]: round(floor, 4),
-           "fraction_of_hbm_floor": round(floor / ms, 3), "launches_per_token": 1, "graph": info,
-           "reference_published_ms_8xH800": 7.41 if world == 8 else None}
+    out.update({"model": "Qwen3-32B (random init)", "tp": world, "bsz": 1, "ctx": 512, "ms_per_token": round(ms, 4),
+                "weight_bytes_per_token_per_rank": wbytes, "hbm_floor_ms_of_" + pk["source"]: round(floor, 4),
+                "fraction_of_hbm_floor": round(floor / ms, 3), "launches_per_token": 1, "graph": info,
+                "reference_published_ms_8xH800": 7.41 if world == 8 else None})
     try:  # per-op-type timeline of one token (in-kernel task stamps), outside the timed region
         builder.enable_profiling(True)
         step()
@@ -195,7 +196,8 @@ def decode_section(rank: int, world: int, steps: int):
     # same-box comparators: the other three columns of the reference's table (docs/mega_triton_kernel.md:29-33), through
     # Engine's CUDA-graph decode step on the SAME weights: torch (cuBLAS + NCCL), triton_dist_AR, triton_dist_gemm_ar
     if os.environ.get("TDIST_BENCH_ENGINE", "1") != "0":
-        out["engine_graph_ms_per_token"] = engine_comparators(dense, cfg, steps)
+        out["engine_graph_ms_per_token"] = {}
+        engine_comparators(dense, cfg, steps, out["engine_graph_ms_per_token"])
         ref_ms = out["engine_graph_ms_per_token"].get("torch")
         if isinstance(ref_ms, float):
             out["megakernel_vs_torch_graph"] = round(ref_ms / ms, 3)
@@ -204,13 +206,12 @@ def decode_section(rank: int, world: int, steps: int):
     return out
 
 
-def engine_comparators(dense, cfg, steps: int) -> dict:
+def engine_comparators(dense, cfg, steps: int, res: dict) -> dict:
     import torch
 
     from triton_dist.models import Engine
     from triton_dist.utils import perf_func_max_over_ranks
 
-    res = {}
     ids = torch.randint(0, 32000, (1, 512), device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
     # torch + graph and the fused all-reduce backend were measured through this function at 1 and 8 GPUs. The fused
     # GEMM+AllReduce backend is opt-in here (TDIST_BENCH_GEMM_AR=1): its layer construction was corrected after the last
@@ -480,21 +481,29 @@ def main() -> None:
         # The headline number must survive the secondary section, whatever happens in it: an exception is recorded, and a
         # section that does not come back within the limit (every rank runs the same timer) ends the process after rank 0
         # has printed the line without it.
-        limit_s = float(os.environ.get("TDIST_BENCH_DECODE_TIMEOUT_S", "1200"))
+        # (600 s: the round-1 driver gave every N of its scaling run 870 s in total, and the headline part needs about a minute)
+        limit_s = float(os.environ.get("TDIST_BENCH_DECODE_TIMEOUT_S", "600"))
+
+        partial: dict = {}
 
         def give_up():
             if rank == 0:
-                out["decode"] = {"error": f"decode section did not finish within {limit_s:.0f} s"}
-                print(json.dumps(out), flush=True)
+                try:
+                    out["decode"] = dict(partial, error=f"decode section did not finish within {limit_s:.0f} s; what was measured until then is kept")
+                    line = json.dumps(out)
+                except Exception:  # noqa: BLE001 - (the section was writing into `partial` at this very moment)
+                    out["decode"] = {"error": f"decode section did not finish within {limit_s:.0f} s"}
+                    line = json.dumps(out)
+                print(line, flush=True)
             os._exit(0)
 
         timer = threading.Timer(limit_s, give_up)
         timer.daemon = True
         timer.start()
         try:
-            out["decode"] = decode_section(rank, world, max(args.steps, 10))
+            out["decode"] = decode_section(rank, world, max(args.steps, 10), partial)
         except Exception as e:
-            out["decode"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            out["decode"] = dict(partial, error=f"{type(e).__name__}: {e}"[:300])
         timer.cancel()
     if rank == 0:
         print(json.dumps(out), flush=True)

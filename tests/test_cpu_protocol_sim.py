@@ -23,6 +23,8 @@ import shutil
 import subprocess
 from pathlib import Path
 
+from concurrent.futures import ThreadPoolExecutor
+
 import pytest
 
 ROOT = Path(__file__).resolve().parent.parent
@@ -88,8 +90,8 @@ def _stage(dst: Path) -> None:
 
 
 def _build(stage_dir: Path, out: Path, *defines: str) -> None:
-    # (the device wait bound of symm.cuh is compiled in: 15 s here instead of 60)
-    cmd = ["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "--param=tsan-instrument-func-entry-exit=0", "-DTDIST_SPIN_TIMEOUT_S=15", *defines,
+    # (the device wait bound of symm.cuh is compiled in: 45 s here instead of 60; several cases share the cores)
+    cmd = ["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "--param=tsan-instrument-func-entry-exit=0", "-DTDIST_SPIN_TIMEOUT_S=45", *defines,
            f"-I{stage_dir / 'csrc'}", f"-I{SIM / 'stub'}", f"-I{SIM}", "-x", "c++", str(SIM / "protocol_sim.cc"), "-o", str(out),
            "-pthread"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
@@ -106,16 +108,62 @@ def sims(tmp_path_factory):
                            capture_output=True, text=True)
     if probe.returncode != 0 or subprocess.run([str(d / "probe")], capture_output=True).returncode != 0:
         pytest.skip("ThreadSanitizer runtime not available (or it cannot run on this kernel's address-space layout)")
-    _build(d / "stage", d / "sim")
-    _build(d / "stage", d / "sim_broken", "-DTDIST_SIM_BREAK_RELEASE")
-    return d / "sim", d / "sim_broken"
+    builds = [_POOL.submit(_build, d / "stage", d / "sim"), _POOL.submit(_build, d / "stage", d / "sim_broken", "-DTDIST_SIM_BREAK_RELEASE")]
+    for b in builds:
+        b.result()
+    good, broken = d / "sim", d / "sim_broken"
+    for case in CLEAN:  # run ahead, in the order the tests will ask for them
+        _submit(good, case)
+    for case, env in AHEAD:
+        _submit(good, case, env)
+    for case in NEGATIVE:
+        _submit(broken, case)
+    for name, (rel, old, new, expect, case, env) in MUTANTS.items():  # mutants: stage, build and run in the pool as well
+        _jobs[("mutant", name)] = _POOL.submit(_mutant, d / f"mut_{name}", rel, old, new, case, env)
+    return good, broken
 
 
-def _run(exe, args, env_extra=None):
+def _mutant(dst, rel, old, new, case, env):
+    _stage(dst / "stage")
+    f = dst / "stage" / "csrc" / rel
+    src = f.read_text()
+    assert old in src, f"the mutated expression is no longer in {rel}: update MUTANTS"
+    f.write_text(src.replace(old, new))
+    _build(dst / "stage", dst / "sim_mut")
+    return _run_now(dst / "sim_mut", case, env)
+
+
+def _run_now(exe, args, env_extra=None):
     env = dict(os.environ)
     env.update(env_extra or {})
     r = subprocess.run([str(exe)] + [str(a) for a in args], capture_output=True, text=True, timeout=900, env=env)
     return r.returncode, r.stdout + r.stderr
+
+
+# The cases are independent processes: a small pool runs them ahead of the tests that look at them (the `sims` fixture submits
+# everything once both binaries exist), which cuts the wall time of this file to a third. Not more workers than half the
+# cores: a case is itself ranks x CTAs spinning threads, and its waits are bounded in wall-clock time.
+_CORES = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 2)
+_POOL = ThreadPoolExecutor(max_workers=max(1, min(4, _CORES // 2)))
+_jobs = {}
+
+
+def _key(exe, args, env_extra):
+    return str(exe), tuple(str(a) for a in args), tuple(sorted((env_extra or {}).items()))
+
+
+def _submit(exe, args, env_extra=None):
+    k = _key(exe, args, env_extra)
+    if k not in _jobs:
+        _jobs[k] = _POOL.submit(_run_now, exe, args, env_extra)
+    return _jobs[k]
+
+
+def _run(exe, args, env_extra=None, fresh=False):
+    """(rc, output) of one simulator run; the result of a run that was submitted ahead is reused unless `fresh`."""
+    if fresh:
+        return _run_now(exe, args, env_extra)
+    return _submit(exe, args, env_extra).result()
 
 
 CLEAN = [
@@ -179,6 +227,17 @@ CLEAN += [("mega", 2, 4, 2, 2, 3, 0, 1, 1, 2, 128, 3), ("mega", 3, 5, 2, 3, 3, 1
           ("mega", 3, 4, 2, 2, 3, 0, 1, 1, 2, 128, 16), ("mega", 1, 2, 1, 2, 1, 0, 0, 1, 12, 64, 3)]
 
 
+# straggler runs of the tests below (same arguments and environment), submitted ahead with the rest
+_S = lambda rank, ms: {"TDIST_SIM_SLOW_RANK": str(rank), "TDIST_SIM_SLOW_MS": str(ms)}  # noqa: E731
+AHEAD = [(("gemm_rs", 4, 768, 64, 16, 1, 2, 1, 3), _S(0, 30)), (("ag_gemm", 4, 192, 40, 16, 1, 3, 3, 1, 3), _S(1, 10)),
+         (("mega", 3, 3, 1, 2, 3, 0, 1, 1, 2, 64, 2), _S(1, 5)), (("fused", "ag", 4, 256, 64, 128, 2, 4, 4, 1, 2, 2), _S(0, 50)),
+         (("fused", "ag2", 4, 512, 64, 128, 2, 6, 4, 1, 2, 2), _S(0, 50))]
+AHEAD += [(("coll", op, 8, 64, 2, 3, 1), _S(1, 5)) for op in ("ar2", "rsmc", "ag_llmc")]
+AHEAD += [(("fused", "rs", 4, 1024, 64, 1, 2, 1, 1), _S(0, 100)), (("fused", "rs", 4, 1024, 64, 1, 2, 1, 1, 1), _S(0, 100)),
+          (("fused", "ag", 8, 256, 64, 128, 2, 4, 4, 1, 0, 1, 0), _S(3, 60))]
+AHEAD += [(("fused", "ag", 8, 256, 64, 128, 2, 4, 4, alt, 0, 1, 1), _S(3, 60)) for alt in (1, 2)]
+
+
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
 def test_protocols_are_race_free(sims, case):
     rc, out = _run(sims[0], case)
@@ -240,16 +299,18 @@ def test_fused_ag_ring_fixed_flag_rows_survive_the_straggler(sims):
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-1500:]
 
 
-@pytest.mark.parametrize("case", [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
+NEGATIVE = [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
                                   ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
                                   ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2),
                                   ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1),
-                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2), ("fused", "ag", 2, 256, 64, 128, 2, 4, 2, 0, 2, 2)],
-                         ids=lambda c: "-".join(map(str, c[:3])))
+                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2), ("fused", "ag", 2, 256, 64, 128, 2, 4, 2, 0, 2, 2)]
+
+
+@pytest.mark.parametrize("case", NEGATIVE, ids=lambda c: "-".join(map(str, c[:3])))
 def test_negative_control_is_reported(sims, case):
     """Same kernels, flags written and polled WITHOUT release / acquire ordering: the checker must see the payload race."""
     for attempt in range(4):  # whether the unordered accesses actually meet depends on the schedule of that run
-        rc, out = _run(sims[1], case)
+        rc, out = _run(sims[1], case, fresh=attempt > 0)
         if "ThreadSanitizer: data race" in out:
             break
     assert "ThreadSanitizer: data race" in out, out[-2000:]
@@ -257,42 +318,32 @@ def test_negative_control_is_reported(sims, case):
         "the report should point into the device sources"
 
 
-@pytest.mark.parametrize("name,good,bad,expect", [
-    ("rope_sign", "lane < 16 ? f[i] * cc[i] - other * sn[i]", "lane < 16 ? f[i] * cc[i] + other * sn[i]", "rope q"),
-    ("gqa_pass_offset", "const int h0 = kvh * g_total + g_offset;", "const int h0 = kvh * g_total;", "flash decode"),
-    ("page_slot", "size_t(pos % page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return", "size_t(pos / page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return", "flash decode"),
-    ("argmax_tie", "(ov == best && oi < bi)", "(ov == best && oi > bi)", "argmax"),
-])
-def test_decode_oracles_catch_a_mutated_kernel(sims, tmp_path, name, good, bad, expect):
-    """Mutation control for the decode scenario: one token of csrc/kernels/decode.cu changed in the staged copy (rotation
-    sign, head offset of the second GQA pass, slot inside a KV page, tie rule of the sampler) — the host oracle of that
-    kernel must report it."""
-    _stage(tmp_path / "stage")
-    f = tmp_path / "stage" / "csrc" / "kernels" / "decode.cu"
-    src = f.read_text()
-    assert good in src, "the mutated expression is no longer in decode.cu: update this test"
-    f.write_text(src.replace(good, bad))
-    _build(tmp_path / "stage", tmp_path / "sim_mut")
-    rc, out = _run(tmp_path / "sim_mut", ("decode", 3, 14, 2, 70, 5, 16, 128, 64, 300, 0))
-    assert rc == 1 and "DATA MISMATCH" in out and expect in out, out[-2000:]
-
-
-@pytest.mark.parametrize("name,good,bad,expect", [
-    # the ldmatrix address ignores the 128 B swizzle the TMA applied to the stage buffer: wrong weights
-    ("swizzle", "const uint8_t* ap = lp + ((uint32_t(s4 * 2) + a_hi) ^ ph) * 16u;", "const uint8_t* ap = lp + (uint32_t(s4 * 2) + a_hi) * 16u;", "DATA MISMATCH"),
+_DECODE_CASE = ("decode", 3, 14, 2, 70, 5, 16, 128, 64, 300, 0)
+_MEGA_CASE = ("mega", 2, 3, 1, 2, 2, 0, 0, 1, 2, 64, 2)
+# name: (file under csrc/, expression, replacement, what the run must print, case, environment)
+MUTANTS = {
+    # decode path: rotation sign, head offset of the second GQA pass, slot inside a KV page, tie rule of the sampler
+    "rope_sign": ("kernels/decode.cu", "lane < 16 ? f[i] * cc[i] - other * sn[i]", "lane < 16 ? f[i] * cc[i] + other * sn[i]", "rope q", _DECODE_CASE, None),
+    "gqa_pass_offset": ("kernels/decode.cu", "const int h0 = kvh * g_total + g_offset;", "const int h0 = kvh * g_total;", "flash decode", _DECODE_CASE, None),
+    "page_slot": ("kernels/decode.cu", "size_t(pos % page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return",
+                  "size_t(pos / page_size) * kv_seq_stride + size_t(kvh) * kv_head_stride;\n    }\n    return", "flash decode", _DECODE_CASE, None),
+    "argmax_tie": ("kernels/decode.cu", "(ov == best && oi < bi)", "(ov == best && oi > bi)", "argmax", _DECODE_CASE, None),
+    # megakernel: the ldmatrix address ignores the 128 B swizzle the TMA applied to the stage buffer (wrong weights)
+    "swizzle": ("mega/megakernel.cu", "const uint8_t* ap = lp + ((uint32_t(s4 * 2) + a_hi) ^ ph) * 16u;",
+                "const uint8_t* ap = lp + (uint32_t(s4 * 2) + a_hi) * 16u;", "DATA MISMATCH", _MEGA_CASE, {"TDIST_SIM_WATCHDOG_S": "240"}),
     # tasks wait for the scoreboard value of the PREVIOUS step: consumers run before their producers
-    ("scoreboard_target", "const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1", "const uint32_t tgt0 = (step - 1) * uint32_t(t.dep0_cnt), tgt1",
-     "ThreadSanitizer: data race"),
+    "scoreboard_target": ("mega/megakernel.cu", "const uint32_t tgt0 = step * uint32_t(t.dep0_cnt), tgt1",
+                          "const uint32_t tgt0 = (step - 1) * uint32_t(t.dep0_cnt), tgt1", "ThreadSanitizer: data race", _MEGA_CASE,
+                          {"TDIST_SIM_WATCHDOG_S": "240"}),
     # the "up" half of a gate | up weight tile is fetched from the gate rows
-    ("pair_rows", "c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);", "c1 = int(e.row0 + blk * e.R);", "DATA MISMATCH"),
-])
-def test_megakernel_mutations_are_caught(sims, tmp_path, name, good, bad, expect):
-    """Mutation control for the megakernel scenario: one expression of csrc/mega/megakernel.cu changed in the staged copy."""
-    _stage(tmp_path / "stage")
-    f = tmp_path / "stage" / "csrc" / "mega" / "megakernel.cu"
-    src = f.read_text()
-    assert good in src, "the mutated expression is no longer in megakernel.cu: update this test"
-    f.write_text(src.replace(good, bad))
-    _build(tmp_path / "stage", tmp_path / "sim_mut")
-    rc, out = _run(tmp_path / "sim_mut", ("mega", 2, 3, 1, 2, 2, 0, 0, 1, 2, 64, 2), {"TDIST_SIM_WATCHDOG_S": "240"})
-    assert rc != 0 and expect in out, out[-2000:]
+    "pair_rows": ("mega/megakernel.cu", "c1 = int(e.row0 + (second ? e.pair_rows : 0u) + blk * e.R);", "c1 = int(e.row0 + blk * e.R);",
+                  "DATA MISMATCH", _MEGA_CASE, {"TDIST_SIM_WATCHDOG_S": "240"}),
+}
+
+
+@pytest.mark.parametrize("name", list(MUTANTS))
+def test_mutated_kernels_are_caught(sims, name):
+    """Mutation controls: ONE expression of csrc/kernels/decode.cu or csrc/mega/megakernel.cu changed in a staged copy — the
+    host oracle of the kernel concerned (or the sanitizer, for the scoreboard) must object."""
+    rc, out = _jobs[("mutant", name)].result()
+    assert rc != 0 and MUTANTS[name][3] in out, out[-2000:]

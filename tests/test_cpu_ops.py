@@ -156,12 +156,12 @@ def test_contextual_autotune_picks_fastest_config():
     @tunable("t_a", {"x": [3, 1, 2]}, key=lambda *a, **k: "k")
     def fa(x=0):
         calls.append(("a", x))
-        time.sleep(0.002 * x)
+        time.sleep(0.02 * x)  # (steps far above the scheduling noise of a loaded box)
 
     @tunable("t_b", {"y": [2, 0]}, key=lambda *a, **k: "k")
     def fb(y=5):
         calls.append(("b", y))
-        time.sleep(0.002 * y)
+        time.sleep(0.02 * y)
 
     def thunk():
         fa()

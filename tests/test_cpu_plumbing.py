@@ -83,6 +83,12 @@ def test_layers_suite_cpu():
     run_dist(N + "run_suite", ["--suite", "layers"], 2, timeout=1200)
 
 
+def test_prims_suite_cpu():
+    """The primitive / host-API scripts (ring put, notify, waits, heap API under its NVSHMEM names, host utils, small-message
+    all-gathers, PP) on the host heap: the parts that need CUDA peer mappings skip themselves, the rest must pass."""
+    run_dist(N + "run_suite", ["--suite", "prims"], 2, timeout=600)
+
+
 def test_mega_suite_cpu():
     """ModelBuilder graphs (per-op cases and the Qwen3 decode graph) through the eager fallback of the builder."""
     run_dist(N + "run_suite", ["--suite", "mega"], 2, timeout=1200)

@@ -1,15 +1,16 @@
-// protocol_sim.cc — runs the tutorial-size distributed kernels of this library on the CPU, one OS thread per CTA (its CUDA
-// threads are fibers) and one "GPU" per rank inside ONE process, under ThreadSanitizer. (SURVEY.md section 5 asks for a flag-protocol
-// checker; the reference has none — its substitute is noise injection on real GPUs.)
+// protocol_sim.cc — runs the distributed kernels of this library on the CPU, one OS thread per CTA (its CUDA threads are
+// fibers) and one "GPU" per rank inside ONE process, under ThreadSanitizer. (SURVEY.md section 5 asks for a flag-protocol
+// checker; the reference has none — its substitute is noise injection on real GPUs.) docs/simulator.md is the guide.
 //
-// The kernel sources are compiled UNMODIFIED up to two mechanical steps done by tests/test_cpu_protocol_sim.py when it
-// stages them: the files are cut before their launch wrappers (which use <<< >>>), and `__shared__ T name[..];` becomes a
-// reference into a per-CTA buffer. csrc/sim/shim/kernels/common.cuh stands in for the device headers: flags become C++
-// atomics with the memory orders the device code uses, payload accesses stay plain, __syncthreads() yields between fibers.
-// ThreadSanitizer then reports any payload access that is not ordered by the flag protocol, a lost wake-up shows up as the
-// 60 s wait bound, and the results are compared with a host computation. Ranks issue their calls independently (no
-// barrier between calls), as streams on different GPUs do. TDIST_SIM_SLOW_RANK=r (+ TDIST_SIM_SLOW_MS) delays every flag write of rank r:
-// the skew that opens the windows a protocol must survive.
+// The kernel sources are compiled UNMODIFIED up to three mechanical steps done by tests/test_cpu_protocol_sim.py when it
+// stages them: the files are cut before their launch wrappers (which use <<< >>> or the runtime API), `__shared__ T name[..];`
+// becomes a reference into a per-CTA buffer, and the two inline-asm functions of the megakernel call their emulations.
+// csrc/sim/shim/device/ptx.cuh stands in for csrc/device/ptx.cuh and csrc/sim/stub/*.h for the CUDA headers: flags become C++
+// atomics with the memory orders the device code uses, payload accesses stay plain, __syncthreads() yields between fibers,
+// bulk / tiled TMA copies are performed at issue. ThreadSanitizer then reports any payload access that is not ordered by the
+// flag protocol, a lost wake-up shows up as the wait bound, and the results are compared with a host computation. Ranks issue
+// their calls independently (no barrier between calls), as streams on different GPUs do. TDIST_SIM_SLOW_RANK=r
+// (+ TDIST_SIM_SLOW_MS) delays every flag write of rank r: the skew that opens the windows a protocol must survive.
 //
 //   protocol_sim queue   <ranks> <items> <item_vecs> <slots> <calls>
 //   protocol_sim ag_gemm <ranks> <rows> <N> <K> <push_ctas> <ctas> <calls> [alternate: 1 = odd calls use rows / div, 2 = even calls] [div = 2]

@@ -64,7 +64,16 @@ def job(name: str) -> str:
         _pool = ThreadPoolExecutor(max_workers=max(1, min(4, cores // 2)))  # a launch is 2-4 ranks, mostly interpreter start-up
         for k, spec in JOBS.items():
             _futures[k] = _pool.submit(_launch, *spec)
+    if _futures[name].cancel():  # still queued (e.g. a run with -k): run it here instead of waiting for its turn
+        return _launch(*JOBS[name])
     return _futures[name].result()
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _drop_unasked_launches():
+    yield
+    for f in _futures.values():  # (a run with -k: do not finish the rest of the queue at exit)
+        f.cancel()
 
 
 @pytest.mark.parametrize("world", [1, 2])

@@ -120,7 +120,9 @@ def sims(tmp_path_factory):
         _submit(broken, case)
     for name, (rel, old, new, expect, case, env) in MUTANTS.items():  # mutants: stage, build and run in the pool as well
         _jobs[("mutant", name)] = _POOL.submit(_mutant, d / f"mut_{name}", rel, old, new, case, env)
-    return good, broken
+    yield good, broken
+    for f in _jobs.values():  # a run with -k leaves most of the queue unasked for: drop it instead of finishing it at exit
+        f.cancel()
 
 
 def _mutant(dst, rel, old, new, case, env):
@@ -163,7 +165,10 @@ def _run(exe, args, env_extra=None, fresh=False):
     """(rc, output) of one simulator run; the result of a run that was submitted ahead is reused unless `fresh`."""
     if fresh:
         return _run_now(exe, args, env_extra)
-    return _submit(exe, args, env_extra).result()
+    fut = _submit(exe, args, env_extra)
+    if fut.cancel():  # still queued (e.g. a run with -k asks for a late case first): run it here instead of waiting for its turn
+        return _run_now(exe, args, env_extra)
+    return fut.result()
 
 
 CLEAN = [

@@ -406,8 +406,8 @@ __device__ __forceinline__ void rs_reduce_body(const GemmParams& p, uint32_t epo
   for (int u = blockIdx.x; u < units; u += gridDim.x) {
     const int j = u / slices, sl = u - j * slices;
     if (j != last_j) {
-      // flags layout (RS): [W src][bps], written by src when its block j of my segment is complete
-      if (threadIdx.x < W) wait_ge_sys(p.flags + threadIdx.x * bps + j, epoch);
+      // flags layout (RS): [W src][bps (or the fixed row, GemmParams::flag_row)], written by src when its block j of my segment is complete
+      if (threadIdx.x < W) wait_ge_sys(p.flags + size_t(threadIdx.x) * (p.flag_row > 0 ? p.flag_row : bps) + j, epoch);
       __syncthreads();
       last_j = j;
     }
@@ -697,6 +697,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
       // tile's stores are issued: by then its NVLink stores have drained, so the fence costs nothing instead of
       // stalling the epilogue for a link round trip per tile.
       int pend_t = -1, pend_shard = 0, pend_blk = 0, pend_nblk = 0;
+      // [sim:epi_publish begin] (csrc/sim runs this lambda against rs_reduce_body on the CPU)
       auto publish = [&](int t_done, int shard, int blk, int n_blk) {
         if (!(p.debug & 2)) ptx::fence_acq_rel_sys();
         if (p.mode == GEMM_RS && p.variant == VARIANT_NVLS) {
@@ -710,12 +711,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_sm100_kernel(const __gri
           if (done == static_cast<uint32_t>(tiles_n)) {
             p.counters[cidx] = 0;
             ptx::fence_acq_rel_sys();
-            notify(p.ctx, p.flags + p.ctx.rank * bps + blk, shard, epoch);
+            notify(p.ctx, p.flags + size_t(p.ctx.rank) * (p.flag_row > 0 ? p.flag_row : bps) + blk, shard, epoch);
           }
         } else {
           ptx::st_release_sys(p.flags + t_done, epoch);
         }
       };
+      // [sim:epi_publish end]
       for (int t = gemm_cta; t < tiles; t += num_gemm) {
         const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
         if (p.block_expert != nullptr && p.block_expert[tc.blk] < 0) continue;

@@ -62,6 +62,45 @@ void fused_cta(const tdist::GemmParams& p) {
   phase_end(p.ps, phase_base, 2);
 }
 
+// GEMM + RS without a multicast mapping (the scatter form): the epilogue stores every partial tile into the OWNER's slot
+// buffer over the peer mapping and publishes it one tile later through the kernel's own `publish` lambda (text between the
+// [sim:epi_publish] markers: per-(owner, block) tile counter, then the flag on the owner); after its tiles every CTA runs the
+// real rs_reduce_body over this rank's segment.
+template <int BLOCK_N>
+void fused_rs_scatter_cta(const tdist::GemmParams& p) {
+  using namespace tdist;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_n = (p.N + BLOCK_N - 1) / BLOCK_N;
+  const int tiles_m = blocks_per_shard(p) * p.ctx.world;
+  const int tiles = tiles_m * tiles_n;
+  const int num_gemm = gridDim.x - p.num_comm_ctas;
+  const int gemm_cta = static_cast<int>(blockIdx.x) - p.num_comm_ctas;
+  const uint32_t phase_base = phase_begin(p.ps);
+  const uint32_t epoch = phase_base + 2;
+  const int parity = (epoch >> 1) & 1;
+  if (warp == 4 && lane == 0) {
+#include "kernels/gemm_epi_publish.inc"
+    int pend_t = -1, pend_shard = 0, pend_blk = 0, pend_nblk = 0;
+    for (int t = gemm_cta; t < tiles; t += num_gemm) {
+      const TileCoord tc = tile_coord(p, t, tiles_m, tiles_n);
+      if (pend_t >= 0) publish(pend_t, pend_shard, pend_blk, pend_nblk);  // (the kernel publishes a tile one tile later)
+      const size_t seg_elems = size_t(p.rows_per_rank) * p.N;
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(symm_at(p.ctx, static_cast<char*>(p.c), tc.shard) + size_t(parity) * p.ws_parity_bytes +
+                                                             size_t(p.ctx.rank) * seg_elems * 2);
+      const int row0 = tc.row0 - tc.shard * p.rows_per_rank, col0 = tc.n_blk * BLOCK_N;
+      for (int r = row0; r < min(row0 + kBlockM, p.rows_per_rank); ++r)
+        for (int c = col0; c < min(col0 + BLOCK_N, p.N); ++c)
+          dst[size_t(r) * p.N + c] = __float2bfloat16(fused_val(p.ctx.rank, tc.shard * p.rows_per_rank + r, c));
+      pend_t = t, pend_shard = tc.shard, pend_blk = tc.blk, pend_nblk = tc.n_blk;
+      sim_yield();
+    }
+    if (pend_t >= 0) publish(pend_t, pend_shard, pend_blk, pend_nblk);
+  }
+  __syncthreads();
+  rs_reduce_body<BF16>(p, epoch);
+  phase_end(p.ps, phase_base, 2);
+}
+
 // The CTA-pair kernel (gemm_sm100_2cta.cuh, the default of the flagship): two consecutive CTAs share a 256-row tile, CTA
 // `cta_rank` of the pair owns its 128-row half; both run a reducer and a publisher of their own.
 template <int BLOCK_N>
@@ -298,7 +337,7 @@ int run_fused_ag(int world, int max_rows, int N, int K, int push_ctas, int ctas,
   return g_errors ? 1 : 0;
 }
 
-// mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; "rs2": the CTA-pair kernel's form, `ctas` must be even; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
+// mode: "rs" GEMM + ReduceScatter (NVLS pull protocol; "rsl": the scatter form used without a multicast mapping; "rs2": the CTA-pair kernel's form, `ctas` must be even; `mc` selects in-switch reduction or peer loads), "ar1" / "ar2" GEMM +
 // AllReduce one-shot / two-shot. Calls alternate between M and M / 2 on the same buffers when `alternate` is 1 (odd calls
 // smaller) or 2 (even calls smaller). `fixed_rows`: one flag row per source rank of constant length (GemmParams::flag_row).
 int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, int calls, int mc, int alternate, int fixed_rows) {
@@ -309,7 +348,7 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
   using namespace tdist;
   using bf16 = __nv_bfloat16;
   constexpr int BLOCK_N = 64;
-  const bool pair = mode == "rs2", rs = mode == "rs" || pair, one_shot = mode == "ar1";
+  const bool pair = mode == "rs2", scatter = mode == "rsl", rs = mode == "rs" || pair || scatter, one_shot = mode == "ar1";
   const size_t W = world;
   const size_t parity_bytes = size_t(max_M) * N * 2;
   const size_t out_bytes = size_t(max_M) * N * 2;  // AR two-shot: the output is symmetric (peers store into it)
@@ -319,7 +358,8 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
   auto M_of = [=](int call) { return alternate && (call & 1) == (alternate & 1) ? max_M / 2 : max_M; };
   sim::run_ranks(world, [&](int rank) {
     uint32_t state[2] = {0, 0};
-    uint32_t counters[4] = {0, 0, 0, 0};
+    std::vector<uint32_t> counter_words(W * size_t((max_M / world + 127) / 128) + 4, 0);  // scatter form: tiles per (owner, block)
+    uint32_t* counters = counter_words.data();
     std::vector<bf16> out_local(size_t(max_M) * N);
     for (int call = 0; call < calls; ++call) {
       const int M = M_of(call);
@@ -333,7 +373,7 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       p.K = 64;
       p.ldc = N;
       p.mode = rs ? GEMM_RS : GEMM_AR;
-      p.variant = VARIANT_NVLS;
+      p.variant = scatter ? VARIANT_LEGACY : VARIANT_NVLS;
       p.is_bf16 = 1;
       p.group_m = 8;
       p.rows_per_rank = rs ? M / world : M;
@@ -350,6 +390,8 @@ int run_fused(const std::string& mode, int world, int max_M, int N, int ctas, in
       const GemmParams* pp = &p;
       if (pair)
         sim::launch(rank, ctas, 256, [=] { fused_pair_cta<BLOCK_N>(*pp); });
+      else if (scatter)
+        sim::launch(rank, ctas, 256, [=] { fused_rs_scatter_cta<BLOCK_N>(*pp); });
       else
         sim::launch(rank, ctas, 256, [=] { fused_cta<BLOCK_N>(*pp); });
       const bf16* got = static_cast<const bf16*>(p.out);

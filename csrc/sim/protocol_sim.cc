@@ -20,7 +20,7 @@
 //   protocol_sim moe_rs <ranks> <tokens> <topk> <row_vecs> <ctas> <calls> [alternate]
 //   protocol_sim a2a <ranks> <max rows per peer> <row_vecs> <experts per rank> <ctas per peer> <calls>
 //   protocol_sim ep <ranks> <tokens> <hidden> <experts> <ctas> <calls> [fp8]
-//   protocol_sim fused rs|rs2|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
+//   protocol_sim fused rs|rsl|rs2|ar1|ar2 <ranks> <M> <N> <ctas> <calls> [in-switch reduction 0/1] [alternate] [fixed flag rows 0/1]   (production GEMM comm side)
 //   protocol_sim decode <batch> <Hq> <Hkv> <max cached tokens> <kv splits> <page size, 0 = dense> <hidden> <intermediate> <vocab> [fp16]
 //                                                                    (one simulated GPU: one decode step, every kernel against a host oracle)
 //   protocol_sim mega <ranks> <CTAs> <layers> <batch> <steps> <graph: 0 fused, 1 op by op, 2 fused + one-task attention> <in-switch all-reduce 0/1>

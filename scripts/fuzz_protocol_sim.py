@@ -41,7 +41,7 @@ def random_case(rng):
                 push + (c([2, 4]) if pair else c([1, 2, 4])),
                 c([1, 2, 4]), c([0, 0, 1, 2]), c([1, 2, 4, 8]), c([1, 2, 4, 8])], W
     if kind == "fused":
-        mode = c(["rs", "rs2", "ar1", "ar2"])
+        mode = c(["rs", "rsl", "rs2", "ar1", "ar2"])
         M = W * c([128, 256, 384]) if mode != "rs2" else W * c([256, 384, 512])
         ctas = c([2, 4, 6]) if mode == "rs2" else c([1, 2, 3, 5])  # the CTA-pair form needs whole pairs
         return ["fused", mode, W, M, c([64, 128, 192]), ctas, c([1, 2, 4]), c([0, 1]), c([0, 0, 1, 2]), 1], W

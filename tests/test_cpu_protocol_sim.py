@@ -82,10 +82,11 @@ def _stage(dst: Path) -> None:
     pair = (ROOT / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").read_text()  # the CTA-pair kernel: tile order + publisher
     cut = pair.index("\ntemplate <int BLOCK_N, int STAGES>\n__global__")
     (dst / "csrc" / "kernels" / "gemm_sm100_2cta.cuh").write_text(pair[:cut] + "\n}  // namespace tdist\n")
-    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair), ("ag_wait", gemm), ("ag_wait_pair", pair)):
+    for name, text in (("rs_publish", gemm), ("ar_publish", gemm), ("rs_publish_pair", pair), ("ag_wait", gemm), ("ag_wait_pair", pair),
+                       ("epi_publish", gemm)):
         a = text.index("\n", text.index(f"[sim:{name} begin]")) + 1
         snippet = text[a:text.index(f"// [sim:{name} end]")]
-        assert spin.search(snippet) or name.startswith("ag_wait"), name  # (the AG wait polls flags, which yield by themselves)
+        assert spin.search(snippet) or name.startswith("ag_wait") or name == "epi_publish", name  # (the AG wait polls flags, which yield by themselves)
         (dst / "csrc" / "kernels" / f"gemm_{name}.inc").write_text(spin.sub(r"\1 sim_yield(); }", snippet))
 
 
@@ -202,6 +203,10 @@ CLEAN += [("fused", "rs", 3, 768, 128, 3, 3, 1), ("fused", "rs", 3, 768, 128, 3,
           ("fused", "ar2", 3, 256, 128, 2, 3, 1), ("fused", "ar2", 2, 256, 128, 2, 2, 0), ("fused", "ar2", 8, 256, 64, 2, 2, 1),
           ("fused", "rs", 3, 768, 128, 3, 4, 1, 2, 1), ("fused", "rs", 8, 2048, 64, 2, 3, 1, 1, 1), ("fused", "rs", 3, 768, 128, 3, 3, 0, 0, 1),
           ("fused", "ar1", 4, 256, 128, 2, 4, 1, 1, 1), ("fused", "ar2", 4, 256, 128, 2, 4, 1, 2, 1),
+          # "rsl": the scatter form of GEMM + RS (no multicast mapping): stores into the owner's slots, the epilogue's publish
+          # lambda (tile counter per (owner, block), then the flag), rs_reduce_body; last argument: fixed flag rows
+          ("fused", "rsl", 3, 768, 128, 3, 3, 0), ("fused", "rsl", 2, 512, 64, 2, 4, 0, 1), ("fused", "rsl", 8, 2048, 64, 4, 2, 0),
+          ("fused", "rsl", 4, 1024, 192, 5, 4, 0, 2), ("fused", "rsl", 4, 1024, 64, 2, 4, 0, 1, 1),
           # "rs2": the CTA-pair kernel's publisher and tile order (the flagship's default), incl. shards of 1.5 pair tiles
           ("fused", "rs2", 2, 1024, 128, 2, 2, 1), ("fused", "rs2", 3, 1536, 128, 4, 3, 1), ("fused", "rs2", 4, 1536, 64, 2, 4, 1, 2),
           ("fused", "rs2", 4, 1536, 64, 4, 4, 1, 1, 1), ("fused", "rs2", 8, 2048, 64, 2, 2, 1), ("fused", "rs2", 3, 1152, 128, 2, 3, 0, 0, 1)]
@@ -241,6 +246,7 @@ AHEAD += [(("coll", op, 8, 64, 2, 3, 1), _S(1, 5)) for op in ("ar2", "rsmc", "ag
 AHEAD += [(("fused", "rs", 4, 1024, 64, 1, 2, 1, 1), _S(0, 100)), (("fused", "rs", 4, 1024, 64, 1, 2, 1, 1, 1), _S(0, 100)),
           (("fused", "ag", 8, 256, 64, 128, 2, 4, 4, 1, 0, 1, 0), _S(3, 60))]
 AHEAD += [(("fused", "ag", 8, 256, 64, 128, 2, 4, 4, alt, 0, 1, 1), _S(3, 60)) for alt in (1, 2)]
+AHEAD += [(("fused", "rsl", 8, 2048, 64, 1, 4, 0, 1, 1), _S(3, 60))]
 
 
 @pytest.mark.parametrize("case", CLEAN, ids=lambda c: "-".join(map(str, c)))
@@ -302,13 +308,17 @@ def test_fused_ag_ring_fixed_flag_rows_survive_the_straggler(sims):
     for alt in (1, 2):
         rc, out = _run(sims[0], ("fused", "ag", 8, 256, 64, 128, 2, 4, 4, alt, 0, 1, 1), {"TDIST_SIM_SLOW_RANK": "3", "TDIST_SIM_SLOW_MS": "60"})
         assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-1500:]
+    # the scatter form of GEMM + RS (unicast flags [source][block]) under the same conditions
+    rc, out = _run(sims[0], ("fused", "rsl", 8, 2048, 64, 1, 4, 0, 1, 1), {"TDIST_SIM_SLOW_RANK": "3", "TDIST_SIM_SLOW_MS": "60"})
+    assert rc == 0 and "data ok" in out and "ThreadSanitizer" not in out and "timed out" not in out, out[-1500:]
 
 
 NEGATIVE = [("queue", 2, 6, 64, 2, 2), ("ag_gemm", 2, 128, 64, 16, 1, 3, 2), ("gemm_rs", 2, 128, 64, 16, 2, 2),
                                   ("coll", "ar2", 2, 96, 2, 2), ("coll", "rsmc", 2, 96, 2, 2), ("coll", "selftest", 2, 96, 2, 2),
                                   ("moe_rs", 2, 32, 2, 3, 2, 2), ("a2a", 2, 16, 3, 2, 1, 2), ("ep", 2, 8, 256, 4, 2, 2),
                                   ("fused", "rs", 2, 256, 64, 1, 1, 1), ("fused", "ar2", 2, 128, 64, 1, 1, 1),
-                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2), ("fused", "ag", 2, 256, 64, 128, 2, 4, 2, 0, 2, 2)]
+                                  ("mega", 2, 3, 1, 2, 2, 0, 1, 1, 2, 64, 2), ("fused", "ag", 2, 256, 64, 128, 2, 4, 2, 0, 2, 2),
+            ("fused", "rsl", 2, 256, 64, 1, 1, 0)]
 
 
 @pytest.mark.parametrize("case", NEGATIVE, ids=lambda c: "-".join(map(str, c[:3])))

@@ -1,22 +1,22 @@
-"""Flag-protocol checker: device code of this library is compiled for the CPU and run with 1-8 simulated ranks in one process
-under ThreadSanitizer (csrc/sim/):
+"""Protocol simulator: device code of this library is compiled for the CPU and run with 1-8 simulated ranks in one process
+under ThreadSanitizer (csrc/sim/, docs/simulator.md), on top of the REAL symm.cuh and common.cuh:
   * the PRODUCTION collectives of csrc/kernels/collectives.cu (barrier, 4 all-reduces, 5 all-gathers incl. the LL packet
     protocol, 2 reduce-scatters; NVLS emulated by reading / writing every rank's copy), primitives_selftest.cu (every
-    NVSHMEM-style primitive of csrc/device/symm.cuh), the MoE kernels of moe.cu (align / sort, tile swizzle, gathers, top-k
-    reduce, fused top-k reduce + reduce-scatter) and the expert-parallel kernels of ep_a2a.cu (low-latency all-to-all,
-    counts exchange, dispatch with bf16 and fp8 payload, combine), and the communication side of the fused tcgen05 GEMM
-    (gemm_sm100.cuh: the real reducer bodies rs_pull_body / ar_reduce_body, the real publisher loops and the real tile
-    order around a stand-in for the tensor-core epilogue), on top of the REAL symm.cuh and common.cuh;
-  * the tutorial-size kernels (csrc/tutorials/*.cu — the queue of tutorial 1 and the two overlap protocols of tutorials
-    7 / 8, which the production tcgen05 GEMM kernels follow).
-Only csrc/device/ptx.cuh (inline PTX) and <cuda_runtime.h> are replaced by host stand-ins.
+    NVSHMEM-style primitive of csrc/device/symm.cuh), the MoE kernels of moe.cu and the expert-parallel kernels of ep_a2a.cu;
+  * the communication side of the fused tcgen05 GEMMs, both kernels and every form: push bodies and the producer warp's
+    arrival wait of AG + GEMM, reducers, publishers and tile orders of GEMM + RS / GEMM + AR, around stand-ins for the TMA
+    loads and the tensor-core epilogue;
+  * the decode megakernel (csrc/mega/megakernel.cu) with its native builder (builder.cc) as they are — TMA tiled loads,
+    mbarrier phases, ldmatrix and mma.sync emulated — on a small Qwen3-style decoder, against a double-precision model;
+  * the decode-path kernels of decode.cu (functional, against host oracles) and the tutorial-size kernels (csrc/tutorials).
+Only csrc/device/ptx.cuh, csrc/runtime/driver.h and the CUDA headers are replaced by host stand-ins.
 
 What a pass means: for every payload access of every rank there is a release / acquire chain through the flags (no data
-race), nobody waits for a flag that never comes (no 60 s wait bound), and the results equal a host computation — over
-several back-to-back calls per rank without any barrier in between, with calls of different sizes on the same buffers and
-with one rank straggling by 30 ms per flag write. The negative control (flags written without release ordering) must be
-reported as a race in every kernel, otherwise a pass would prove nothing.
-No GPU and no CUDA toolkit needed: g++ with -fsanitize=thread."""
+race), nobody waits for a flag that never comes (no wait bound), and the results equal a host computation — over several
+back-to-back calls per rank without any barrier in between, with calls of different sizes on the same buffers and with one
+rank straggling per flag write. The negative controls (flags written without release ordering) must be reported as races
+and the mutation controls (one expression of a kernel changed) as wrong results, otherwise a pass would prove nothing.
+The cases run through a small process pool (see _POOL). No GPU and no CUDA toolkit needed: g++ with -fsanitize=thread."""
 import os
 import re
 import shutil
